@@ -1,0 +1,141 @@
+/* lvb_gpu.h — C-ABI of the B200 (sm_100a) Fitch tree-length engine for LVB.
+ *
+ * This is the whole drop-in boundary: plain pointers and sizes, no C++ or torch
+ * types.  LVB's host code (C compiled as C++, see /root/reference/Makefile:74-81)
+ * keeps its structs (TREESTACK_TREE_NODES, DataStructure) and calls these entry
+ * points where it used to touch state rows on the CPU.  Reference locations each
+ * entry point replaces are given as file:line relative to the reference tree.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; the message is in
+ *     lvb_gpu_last_error() (per thread).  LVB host code turns non-zero into
+ *     crash() (src/Error.c:49-62); see INTEGRATION.md.
+ *   - nodes are numbered as in LVB: 0..n-1 leaves (taxon i), n..2n-4 internal; the
+ *     root is a leaf index with two children (src/TreeOperations.c:897-900, :588).
+ *   - topologies are passed as two strided int64 views so that LVB's own array of
+ *     40-byte TREESTACK_TREE_NODES structs (src/LVB.h:121-128) can be handed over
+ *     without conversion: left = &tree[0].left, right = &tree[0].right,
+ *     stride_bytes = sizeof(TREESTACK_TREE_NODES).  Plain int64 arrays use stride 8.
+ *   - one host thread per context; all device work of a context runs on one stream.
+ *   - there is no CPU fallback anywhere behind this interface.
+ */
+#ifndef LVB_GPU_H
+#define LVB_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lvb_gpu_ctx lvb_gpu_ctx;
+
+/* A tree (or candidate tree) as getplen() sees it (src/TreeEvaluation.c:49-62):
+ * child links, the root, and the set of internal nodes whose state rows must be
+ * recomputed — LVB's "dirty" nodes, i.e. those whose sitestate[0] == 0
+ * (src/TreeOperations.c:49-59, 88-103, 631-635).  Only left/right of the dirty nodes
+ * and of the root are read. */
+typedef struct lvb_gpu_topology
+{
+    const int64_t *left;   /* left[i]  at byte offset i*stride_bytes */
+    const int64_t *right;  /* right[i] at byte offset i*stride_bytes */
+    int64_t stride_bytes;  /* 40 for TREESTACK_TREE_NODES[], 8 for int64_t[] */
+    int64_t root;          /* leaf index */
+    const int64_t *dirty;  /* internal node numbers, any order; ignored if n_dirty < 0 */
+    int64_t n_dirty;       /* < 0: every internal node (what ss_init / lvb_reroot leave) */
+} lvb_gpu_topology;
+
+/* ---- device / context:  Main.c:82 lvb_initialize() gains device init ---- */
+int lvb_gpu_device_count(int *count);
+int lvb_gpu_init(int device, lvb_gpu_ctx **ctx);
+int lvb_gpu_shutdown(lvb_gpu_ctx *ctx);
+const char *lvb_gpu_last_error(void);
+/* the CUDA stream all work of this context is enqueued on (a cudaStream_t) */
+void *lvb_gpu_stream(lvb_gpu_ctx *ctx);
+
+/* ---- packed state matrix:  DataOperations.c:164-249 DNAToBinary output, and
+ * TreeOperations.c:1500-1513 ss_init (leaf rows installed once, on the device) ----
+ * enc_rows: n pointers to nwords 64-bit words each (Solve.c:516-519 layout).
+ * [word_begin, word_begin+word_count) is the block of words this context owns
+ * (site-block sharding, same decomposition as TreeEvaluation.c:95-97); pass 0,nwords
+ * for the whole alignment.  max_trees bounds lvb_gpu_tree_create(). */
+int lvb_gpu_matrix_upload(lvb_gpu_ctx *ctx, int64_t n, int64_t nwords, const uint64_t *const *enc_rows,
+                          int64_t word_begin, int64_t word_count, int64_t max_trees);
+/* same, from one contiguous n x nwords row-major array */
+int lvb_gpu_matrix_upload_flat(lvb_gpu_ctx *ctx, int64_t n, int64_t nwords, const uint64_t *enc,
+                               int64_t word_begin, int64_t word_count, int64_t max_trees);
+/* DNAToBinary on the device: rows = n pointers to m characters (after matchange);
+ * returns non-zero on a symbol DNAToBinary would crash on (DataOperations.c:235-241). */
+int lvb_gpu_matrix_pack(lvb_gpu_ctx *ctx, int64_t n, int64_t m, const char *const *rows,
+                        int64_t word_begin, int64_t word_count, int64_t max_trees);
+
+/* ---- trees: device-resident state rows + cached per-node change counts of one
+ * search chain's current tree (what treealloc gives Anneal, TreeOperations.c:914-955;
+ * Solve.c:194-197).  A new tree has every internal node dirty. ---- */
+int lvb_gpu_tree_create(lvb_gpu_ctx *ctx, int *tree);
+int lvb_gpu_tree_destroy(lvb_gpu_ctx *ctx, int tree);
+/* treecopy with state sets (TreeOperations.c:737-773), device to device */
+int lvb_gpu_tree_copy(lvb_gpu_ctx *ctx, int dst_tree, int src_tree);
+
+/* ---- getplen that stores (TreeEvaluation.c:49-270): recompute the dirty nodes of
+ * `topo` in post-order, write their state rows and change counts into `tree`, add the
+ * root step (:238-264), return the tree length.  Used for the first evaluation
+ * (n_dirty < 0), for an accepted proposal (replaces treecopy + SwapTrees,
+ * TreeOperations.c:737-773, 1062-1080; Solve.c:323, 370) and for re-rooting
+ * (TreeOperations.c:576-656: only nodes on the old-root..new-root path change).
+ * length may be NULL, in which case the call does not wait for the device. ---- */
+int lvb_gpu_tree_commit(lvb_gpu_ctx *ctx, int tree, const lvb_gpu_topology *topo, int64_t *length);
+
+/* the same for several trees at once (independent SA replicates): trees[] must be distinct */
+int lvb_gpu_commit_batch(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                         int64_t *lengths);
+
+/* ---- getplen on proposals, score only (Solve.c:300, StartingTemperature.c:128):
+ * candidate k is `topos[k]`, a rearrangement of the current tree `trees[k]` whose
+ * dirty list names every node whose subtree changed (what mutate_nni/spr/tbr mark,
+ * TreeOperations.c:207, 330-334, 520-537).  Nothing is written to the trees.
+ * All candidates are evaluated in one launch; lengths[k] is what getplen would
+ * return for candidate k. ---- */
+int lvb_gpu_score_batch(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                        int64_t *lengths);
+
+/* ---- parity / debugging (treedump, TreeOperations.c:1082-1112) ---- */
+/* state row of `node` (leaf or internal) of `tree`: word_count words of this context's block */
+int lvb_gpu_download_row(lvb_gpu_ctx *ctx, int tree, int64_t node, uint64_t *out);
+/* cached change counts of all 2n-3 nodes (leaves give 0), summed over this context's block */
+int lvb_gpu_tree_changes(lvb_gpu_ctx *ctx, int tree, int64_t *changes);
+
+/* ---- multi-GPU site-block sharding: one context per rank, each owning a block of
+ * words; per-tree partial lengths are summed with one NCCL all-reduce over NVLink
+ * inside commit/score_batch once a communicator is attached.  The 128-byte id comes
+ * from rank 0 and is distributed by the host program (MPI, torch.distributed, a file). ---- */
+int lvb_gpu_comm_unique_id(void *id128);
+int lvb_gpu_comm_init(lvb_gpu_ctx *ctx, int nranks, int rank, const void *id128);
+
+/* ---- introspection for tests and bench ---- */
+/* number of kernel launches issued by this context so far */
+int64_t lvb_gpu_launch_count(lvb_gpu_ctx *ctx);
+/* device time (ms) of the Fitch kernel of the most recent commit/score_batch call, measured
+ * with CUDA events on the context's stream; waits for the kernel to finish */
+int lvb_gpu_last_kernel_ms(lvb_gpu_ctx *ctx, float *ms);
+/* sum of the device times (ms) of all Fitch kernel launches of this context since the last reset,
+ * from CUDA events recorded on the context's stream around each launch; waits for pending ones */
+int lvb_gpu_kernel_time(lvb_gpu_ctx *ctx, double *total_ms, int64_t *launches, int reset);
+/* launch again the batch left on the device by the last commit/score call (same programs, no
+ * host compile, no host-to-device copy): device-resident timing, and re-scoring after the trees
+ * changed.  lengths may be NULL (no wait). */
+int lvb_gpu_rerun_last_batch(lvb_gpu_ctx *ctx, int64_t *lengths);
+/* wait for all work enqueued on the context's stream */
+int lvb_gpu_synchronize(lvb_gpu_ctx *ctx);
+/* Host-only: compile `topo` into the instruction stream the kernels execute, without a device.
+ * instr receives up to cap 16-byte instructions {a, b, node, ctl}; returns the count in *n_instr
+ * and the number of on-chip stack slots in *n_slots.
+ * Used by the CPU tests of the schedule compiler. */
+int lvb_gpu_compile_schedule(int64_t n, const lvb_gpu_topology *topo, int store, int32_t *instr, int64_t cap,
+                             int64_t *n_instr, int64_t *n_slots);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LVB_GPU_H */

@@ -1,0 +1,49 @@
+/* fitch_kernels.h — launch wrappers of the sm_100a kernels (fitch_kernels.cu). */
+#ifndef LVB_B200_FITCH_KERNELS_H
+#define LVB_B200_FITCH_KERNELS_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "fitch_isa.h"
+
+namespace lvbgpu
+{
+
+/* Everything a batch launch needs; lives in kernel parameter space. */
+struct ExecParams
+{
+    uint4 *pool;                 /* row pool: rows [0,n) leaves, then I rows per tree */
+    int64_t stride_u4;           /* row stride in 16-byte columns */
+    int32_t ncols;               /* columns to process (= stride_u4) */
+    int32_t n;                   /* leaves */
+    int32_t n_internal;          /* I = n - 3 */
+    int32_t n_prog;
+    int32_t n_colblocks;
+    int32_t n_slots;             /* stack slots of the deepest program in the batch */
+    const FitchInstr *instr;
+    const FitchProgram *prog;
+    unsigned long long *totals;  /* [n_prog] += change counts (and base length in score mode) */
+    int32_t *cnts;               /* [n_instr of batch] per-instruction counts (store mode) */
+    const int32_t *chg;          /* [trees][I] cached per-node change counts */
+    const long long *sum_chg;    /* [trees] sum of chg over internal nodes */
+};
+
+/* block: threads per CTA (multiple of 32).  per_node: store-mode batch (per-instruction
+ * counts are produced, base length is not added). */
+cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cudaStream_t stream);
+
+/* After a store-mode batch: chg[tree][node] <- new count, sum_chg[tree] += delta,
+ * lengths[p] <- sum_chg[tree] + root step counts.  Trees of the batch must be distinct. */
+cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, const int32_t *cnts,
+                                   int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
+                                   cudaStream_t stream);
+
+/* DNAToBinary on the device (reference: src/DataOperations.c:164-249).  text: n x m bytes
+ * row-major; writes words [word_begin, word_begin + word_count) of each leaf row into the pool;
+ * *bad is set to 1 + the offending byte if a symbol is not allowed. */
+cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int64_t word_begin, int64_t word_count,
+                            uint4 *pool, int64_t stride_u4, int *bad, cudaStream_t stream);
+
+} // namespace lvbgpu
+#endif

@@ -1,0 +1,792 @@
+/* lvb_gpu.cu — context, device memory and the C-ABI of include/lvb_gpu.h.
+ *
+ * Device-resident layout (HBM), per context:
+ *   pool      one allocation of (n + max_trees*(n-3)) rows x stride_u4 16-byte columns.
+ *             rows [0,n)            : the packed alignment (DNAToBinary words of this
+ *                                     context's word block), padded to a 128-byte multiple
+ *                                     with all-ones ('N', DataOperations.c:187-188)
+ *             rows n + t*(n-3) + k  : state row of internal node n+k of device tree t
+ *   chg       int32 [max_trees][n-3] cached per-node change counts (.changes, LVB.h:125)
+ *   sum_chg   int64 [max_trees]      their sum per tree
+ * One state row per node: an accepted proposal is committed in place (only its dirty
+ * rows are rewritten), rejected proposals are scored without writing, so the reference's
+ * whole-tree copy per proposal (treecopy, TreeOperations.c:737-773) has no counterpart.
+ */
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/lvb_gpu.h"
+#include "fitch_isa.h"
+#include "fitch_kernels.h"
+#include "schedule.h"
+
+using namespace lvbgpu;
+
+static thread_local std::string g_err;
+
+static int fail(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CU(call)                                                                                                      \
+    do                                                                                                                \
+    {                                                                                                                 \
+        cudaError_t e_ = (call);                                                                                      \
+        if (e_ != cudaSuccess)                                                                                        \
+            return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);                  \
+    } while (0)
+
+/* ---- NCCL, bound at run time so that the library loads where NCCL is absent ---- */
+struct NcclId
+{
+    char internal[128];
+};
+struct NcclApi
+{
+    void *lib = nullptr;
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+enum
+{
+    kNcclInt32 = 2,
+    kNcclInt64 = 4,
+    kNcclSum = 0
+};
+
+static int nccl_load()
+{
+    if (g_nccl.lib)
+        return 0;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names)
+    {
+        g_nccl.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.lib)
+            break;
+    }
+    if (!g_nccl.lib)
+        return fail("NCCL: cannot dlopen libnccl.so.2: %s", dlerror());
+    *(void **)&g_nccl.GetUniqueId = dlsym(g_nccl.lib, "ncclGetUniqueId");
+    *(void **)&g_nccl.CommInitRank = dlsym(g_nccl.lib, "ncclCommInitRank");
+    *(void **)&g_nccl.AllReduce = dlsym(g_nccl.lib, "ncclAllReduce");
+    *(void **)&g_nccl.CommDestroy = dlsym(g_nccl.lib, "ncclCommDestroy");
+    *(void **)&g_nccl.GetErrorString = dlsym(g_nccl.lib, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy)
+        return fail("NCCL: missing symbols in libnccl");
+    return 0;
+}
+
+struct lvb_gpu_ctx
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+
+    int64_t n = 0, nwords = 0, word_begin = 0, word_count = 0, B = 0, I = 0;
+    int64_t stride_u4 = 0, max_trees = 0;
+    uint4 *pool = nullptr;
+    int32_t *chg = nullptr;
+    long long *sum_chg = nullptr;
+    std::vector<uint8_t> tree_used, tree_ready;
+    ScheduleCompiler *sc = nullptr;
+
+    /* batch staging */
+    std::vector<FitchInstr> instr;
+    std::vector<FitchProgram> prog;
+    FitchInstr *d_instr = nullptr, *h_instr = nullptr;
+    size_t cap_instr = 0;
+    FitchProgram *d_prog = nullptr, *h_prog = nullptr;
+    size_t cap_prog = 0;
+    unsigned long long *d_totals = nullptr;
+    long long *h_totals = nullptr;
+    int32_t *d_cnts = nullptr;
+    int block_override = 0;
+
+    int64_t launches = 0;
+
+    /* the batch that is resident in d_instr/d_prog (for lvb_gpu_rerun_last_batch) */
+    int64_t last_K = 0;
+    bool last_store = false;
+    int last_slots = 0;
+    /* device time of the Fitch kernel, accumulated over launches (events on the stream) */
+    static const int kEvRing = 32;
+    cudaEvent_t ring0[kEvRing] = {}, ring1[kEvRing] = {};
+    int ring_used = 0;
+    double kernel_ms_total = 0;
+    int64_t kernel_launches_timed = 0;
+
+    void *comm = nullptr;
+    int nranks = 1, rank = 0;
+};
+
+static int ensure_batch_capacity(lvb_gpu_ctx *c, size_t n_instr, size_t n_prog)
+{
+    if (n_instr > c->cap_instr)
+    {
+        size_t cap = c->cap_instr ? c->cap_instr : 4096;
+        while (cap < n_instr)
+            cap *= 2;
+        if (c->d_instr)
+        {
+            CU(cudaStreamSynchronize(c->stream));
+            CU(cudaFree(c->d_instr));
+            CU(cudaFree(c->d_cnts));
+            CU(cudaFreeHost(c->h_instr));
+        }
+        CU(cudaMalloc(&c->d_instr, cap * sizeof(FitchInstr)));
+        CU(cudaMalloc(&c->d_cnts, cap * sizeof(int32_t)));
+        CU(cudaMallocHost(&c->h_instr, cap * sizeof(FitchInstr)));
+        c->cap_instr = cap;
+    }
+    if (n_prog > c->cap_prog)
+    {
+        size_t cap = c->cap_prog ? c->cap_prog : 256;
+        while (cap < n_prog)
+            cap *= 2;
+        if (c->d_prog)
+        {
+            CU(cudaStreamSynchronize(c->stream));
+            CU(cudaFree(c->d_prog));
+            CU(cudaFree(c->d_totals));
+            CU(cudaFreeHost(c->h_prog));
+            CU(cudaFreeHost(c->h_totals));
+        }
+        CU(cudaMalloc(&c->d_prog, cap * sizeof(FitchProgram)));
+        CU(cudaMalloc(&c->d_totals, cap * sizeof(unsigned long long)));
+        CU(cudaMallocHost(&c->h_prog, cap * sizeof(FitchProgram)));
+        CU(cudaMallocHost(&c->h_totals, cap * sizeof(long long)));
+        c->cap_prog = cap;
+    }
+    return 0;
+}
+
+static int pick_block(const lvb_gpu_ctx *c)
+{
+    if (c->block_override)
+        return c->block_override;
+    if (c->stride_u4 >= 4096)
+        return 256;
+    if (c->stride_u4 >= 1024)
+        return 128;
+    return 64;
+}
+
+/* fold finished event pairs into the running kernel-time total */
+static int drain_kernel_events(lvb_gpu_ctx *c)
+{
+    for (int i = 0; i < c->ring_used; i++)
+    {
+        float ms = 0;
+        CU(cudaEventSynchronize(c->ring1[i]));
+        CU(cudaEventElapsedTime(&ms, c->ring0[i], c->ring1[i]));
+        c->kernel_ms_total += ms;
+        c->kernel_launches_timed++;
+    }
+    c->ring_used = 0;
+    return 0;
+}
+
+/* launch the batch that is resident in d_instr/d_prog */
+static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
+{
+    const int64_t K = c->last_K;
+    const bool store = c->last_store;
+    CU(cudaMemsetAsync(c->d_totals, 0, K * sizeof(unsigned long long), c->stream));
+    if (store)
+        CU(cudaMemsetAsync(c->d_cnts, 0, c->instr.size() * sizeof(int32_t), c->stream));
+
+    ExecParams p;
+    p.pool = c->pool;
+    p.stride_u4 = c->stride_u4;
+    p.ncols = (int32_t)c->stride_u4;
+    p.n = (int32_t)c->n;
+    p.n_internal = (int32_t)c->I;
+    p.n_prog = (int32_t)K;
+    const int block = pick_block(c);
+    p.n_colblocks = (int32_t)((c->stride_u4 + block - 1) / block);
+    p.n_slots = c->last_slots;
+    p.instr = c->d_instr;
+    p.prog = c->d_prog;
+    p.totals = c->d_totals;
+    p.cnts = c->d_cnts;
+    p.chg = c->chg;
+    p.sum_chg = c->sum_chg;
+    if ((int64_t)p.n_prog * p.n_colblocks > (int64_t)INT32_MAX)
+        return fail("batch too large: %lld CTAs", (long long)p.n_prog * p.n_colblocks);
+
+    if (c->ring_used == lvb_gpu_ctx::kEvRing && drain_kernel_events(c))
+        return 1;
+    const int slot = c->ring_used++;
+    CU(cudaEventRecord(c->ring0[slot], c->stream));
+    CU(launch_fitch_exec(p, store, block, c->stream));
+    CU(cudaEventRecord(c->ring1[slot], c->stream));
+    c->ev0 = c->ring0[slot];
+    c->ev1 = c->ring1[slot];
+    c->timed = true;
+    c->launches++;
+    if (store)
+    {
+        CU(launch_commit_finalize(c->d_instr, c->d_prog, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
+                                  (long long *)c->d_totals, c->stream));
+        c->launches++;
+    }
+    if (c->comm && (lengths || !store))
+    {
+        int r = g_nccl.AllReduce(c->d_totals, c->d_totals, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
+        if (r != 0)
+            return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    }
+    if (lengths)
+    {
+        CU(cudaMemcpyAsync(c->h_totals, c->d_totals, K * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        for (int64_t k = 0; k < K; k++)
+            lengths[k] = (int64_t)c->h_totals[k];
+    }
+    return 0;
+}
+
+/* compile + launch one batch; store: commit semantics, else score semantics */
+static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_topology *topos, bool store,
+                     int64_t *lengths)
+{
+    if (!c->pool)
+        return fail("no alignment on the device: call lvb_gpu_matrix_upload first");
+    if (K <= 0)
+        return 0;
+    CU(cudaSetDevice(c->device));
+    c->last_K = 0;
+    c->instr.clear();
+    c->prog.clear();
+    int n_slots = 0;
+    std::string err;
+    for (int64_t k = 0; k < K; k++)
+    {
+        const int t = trees[k];
+        if (t < 0 || t >= c->max_trees || !c->tree_used[t])
+            return fail("candidate %lld: tree %d does not exist", (long long)k, t);
+        if (!store && !c->tree_ready[t])
+            return fail("candidate %lld: tree %d has never been evaluated (commit it first)", (long long)k, t);
+        if (store && !c->tree_ready[t] && topos[k].n_dirty >= 0)
+            return fail("tree %d: first commit must recompute every internal node (n_dirty < 0)", t);
+        const size_t begin = c->instr.size();
+        int slots = 0;
+        if (!c->sc->compile(topos[k], store, c->instr, slots, err))
+            return fail("candidate %lld: %s", (long long)k, err.c_str());
+        if (slots > n_slots)
+            n_slots = slots;
+        c->prog.push_back(FitchProgram{(int32_t)begin, (int32_t)(c->instr.size() - begin), t, store ? 1 : 0});
+    }
+    if (store)
+    { /* in-place commits of one tree must not share a launch */
+        std::vector<uint8_t> seen(c->max_trees, 0);
+        for (int64_t k = 0; k < K; k++)
+        {
+            if (seen[trees[k]])
+                return fail("commit batch names tree %d twice", trees[k]);
+            seen[trees[k]] = 1;
+        }
+    }
+    if (c->instr.size() > (size_t)INT32_MAX)
+        return fail("batch too large: %zu instructions", c->instr.size());
+    if (ensure_batch_capacity(c, c->instr.size(), c->prog.size()))
+        return 1;
+    /* a previous asynchronous batch may still be reading the pinned staging buffers */
+    CU(cudaStreamSynchronize(c->stream));
+    memcpy(c->h_instr, c->instr.data(), c->instr.size() * sizeof(FitchInstr));
+    memcpy(c->h_prog, c->prog.data(), c->prog.size() * sizeof(FitchProgram));
+    CU(cudaMemcpyAsync(c->d_instr, c->h_instr, c->instr.size() * sizeof(FitchInstr), cudaMemcpyHostToDevice,
+                       c->stream));
+    CU(cudaMemcpyAsync(c->d_prog, c->h_prog, c->prog.size() * sizeof(FitchProgram), cudaMemcpyHostToDevice,
+                       c->stream));
+    if (store)
+        for (int64_t k = 0; k < K; k++)
+            c->tree_ready[trees[k]] = 1;
+    c->last_K = K;
+    c->last_store = store;
+    c->last_slots = n_slots;
+    return launch_resident(c, lengths);
+}
+
+static void free_matrix(lvb_gpu_ctx *c)
+{
+    cudaFree(c->pool);
+    cudaFree(c->chg);
+    cudaFree(c->sum_chg);
+    c->pool = nullptr;
+    c->chg = nullptr;
+    c->sum_chg = nullptr;
+    delete c->sc;
+    c->sc = nullptr;
+}
+
+static int alloc_matrix(lvb_gpu_ctx *c, int64_t n, int64_t nwords, int64_t word_begin, int64_t word_count,
+                        int64_t max_trees)
+{
+    if (n < 5)
+        return fail("alignment needs at least 5 rows (MIN_N, LVB.h:107), got %lld", (long long)n);
+    if (nwords < 1 || word_begin < 0 || word_count < 1 || word_begin + word_count > nwords)
+        return fail("bad word block [%lld,+%lld) of %lld", (long long)word_begin, (long long)word_count,
+                    (long long)nwords);
+    if (max_trees < 1)
+        return fail("max_trees must be >= 1");
+    if (2 * n - 3 > (int64_t)INT32_MAX / 2)
+        return fail("too many rows");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    free_matrix(c);
+    c->last_K = 0;
+    c->n = n;
+    c->nwords = nwords;
+    c->word_begin = word_begin;
+    c->word_count = word_count;
+    c->B = 2 * n - 3;
+    c->I = n - 3;
+    c->max_trees = max_trees;
+    /* two words per 16-byte column; rows padded to 128 bytes so that every warp access is line-aligned */
+    const int64_t cols = (word_count + 1) / 2;
+    c->stride_u4 = (cols + 7) / 8 * 8;
+    const int64_t rows = n + max_trees * c->I;
+    if (rows > (int64_t)INT32_MAX)
+        return fail("row pool too large");
+    CU(cudaMalloc(&c->pool, (size_t)rows * c->stride_u4 * sizeof(uint4)));
+    CU(cudaMalloc(&c->chg, (size_t)max_trees * c->I * sizeof(int32_t)));
+    CU(cudaMalloc(&c->sum_chg, (size_t)max_trees * sizeof(long long)));
+    CU(cudaMemsetAsync(c->pool, 0xFF, (size_t)n * c->stride_u4 * sizeof(uint4), c->stream));
+    CU(cudaMemsetAsync(c->chg, 0, (size_t)max_trees * c->I * sizeof(int32_t), c->stream));
+    CU(cudaMemsetAsync(c->sum_chg, 0, (size_t)max_trees * sizeof(long long), c->stream));
+    c->tree_used.assign(max_trees, 0);
+    c->tree_ready.assign(max_trees, 0);
+    c->sc = new ScheduleCompiler(n);
+    return 0;
+}
+
+/* rows(i) gives a pointer to the nwords words of row i */
+template <class RowFn>
+static int upload_rows(lvb_gpu_ctx *c, RowFn rows)
+{
+    const size_t row_bytes = (size_t)c->word_count * 8;
+    size_t chunk_rows = (64u << 20) / row_bytes;
+    if (chunk_rows < 1)
+        chunk_rows = 1;
+    if (chunk_rows > (size_t)c->n)
+        chunk_rows = (size_t)c->n;
+    unsigned char *stage = nullptr;
+    CU(cudaMallocHost(&stage, chunk_rows * row_bytes));
+    for (int64_t r0 = 0; r0 < c->n; r0 += (int64_t)chunk_rows)
+    {
+        const int64_t nr = std::min<int64_t>((int64_t)chunk_rows, c->n - r0);
+        for (int64_t r = 0; r < nr; r++)
+            memcpy(stage + r * row_bytes, rows(r0 + r) + c->word_begin, row_bytes);
+        cudaError_t e = cudaMemcpy2DAsync(c->pool + r0 * c->stride_u4, (size_t)c->stride_u4 * sizeof(uint4), stage,
+                                          row_bytes, row_bytes, (size_t)nr, cudaMemcpyHostToDevice, c->stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess)
+        {
+            cudaFreeHost(stage);
+            return fail("leaf row upload failed: %s", cudaGetErrorString(e));
+        }
+    }
+    cudaFreeHost(stage);
+    return 0;
+}
+
+extern "C"
+{
+
+    const char *lvb_gpu_last_error(void) { return g_err.c_str(); }
+
+    int lvb_gpu_device_count(int *count)
+    {
+        CU(cudaGetDeviceCount(count));
+        return 0;
+    }
+
+    int lvb_gpu_init(int device, lvb_gpu_ctx **out)
+    {
+        if (!out)
+            return fail("lvb_gpu_init: null out pointer");
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0)
+            return fail("no CUDA device: %s (this library has no CPU path)", cudaGetErrorString(e));
+        if (device < 0 || device >= count)
+            return fail("device %d out of range (have %d)", device, count);
+        CU(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, device));
+        if (prop.major != 10)
+            return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major,
+                        prop.minor);
+        lvb_gpu_ctx *c = new lvb_gpu_ctx();
+        c->device = device;
+        CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        for (int i = 0; i < lvb_gpu_ctx::kEvRing; i++)
+        {
+            CU(cudaEventCreate(&c->ring0[i]));
+            CU(cudaEventCreate(&c->ring1[i]));
+        }
+        const char *b = getenv("LVB_GPU_BLOCK");
+        if (b)
+        {
+            const int v = atoi(b);
+            if (v >= 32 && v <= 256 && v % 32 == 0)
+                c->block_override = v;
+        }
+        *out = c;
+        return 0;
+    }
+
+    int lvb_gpu_shutdown(lvb_gpu_ctx *c)
+    {
+        if (!c)
+            return 0;
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->stream);
+        if (c->comm && g_nccl.CommDestroy)
+            g_nccl.CommDestroy(c->comm);
+        free_matrix(c);
+        cudaFree(c->d_instr);
+        cudaFree(c->d_cnts);
+        cudaFree(c->d_prog);
+        cudaFree(c->d_totals);
+        cudaFreeHost(c->h_instr);
+        cudaFreeHost(c->h_prog);
+        cudaFreeHost(c->h_totals);
+        for (int i = 0; i < lvb_gpu_ctx::kEvRing; i++)
+        {
+            cudaEventDestroy(c->ring0[i]);
+            cudaEventDestroy(c->ring1[i]);
+        }
+        cudaStreamDestroy(c->stream);
+        delete c;
+        return 0;
+    }
+
+    void *lvb_gpu_stream(lvb_gpu_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+    int lvb_gpu_matrix_upload(lvb_gpu_ctx *c, int64_t n, int64_t nwords, const uint64_t *const *enc_rows,
+                              int64_t word_begin, int64_t word_count, int64_t max_trees)
+    {
+        if (!c || !enc_rows)
+            return fail("lvb_gpu_matrix_upload: null argument");
+        if (alloc_matrix(c, n, nwords, word_begin, word_count, max_trees))
+            return 1;
+        return upload_rows(c, [&](int64_t i) { return enc_rows[i]; });
+    }
+
+    int lvb_gpu_matrix_upload_flat(lvb_gpu_ctx *c, int64_t n, int64_t nwords, const uint64_t *enc, int64_t word_begin,
+                                   int64_t word_count, int64_t max_trees)
+    {
+        if (!c || !enc)
+            return fail("lvb_gpu_matrix_upload_flat: null argument");
+        if (alloc_matrix(c, n, nwords, word_begin, word_count, max_trees))
+            return 1;
+        return upload_rows(c, [&](int64_t i) { return enc + i * nwords; });
+    }
+
+    int lvb_gpu_matrix_pack(lvb_gpu_ctx *c, int64_t n, int64_t m, const char *const *rows, int64_t word_begin,
+                            int64_t word_count, int64_t max_trees)
+    {
+        if (!c || !rows)
+            return fail("lvb_gpu_matrix_pack: null argument");
+        if (m < 1)
+            return fail("alignment needs at least 1 column (MIN_M, LVB.h:103)");
+        const int64_t nwords = (m + 15) / 16;
+        if (alloc_matrix(c, n, nwords, word_begin, word_count, max_trees))
+            return 1;
+        /* only the characters of this context's word block travel */
+        const int64_t site0 = word_begin * 16;
+        const int64_t site1 = std::min<int64_t>(m, (word_begin + word_count) * 16);
+        const int64_t mloc = site1 - site0;
+        unsigned char *d_text = nullptr, *h_text = nullptr;
+        int *d_bad = nullptr;
+        CU(cudaMalloc(&d_text, (size_t)n * mloc));
+        CU(cudaMalloc(&d_bad, sizeof(int)));
+        CU(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
+        const size_t chunk_rows = std::max<size_t>(1, std::min<size_t>((size_t)n, (64u << 20) / (size_t)mloc));
+        CU(cudaMallocHost(&h_text, chunk_rows * mloc));
+        int rc = 0;
+        for (int64_t r0 = 0; r0 < n && !rc; r0 += (int64_t)chunk_rows)
+        {
+            const int64_t nr = std::min<int64_t>((int64_t)chunk_rows, n - r0);
+            for (int64_t r = 0; r < nr; r++)
+                memcpy(h_text + r * mloc, rows[r0 + r] + site0, (size_t)mloc);
+            cudaError_t e = cudaMemcpyAsync(d_text + r0 * mloc, h_text, (size_t)nr * mloc, cudaMemcpyHostToDevice,
+                                            c->stream);
+            if (e == cudaSuccess)
+                e = cudaStreamSynchronize(c->stream);
+            if (e != cudaSuccess)
+                rc = fail("text upload failed: %s", cudaGetErrorString(e));
+        }
+        int bad = 0;
+        if (!rc)
+        {
+            /* the kernel sees a local alignment of mloc columns starting at word 0 */
+            cudaError_t e = launch_pack_dna(d_text, n, mloc, 0, word_count, c->pool, c->stride_u4, d_bad, c->stream);
+            c->launches++;
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+            if (e == cudaSuccess)
+                e = cudaStreamSynchronize(c->stream);
+            if (e != cudaSuccess)
+                rc = fail("pack kernel failed: %s", cudaGetErrorString(e));
+        }
+        cudaFree(d_text);
+        cudaFree(d_bad);
+        cudaFreeHost(h_text);
+        if (!rc && bad)
+            rc = fail("bad base symbol in data MSA: %c (cannot read data MSA)", (char)(bad - 1));
+        return rc;
+    }
+
+    int lvb_gpu_tree_create(lvb_gpu_ctx *c, int *tree)
+    {
+        if (!c || !tree)
+            return fail("lvb_gpu_tree_create: null argument");
+        if (!c->pool)
+            return fail("no alignment on the device: call lvb_gpu_matrix_upload first");
+        for (int64_t t = 0; t < c->max_trees; t++)
+        {
+            if (!c->tree_used[t])
+            {
+                c->tree_used[t] = 1;
+                c->tree_ready[t] = 0;
+                CU(cudaSetDevice(c->device));
+                CU(cudaMemsetAsync(c->chg + t * c->I, 0, (size_t)c->I * sizeof(int32_t), c->stream));
+                CU(cudaMemsetAsync(c->sum_chg + t, 0, sizeof(long long), c->stream));
+                *tree = (int)t;
+                return 0;
+            }
+        }
+        return fail("all %lld device trees are in use (max_trees of lvb_gpu_matrix_upload)", (long long)c->max_trees);
+    }
+
+    int lvb_gpu_tree_destroy(lvb_gpu_ctx *c, int tree)
+    {
+        if (!c || tree < 0 || tree >= c->max_trees || !c->tree_used[tree])
+            return fail("lvb_gpu_tree_destroy: tree %d does not exist", tree);
+        c->tree_used[tree] = 0;
+        c->tree_ready[tree] = 0;
+        return 0;
+    }
+
+    int lvb_gpu_tree_copy(lvb_gpu_ctx *c, int dst, int src)
+    {
+        if (!c || dst < 0 || src < 0 || dst >= c->max_trees || src >= c->max_trees || !c->tree_used[dst] ||
+            !c->tree_used[src])
+            return fail("lvb_gpu_tree_copy: bad tree %d <- %d", dst, src);
+        if (dst == src)
+            return 0;
+        CU(cudaSetDevice(c->device));
+        const size_t bytes = (size_t)c->I * c->stride_u4 * sizeof(uint4);
+        CU(cudaMemcpyAsync(c->pool + (c->n + dst * c->I) * c->stride_u4, c->pool + (c->n + src * c->I) * c->stride_u4,
+                           bytes, cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->chg + dst * c->I, c->chg + src * c->I, (size_t)c->I * sizeof(int32_t),
+                           cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->sum_chg + dst, c->sum_chg + src, sizeof(long long), cudaMemcpyDeviceToDevice,
+                           c->stream));
+        c->tree_ready[dst] = c->tree_ready[src];
+        return 0;
+    }
+
+    int lvb_gpu_tree_commit(lvb_gpu_ctx *c, int tree, const lvb_gpu_topology *topo, int64_t *length)
+    {
+        if (!c || !topo)
+            return fail("lvb_gpu_tree_commit: null argument");
+        return run_batch(c, 1, &tree, topo, true, length);
+    }
+
+    int lvb_gpu_commit_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                             int64_t *lengths)
+    {
+        if (!c || !trees || !topos)
+            return fail("lvb_gpu_commit_batch: null argument");
+        return run_batch(c, n_cand, trees, topos, true, lengths);
+    }
+
+    int lvb_gpu_score_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                            int64_t *lengths)
+    {
+        if (!c || !trees || !topos || !lengths)
+            return fail("lvb_gpu_score_batch: null argument");
+        return run_batch(c, n_cand, trees, topos, false, lengths);
+    }
+
+    int lvb_gpu_download_row(lvb_gpu_ctx *c, int tree, int64_t node, uint64_t *out)
+    {
+        if (!c || !out || !c->pool)
+            return fail("lvb_gpu_download_row: null argument or no alignment");
+        if (node < 0 || node >= c->B)
+            return fail("lvb_gpu_download_row: node %lld out of range", (long long)node);
+        int64_t row = node;
+        if (node >= c->n)
+        {
+            if (tree < 0 || tree >= c->max_trees || !c->tree_used[tree])
+                return fail("lvb_gpu_download_row: tree %d does not exist", tree);
+            row = node + (int64_t)tree * c->I;
+        }
+        CU(cudaSetDevice(c->device));
+        CU(cudaMemcpyAsync(out, c->pool + row * c->stride_u4, (size_t)c->word_count * 8, cudaMemcpyDeviceToHost,
+                           c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+
+    int lvb_gpu_tree_changes(lvb_gpu_ctx *c, int tree, int64_t *changes)
+    {
+        if (!c || !changes || tree < 0 || tree >= c->max_trees || !c->tree_used[tree])
+            return fail("lvb_gpu_tree_changes: bad argument");
+        CU(cudaSetDevice(c->device));
+        std::vector<int32_t> h((size_t)c->I);
+        const int32_t *src = c->chg + (int64_t)tree * c->I;
+        int32_t *tmp = nullptr;
+        if (c->comm)
+        {
+            CU(cudaMalloc(&tmp, (size_t)c->I * sizeof(int32_t)));
+            int r = g_nccl.AllReduce(src, tmp, (size_t)c->I, kNcclInt32, kNcclSum, c->comm, c->stream);
+            if (r != 0)
+            {
+                cudaFree(tmp);
+                return fail("ncclAllReduce failed");
+            }
+            src = tmp;
+        }
+        CU(cudaMemcpyAsync(h.data(), src, (size_t)c->I * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if (tmp)
+            cudaFree(tmp);
+        for (int64_t i = 0; i < c->n; i++)
+            changes[i] = 0;
+        for (int64_t i = 0; i < c->I; i++)
+            changes[c->n + i] = h[i];
+        return 0;
+    }
+
+    int lvb_gpu_comm_unique_id(void *id128)
+    {
+        if (!id128)
+            return fail("lvb_gpu_comm_unique_id: null argument");
+        if (nccl_load())
+            return 1;
+        int r = g_nccl.GetUniqueId(id128);
+        if (r != 0)
+            return fail("ncclGetUniqueId failed: %d", r);
+        return 0;
+    }
+
+    int lvb_gpu_comm_init(lvb_gpu_ctx *c, int nranks, int rank, const void *id128)
+    {
+        if (!c || !id128)
+            return fail("lvb_gpu_comm_init: null argument");
+        if (nccl_load())
+            return 1;
+        CU(cudaSetDevice(c->device));
+        NcclId id;
+        memcpy(&id, id128, sizeof id);
+        int r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+        if (r != 0)
+        {
+            c->comm = nullptr;
+            return fail("ncclCommInitRank failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+        }
+        c->nranks = nranks;
+        c->rank = rank;
+        return 0;
+    }
+
+    int64_t lvb_gpu_launch_count(lvb_gpu_ctx *c) { return c ? c->launches : 0; }
+
+    int lvb_gpu_last_kernel_ms(lvb_gpu_ctx *c, float *ms)
+    {
+        if (!c || !ms)
+            return fail("lvb_gpu_last_kernel_ms: null argument");
+        if (!c->timed)
+            return fail("no Fitch kernel has been launched yet");
+        CU(cudaEventSynchronize(c->ev1));
+        CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+        return 0;
+    }
+
+    int lvb_gpu_rerun_last_batch(lvb_gpu_ctx *c, int64_t *lengths)
+    {
+        if (!c)
+            return fail("lvb_gpu_rerun_last_batch: null argument");
+        if (c->last_K <= 0)
+            return fail("no batch is resident on the device");
+        CU(cudaSetDevice(c->device));
+        return launch_resident(c, lengths);
+    }
+
+    int lvb_gpu_kernel_time(lvb_gpu_ctx *c, double *total_ms, int64_t *launches, int reset)
+    {
+        if (!c || !total_ms || !launches)
+            return fail("lvb_gpu_kernel_time: null argument");
+        CU(cudaSetDevice(c->device));
+        if (drain_kernel_events(c))
+            return 1;
+        *total_ms = c->kernel_ms_total;
+        *launches = c->kernel_launches_timed;
+        if (reset)
+        {
+            c->kernel_ms_total = 0;
+            c->kernel_launches_timed = 0;
+        }
+        return 0;
+    }
+
+    int lvb_gpu_synchronize(lvb_gpu_ctx *c)
+    {
+        if (!c)
+            return fail("lvb_gpu_synchronize: null argument");
+        CU(cudaSetDevice(c->device));
+        CU(cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+
+    int lvb_gpu_compile_schedule(int64_t n, const lvb_gpu_topology *topo, int store, int32_t *instr, int64_t cap,
+                                 int64_t *n_instr, int64_t *n_slots)
+    {
+        if (!topo || !n_instr || !n_slots)
+            return fail("lvb_gpu_compile_schedule: null argument");
+        if (n < 3)
+            return fail("lvb_gpu_compile_schedule: n too small");
+        ScheduleCompiler sc(n);
+        std::vector<FitchInstr> out;
+        int slots = 0;
+        std::string err;
+        if (!sc.compile(*topo, store != 0, out, slots, err))
+            return fail("%s", err.c_str());
+        *n_instr = (int64_t)out.size();
+        *n_slots = slots;
+        if (instr)
+        {
+            if ((int64_t)out.size() > cap)
+                return fail("instruction buffer too small: need %zu", out.size());
+            memcpy(instr, out.data(), out.size() * sizeof(FitchInstr));
+        }
+        return 0;
+    }
+
+} /* extern "C" */

@@ -1,0 +1,259 @@
+"""ctypes binding of include/lvb_gpu.h (lvb_b200/lib/liblvbgpu.so).
+
+Plumbing only: every call goes straight to the C-ABI; there is no arithmetic and no CPU
+fallback here.  If the library is missing, import fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Iterable, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "liblvbgpu.so")
+
+
+class GpuError(RuntimeError):
+    """A non-zero status from the C-ABI (LVB host code would crash() on it, src/Error.c:49)."""
+
+
+class _Topo(C.Structure):
+    _fields_ = [
+        ("left", C.c_void_p),
+        ("right", C.c_void_p),
+        ("stride_bytes", C.c_int64),
+        ("root", C.c_int64),
+        ("dirty", C.c_void_p),
+        ("n_dirty", C.c_int64),
+    ]
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load liblvbgpu.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C lvb_b200/csrc`. lvb_b200 has no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    vp, i64, i32p = C.c_void_p, C.c_int64, C.POINTER(C.c_int)
+    lib.lvb_gpu_last_error.restype = C.c_char_p
+    lib.lvb_gpu_device_count.argtypes = [i32p]
+    lib.lvb_gpu_init.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.lvb_gpu_shutdown.argtypes = [vp]
+    lib.lvb_gpu_stream.restype = vp
+    lib.lvb_gpu_stream.argtypes = [vp]
+    lib.lvb_gpu_matrix_upload.argtypes = [vp, i64, i64, C.POINTER(vp), i64, i64, i64]
+    lib.lvb_gpu_matrix_upload_flat.argtypes = [vp, i64, i64, vp, i64, i64, i64]
+    lib.lvb_gpu_matrix_pack.argtypes = [vp, i64, i64, C.POINTER(C.c_char_p), i64, i64, i64]
+    lib.lvb_gpu_tree_create.argtypes = [vp, i32p]
+    lib.lvb_gpu_tree_destroy.argtypes = [vp, C.c_int]
+    lib.lvb_gpu_tree_copy.argtypes = [vp, C.c_int, C.c_int]
+    lib.lvb_gpu_tree_commit.argtypes = [vp, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
+    lib.lvb_gpu_commit_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
+    lib.lvb_gpu_score_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
+    lib.lvb_gpu_download_row.argtypes = [vp, C.c_int, i64, vp]
+    lib.lvb_gpu_tree_changes.argtypes = [vp, C.c_int, vp]
+    lib.lvb_gpu_comm_unique_id.argtypes = [vp]
+    lib.lvb_gpu_comm_init.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.lvb_gpu_launch_count.restype = i64
+    lib.lvb_gpu_launch_count.argtypes = [vp]
+    lib.lvb_gpu_last_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    lib.lvb_gpu_kernel_time.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.c_int]
+    lib.lvb_gpu_rerun_last_batch.argtypes = [vp, C.POINTER(i64)]
+    lib.lvb_gpu_synchronize.argtypes = [vp]
+    lib.lvb_gpu_compile_schedule.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64)]
+    _lib = lib
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise GpuError(load_library().lvb_gpu_last_error().decode(errors="replace"))
+
+
+class Topology:
+    """A (candidate) tree as getplen sees it: child links, root, dirty internal nodes.
+
+    ``left``/``right`` are int64 arrays over all 2n-3 nodes (leaves hold -1, LVB's UNSET);
+    ``dirty`` is None for "every internal node".  Arrays are kept alive by this object.
+    """
+
+    def __init__(self, left, right, root: int, dirty: Optional[Iterable[int]] = None):
+        self.left = np.ascontiguousarray(left, dtype=np.int64)
+        self.right = np.ascontiguousarray(right, dtype=np.int64)
+        self.root = int(root)
+        self.dirty = None if dirty is None else np.ascontiguousarray(list(dirty) if not isinstance(dirty, np.ndarray) else dirty, dtype=np.int64)
+
+    def fill(self, t: _Topo) -> None:
+        t.left = self.left.ctypes.data
+        t.right = self.right.ctypes.data
+        t.stride_bytes = 8
+        t.root = self.root
+        if self.dirty is None:
+            t.dirty = None
+            t.n_dirty = -1
+        else:
+            t.dirty = self.dirty.ctypes.data if self.dirty.size else None
+            t.n_dirty = int(self.dirty.size)
+
+    def as_struct(self) -> _Topo:
+        t = _Topo()
+        self.fill(t)
+        return t
+
+
+def compile_schedule(n: int, topo: Topology, store: bool = False):
+    """Host-only: the instruction stream for `topo` as an (k, 4) int32 array and its slot count."""
+    lib = load_library()
+    ts = topo.as_struct()
+    k, slots = C.c_int64(0), C.c_int64(0)
+    _check(lib.lvb_gpu_compile_schedule(n, C.byref(ts), int(store), None, 0, C.byref(k), C.byref(slots)))
+    out = np.zeros((k.value, 4), dtype=np.int32)
+    _check(lib.lvb_gpu_compile_schedule(n, C.byref(ts), int(store), out.ctypes.data, k.value, C.byref(k), C.byref(slots)))
+    return out, int(slots.value)
+
+
+class Engine:
+    """One context = one GPU, one stream (lvb_gpu_init .. lvb_gpu_shutdown)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.ctx = C.c_void_p()
+        _check(self.lib.lvb_gpu_init(device, C.byref(self.ctx)))
+        self.n = self.nwords = self.word_count = 0
+
+    def close(self) -> None:
+        if self.ctx:
+            self.lib.lvb_gpu_shutdown(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- alignment ----
+    def upload(self, enc: np.ndarray, word_begin: int = 0, word_count: Optional[int] = None, max_trees: int = 1) -> None:
+        enc = np.ascontiguousarray(enc, dtype=np.uint64)
+        n, nwords = enc.shape
+        wc = nwords - word_begin if word_count is None else word_count
+        _check(self.lib.lvb_gpu_matrix_upload_flat(self.ctx, n, nwords, enc.ctypes.data, word_begin, wc, max_trees))
+        self.n, self.nwords, self.word_count = n, nwords, wc
+
+    def upload_rows(self, rows: Sequence[np.ndarray], word_begin: int = 0, word_count: Optional[int] = None, max_trees: int = 1) -> None:
+        """Non-contiguous rows, the layout GetSoln builds (Solve.c:516-519)."""
+        rows = [np.ascontiguousarray(r, dtype=np.uint64) for r in rows]
+        n, nwords = len(rows), rows[0].size
+        ptrs = (C.c_void_p * n)(*[r.ctypes.data for r in rows])
+        wc = nwords - word_begin if word_count is None else word_count
+        _check(self.lib.lvb_gpu_matrix_upload(self.ctx, n, nwords, ptrs, word_begin, wc, max_trees))
+        self.n, self.nwords, self.word_count = n, nwords, wc
+
+    def pack(self, rows: Sequence[bytes], word_begin: int = 0, word_count: Optional[int] = None, max_trees: int = 1) -> None:
+        n, m = len(rows), len(rows[0])
+        nwords = (m + 15) // 16
+        arr = (C.c_char_p * n)(*rows)
+        wc = nwords - word_begin if word_count is None else word_count
+        _check(self.lib.lvb_gpu_matrix_pack(self.ctx, n, m, arr, word_begin, wc, max_trees))
+        self.n, self.nwords, self.word_count = n, nwords, wc
+
+    # ---- trees ----
+    def tree_create(self) -> int:
+        t = C.c_int(-1)
+        _check(self.lib.lvb_gpu_tree_create(self.ctx, C.byref(t)))
+        return t.value
+
+    def tree_destroy(self, tree: int) -> None:
+        _check(self.lib.lvb_gpu_tree_destroy(self.ctx, tree))
+
+    def tree_copy(self, dst: int, src: int) -> None:
+        _check(self.lib.lvb_gpu_tree_copy(self.ctx, dst, src))
+
+    def commit(self, tree: int, topo: Topology, wait: bool = True) -> Optional[int]:
+        ts = topo.as_struct()
+        if not wait:
+            _check(self.lib.lvb_gpu_tree_commit(self.ctx, tree, C.byref(ts), None))
+            return None
+        length = C.c_int64(0)
+        _check(self.lib.lvb_gpu_tree_commit(self.ctx, tree, C.byref(ts), C.byref(length)))
+        return int(length.value)
+
+    def _batch(self, fn, trees: Sequence[int], topos: Sequence[Topology]) -> np.ndarray:
+        k = len(topos)
+        tarr = (C.c_int * k)(*[int(t) for t in trees])
+        sarr = (_Topo * k)()
+        for i, tp in enumerate(topos):
+            tp.fill(sarr[i])
+        out = np.zeros(k, dtype=np.int64)
+        _check(fn(self.ctx, k, tarr, sarr, out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return out
+
+    def commit_batch(self, trees: Sequence[int], topos: Sequence[Topology]) -> np.ndarray:
+        return self._batch(self.lib.lvb_gpu_commit_batch, trees, topos)
+
+    def score_batch(self, trees: Sequence[int], topos: Sequence[Topology]) -> np.ndarray:
+        return self._batch(self.lib.lvb_gpu_score_batch, trees, topos)
+
+    # ---- parity helpers ----
+    def download_row(self, tree: int, node: int) -> np.ndarray:
+        out = np.zeros(self.word_count, dtype=np.uint64)
+        _check(self.lib.lvb_gpu_download_row(self.ctx, tree, node, out.ctypes.data))
+        return out
+
+    def changes(self, tree: int) -> np.ndarray:
+        out = np.zeros(2 * self.n - 3, dtype=np.int64)
+        _check(self.lib.lvb_gpu_tree_changes(self.ctx, tree, out.ctypes.data))
+        return out
+
+    # ---- multi-GPU ----
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        _check(load_library().lvb_gpu_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, nranks: int, rank: int, uid: bytes) -> None:
+        buf = C.create_string_buffer(uid, 128)
+        _check(self.lib.lvb_gpu_comm_init(self.ctx, nranks, rank, buf))
+
+    # ---- introspection ----
+    @property
+    def launches(self) -> int:
+        return int(self.lib.lvb_gpu_launch_count(self.ctx))
+
+    def last_kernel_ms(self) -> float:
+        ms = C.c_float(0)
+        _check(self.lib.lvb_gpu_last_kernel_ms(self.ctx, C.byref(ms)))
+        return float(ms.value)
+
+    def kernel_time(self, reset: bool = False):
+        """(total ms, launches) of the Fitch kernel since the last reset (CUDA events on the stream)"""
+        ms, k = C.c_double(0), C.c_int64(0)
+        _check(self.lib.lvb_gpu_kernel_time(self.ctx, C.byref(ms), C.byref(k), int(reset)))
+        return float(ms.value), int(k.value)
+
+    def rerun_last_batch(self, count: int = 0) -> Optional[np.ndarray]:
+        """launch the device-resident batch again; count > 0 -> wait and return its lengths"""
+        if count <= 0:
+            _check(self.lib.lvb_gpu_rerun_last_batch(self.ctx, None))
+            return None
+        out = np.zeros(count, dtype=np.int64)
+        _check(self.lib.lvb_gpu_rerun_last_batch(self.ctx, out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return out
+
+    def synchronize(self) -> None:
+        _check(self.lib.lvb_gpu_synchronize(self.ctx))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.lvb_gpu_stream(self.ctx) or 0)

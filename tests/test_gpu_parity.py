@@ -1,0 +1,320 @@
+"""GPU (-m gpu): the CUDA path, called through the C-ABI (include/lvb_gpu.h), against the
+oracle and the reference's golden vectors.  Integer work: every comparison is bit-exact."""
+import os
+
+import numpy as np
+import pytest
+
+import oracles
+from lvb_b200 import Engine, GpuError, Topology, synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def all_rows(eng, tree, n):
+    return np.stack([eng.download_row(tree, v) for v in range(2 * n - 3)])
+
+
+def closure_dirty(left, right, root, cur_l, cur_r, n):
+    """internal nodes whose children differ from the device's current tree, closed towards the root"""
+    B = 2 * n - 3
+    changed = np.nonzero((left != cur_l) | (right != cur_r))[0]
+    parent = np.full(B, -1, dtype=np.int64)
+    for v in range(n, B):
+        parent[left[v]] = v
+        parent[right[v]] = v
+    dirty = set()
+    for v in changed[changed >= n].tolist():
+        while v >= n and v not in dirty:
+            dirty.add(v)
+            v = int(parent[v])
+    return np.array(sorted(dirty), dtype=np.int64)
+
+
+def test_known_answer_chain(engine, golden_dir):
+    """11808 -> nni 11834 -> spr 11835 -> tbr 11827 -> reroot 11827, with
+    every state row and every per-node change count equal to the reference's"""
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n = enc.shape[0]
+    engine.upload(enc, max_trees=2)
+    t = engine.tree_create()
+    assert engine.commit(t, Topology(g["random_left"], g["random_right"], 0)) == 11808
+    assert np.array_equal(all_rows(engine, t, n), g["random_rows_after"])
+    assert np.array_equal(engine.changes(t)[n:], g["random_changes_after"][n:])
+    cur_l, cur_r = g["random_left"], g["random_right"]
+    for step, want in [("nni", 11834), ("spr", 11835), ("tbr", 11827), ("reroot", 11827)]:
+        left, right, root = g[f"{step}_left"], g[f"{step}_right"], int(g[f"{step}_root"])
+        dirty = np.nonzero(g[f"{step}_dirty"])[0] if step != "reroot" else closure_dirty(left, right, root, cur_l, cur_r, n)
+        topo = Topology(left, right, root, dirty)
+        assert engine.score_batch([t], [topo]).tolist() == [want]
+        assert np.array_equal(engine.changes(t)[n:], g[f"{'random' if step == 'nni' else prev}_changes_after"][n:])
+        assert engine.commit(t, topo) == want
+        assert np.array_equal(all_rows(engine, t, n), g[f"{step}_rows_after"]), step
+        assert np.array_equal(engine.changes(t)[n:], g[f"{step}_changes_after"][n:]), step
+        cur_l, cur_r, prev = left, right, step
+    # full re-evaluation of the final tree gives the same state
+    assert engine.commit(t, Topology(left, right, root)) == 11827
+    assert np.array_equal(all_rows(engine, t, n), g["reroot_rows_after"])
+    engine.tree_destroy(t)
+
+
+def test_proposal_series(engine, golden_dir):
+    """300 reference proposals: score against the device tree, commit the accepted ones"""
+    g = load(golden_dir, "proposals.npz")
+    enc = load(golden_dir, "example.npz")["enc"]
+    n = enc.shape[0]
+    engine.upload(enc, max_trees=1)
+    t = engine.tree_create()
+    cur_l, cur_r = g["start_left"].astype(np.int64), g["start_right"].astype(np.int64)
+    engine.commit(t, Topology(cur_l, cur_r, int(g["start_root"])))
+    pending, want = [], []
+    for i in range(len(g["length"])):
+        left, right, root = g["left"][i].astype(np.int64), g["right"][i].astype(np.int64), int(g["root"][i])
+        ref_dirty = np.nonzero(g["dirty"][i])[0]
+        dirty = ref_dirty if len(ref_dirty) < n - 3 else closure_dirty(left, right, root, cur_l, cur_r, n)
+        topo = Topology(left, right, root, dirty)
+        pending.append(topo)
+        want.append(int(g["length"][i]))
+        if g["accepted"][i] or i == len(g["length"]) - 1:
+            # everything proposed since the last accept was derived from the same current tree:
+            # one launch scores the whole run
+            got = engine.score_batch([t] * len(pending), pending)
+            assert got.tolist() == want, i
+            pending, want = [], []
+            if g["accepted"][i]:
+                assert engine.commit(t, topo) == int(g["length"][i])
+                cur_l, cur_r = left, right
+    engine.tree_destroy(t)
+
+
+@pytest.mark.parametrize("key", ["tl1", "tl2", "tl3", "tl4", "tl5_thread_2", "tl6_thread_2", "tl6_thread_3", "tl7_thread_2"])
+def test_reference_test_inputs(engine, golden_dir, key):
+    """alignments of the reference's test_treelength_* (ambiguity codes, gaps, 1-word rows)"""
+    g = load(golden_dir, "treelength.npz")
+    enc = g[f"{key}_enc"]
+    n = enc.shape[0]
+    engine.upload(enc, max_trees=1)
+    t = engine.tree_create()
+    lens = g[f"{key}_length"]
+    for i in range(len(lens)):
+        left, right = g[f"{key}_left"][i].astype(np.int64), g[f"{key}_right"][i].astype(np.int64)
+        assert engine.commit(t, Topology(left, right, int(g[f"{key}_root"][i]))) == int(lens[i]), (key, i)
+    engine.tree_destroy(t)
+
+
+def test_upload_paths_and_device_pack(engine, golden_dir):
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n = enc.shape[0]
+    rows = [bytes(r) for r in g["text"]]
+    topo = Topology(g["random_left"], g["random_right"], 0)
+    engine.upload_rows([enc[i].copy() for i in range(n)], max_trees=1)  # Solve.c:516-519 layout
+    t = engine.tree_create()
+    assert engine.commit(t, topo) == 11808
+    engine.pack(rows, max_trees=1)  # DNAToBinary on the device
+    t = engine.tree_create()
+    for v in range(n):
+        assert np.array_equal(engine.download_row(t, v), enc[v])
+    assert engine.commit(t, topo) == 11808
+    with pytest.raises(GpuError, match="bad base symbol"):
+        engine.pack([b"ACGTO"] + [b"ACGTA"] * 4)
+
+
+def test_pack_all_symbols(engine):
+    rng = np.random.default_rng(11)
+    sym = np.frombuffer(b"ACGTUYRWSKMBDHVNX?-", dtype=np.uint8)
+    for n, m in [(5, 1), (6, 15), (7, 16), (8, 17), (9, 1000)]:
+        mat = sym[rng.integers(0, len(sym), size=(n, m))]
+        rows = [bytes(r) for r in mat]
+        engine.pack(rows, max_trees=1)
+        t = engine.tree_create()
+        want = oracles.oracle_pack(rows)
+        for v in range(n):
+            assert np.array_equal(engine.download_row(t, v), want[v])
+
+
+def test_site_blocks_sum_to_whole(golden_dir):
+    """site-block sharding (TreeEvaluation.c:95-97 decomposition): partial lengths of disjoint
+    word blocks add up to the whole, for full passes and for scored candidates"""
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n, nwords = enc.shape
+    topo = Topology(g["random_left"], g["random_right"], 0)
+    cand = Topology(g["nni_left"], g["nni_right"], 0, np.nonzero(g["nni_dirty"])[0])
+    for blocks in (2, 3, 8):
+        bounds = [nwords * b // blocks for b in range(blocks + 1)]
+        full, scored = 0, 0
+        for b in range(blocks):
+            e = Engine(0)
+            e.upload(enc, word_begin=bounds[b], word_count=bounds[b + 1] - bounds[b], max_trees=1)
+            t = e.tree_create()
+            full += e.commit(t, topo)
+            scored += int(e.score_batch([t], [cand])[0])
+            assert np.array_equal(e.download_row(t, n + 3), g["random_rows_after"][n + 3, bounds[b]:bounds[b + 1]])
+            e.close()
+        assert (full, scored) == (11808, 11834)
+
+
+def test_replicate_batches(engine):
+    """several independent trees in one launch (SA replicates): commit_batch + score_batch"""
+    n, m, R = 40, 3000, 6
+    st = synthetic.states(n, m, seed=5, p=0.08)
+    enc = synthetic.pack_states(st)
+    engine.upload(enc, max_trees=R)
+    trees = [engine.tree_create() for _ in range(R)]
+    topos = [Topology(*synthetic.random_topology(n, seed=100 + r)) for r in range(R)]
+    got = engine.commit_batch(trees, topos)
+    want = [oracles.oracle_getplen(enc, tp.left, tp.right, tp.root) for tp in topos]
+    assert got.tolist() == [w[0] for w in want]
+    for r in range(R):
+        assert np.array_equal(engine.changes(trees[r])[n:], want[r][2][n:])
+    # device-to-device copy keeps rows and counts
+    engine.tree_copy(trees[0], trees[3])
+    assert np.array_equal(engine.changes(trees[0]), engine.changes(trees[3]))
+    assert np.array_equal(engine.download_row(trees[0], n + 5), want[3][1][n + 5])
+    with pytest.raises(GpuError, match="twice"):
+        engine.commit_batch([trees[1], trees[1]], topos[:2])
+    for t in trees:
+        engine.tree_destroy(t)
+
+
+def nni_neighbourhood(left, right, root, n):
+    """every NNI candidate of a tree (mutate_deterministic, TreeOperations.c:105-158) with its
+    dirty path; a plain-python restatement used only to make test inputs"""
+    B = 2 * n - 3
+    parent = np.full(B, -1, dtype=np.int64)
+    for v in list(range(n, B)) + [root]:
+        parent[left[v]] = v
+        parent[right[v]] = v
+    out = []
+    for u in range(n, B):
+        v = int(parent[u])
+        a, b = int(left[u]), int(right[u])
+        c = int(right[v]) if left[v] == u else int(left[v])
+        for swap_a in (False, True):
+            l2, r2 = left.copy(), right.copy()
+            moved = a if swap_a else b
+            if l2[v] == u:
+                r2[v] = moved
+            else:
+                l2[v] = moved
+            l2[u], r2[u] = (b, c) if swap_a else (a, c)
+            dirty, w = [], u
+            while w != root:
+                dirty.append(w)
+                w = int(parent[w])
+            out.append(Topology(l2, r2, root, dirty))
+    return out
+
+
+@pytest.mark.parametrize("n,m", [(30, 500), (150, 20000)])
+def test_nni_neighbourhood_batch(engine, n, m):
+    """2(n-3) candidates of one tree in a single launch (deterministic_hillclimb's loop,
+    Solve.c:64-142) against full oracle passes"""
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=9, p=0.05))
+    left, right, root = synthetic.random_topology(n, seed=4)
+    engine.upload(enc, max_trees=1)
+    t = engine.tree_create()
+    assert engine.commit(t, Topology(left, right, root)) == oracles.oracle_getplen(enc, left, right, root)[0]
+    cands = nni_neighbourhood(left, right, root, n)
+    assert len(cands) == 2 * (n - 3)
+    got = engine.score_batch([t] * len(cands), cands)
+    step = max(1, len(cands) // 40)
+    for k in range(0, len(cands), step):
+        assert got[k] == oracles.oracle_getplen(enc, cands[k].left, cands[k].right, root)[0], k
+    engine.tree_destroy(t)
+
+
+@pytest.mark.parametrize("n,m,seed", [(5, 1, 1), (5, 16, 2), (6, 17, 3), (17, 4097, 4), (64, 8 * 16 * 256 + 5, 5), (500, 100000, 6)])
+def test_full_pass_shapes(engine, n, m, seed):
+    """ragged row widths (1 word, not a multiple of the 16-byte column, of the 128-byte pad,
+    of the CTA width) up to BASELINE config 3's 500 x 100k"""
+    st = synthetic.states(n, m, seed=seed, p=0.1)
+    enc = synthetic.pack_states(st)
+    left, right, root = synthetic.random_topology(n, seed=seed)
+    engine.upload(enc, max_trees=1)
+    t = engine.tree_create()
+    want, rows, chg = oracles.oracle_getplen(enc, left, right, root)
+    assert engine.commit(t, Topology(left, right, root)) == want
+    assert np.array_equal(engine.changes(t)[n:], chg[n:])
+    for v in {n, (3 * n) // 2, 2 * n - 4}:
+        assert np.array_equal(engine.download_row(t, v), rows[v])
+    engine.tree_destroy(t)
+
+
+def test_caterpillar_and_balanced_trees(engine):
+    """extreme shapes: dependency chain of n-3 nodes with no stack, and the deepest stack"""
+    n, m = 129, 5000
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=3, p=0.1))
+    B = 2 * n - 3
+    left, right = np.full(B, -1, dtype=np.int64), np.full(B, -1, dtype=np.int64)
+    left[0], right[0] = n, 1
+    leaf = 2
+    for v in range(n, B):
+        if v + 1 < B:
+            left[v], right[v] = v + 1, leaf
+            leaf += 1
+        else:
+            left[v], right[v] = leaf, leaf + 1
+    engine.upload(enc, max_trees=1)
+    t = engine.tree_create()
+    assert engine.commit(t, Topology(left, right, 0)) == oracles.oracle_getplen(enc, left, right, 0)[0]
+    left, right = np.full(B, -1, dtype=np.int64), np.full(B, -1, dtype=np.int64)
+    level, nxt = list(range(1, n)), n
+    while len(level) > 2:
+        new = []
+        for k in range(0, len(level), 2):
+            left[nxt], right[nxt] = level[k], level[k + 1]
+            new.append(nxt)
+            nxt += 1
+        level = new
+    left[0], right[0] = level
+    want, rows, _ = oracles.oracle_getplen(enc, left, right, 0)
+    assert engine.commit(t, Topology(left, right, 0)) == want
+    assert np.array_equal(engine.download_row(t, B - 1), rows[B - 1])
+
+
+def test_errors_are_loud(engine, golden_dir):
+    g = load(golden_dir, "example.npz")
+    engine.upload(g["enc"], max_trees=1)
+    t = engine.tree_create()
+    topo = Topology(g["random_left"], g["random_right"], 0)
+    with pytest.raises(GpuError, match="never been evaluated"):
+        engine.score_batch([t], [topo])
+    with pytest.raises(GpuError, match="first commit"):
+        engine.commit(t, Topology(g["random_left"], g["random_right"], 0, [150]))
+    with pytest.raises(GpuError, match="in use"):
+        engine.tree_create()
+    with pytest.raises(GpuError, match="does not exist"):
+        engine.score_batch([5], [topo])
+    with pytest.raises(GpuError, match="not a leaf"):
+        engine.commit(t, Topology(g["random_left"], g["random_right"], 120))
+
+
+def test_full_size_2000x1M(engine):
+    """BASELINE config 4 shape on one GPU (2.0 GB of state rows): full pass bit-exact against
+    the oracle, root-invariance of the length, and incremental == full on the same tree"""
+    n, nwords = 2000, 62500
+    enc = synthetic.random_packed(n, nwords, seed=2)
+    left, right, root = synthetic.random_topology(n, seed=8)
+    engine.upload(enc, max_trees=1)
+    t = engine.tree_create()
+    want, rows, chg = oracles.oracle_getplen(enc, left, right, root)
+    assert engine.commit(t, Topology(left, right, root)) == want
+    assert np.array_equal(engine.changes(t)[n:], chg[n:])
+    for v in (n, n + 999, 2 * n - 4):
+        assert np.array_equal(engine.download_row(t, v), rows[v])
+    # a candidate: NNI at some deep node, scored incrementally, then committed, then re-evaluated in full
+    cands = nni_neighbourhood(left, right, root, n)
+    pick = [cands[k] for k in (0, 1777, 3993)]
+    got = engine.score_batch([t] * 3, pick)
+    full = oracles.oracle_getplen(enc, pick[1].left, pick[1].right, root)[0]
+    assert got[1] == full
+    assert engine.commit(t, pick[1]) == full
+    assert engine.commit(t, Topology(pick[1].left, pick[1].right, root)) == full
+    engine.tree_destroy(t)

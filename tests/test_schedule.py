@@ -1,0 +1,197 @@
+"""CPU: the host schedule compiler (lvb_b200/csrc/schedule.cpp, reached through the C-ABI's
+lvb_gpu_compile_schedule) checked by interpreting its instruction stream in numpy
+(tests/fitch_vm.py) against the reference's golden lengths / rows / per-node counts."""
+import os
+
+import numpy as np
+import pytest
+
+import fitch_vm
+from lvb_b200 import GpuError, Topology, compile_schedule
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def fresh_rows(enc):
+    n, nwords = enc.shape
+    rows = np.zeros((2 * n - 3, nwords), dtype=np.uint64)
+    rows[:n] = enc
+    return rows
+
+
+def test_full_pass_program_shape_and_result(golden_dir):
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n = enc.shape[0]
+    topo = Topology(g["random_left"], g["random_right"], int(g["random_root"]))
+    instr, slots = compile_schedule(n, topo, store=True)
+    assert instr.shape == (n - 3 + 2, 4)  # one per internal node + the two root-step applications
+    assert 0 < slots <= 24
+    nodes = instr[:, 2]
+    assert sorted(nodes[nodes >= 0].tolist()) == list(range(n, 2 * n - 3))
+    # every HBM operand is a leaf row: internal results travel in registers / stack slots only
+    ops = instr[:, :2]
+    assert ops.max() < n
+    rows = fresh_rows(enc)
+    total, per_node, rootc = fitch_vm.run_program(instr, rows, n, store=True)
+    assert total == int(g["random_length"]) == 11808
+    assert np.array_equal(rows, g["random_rows_after"])
+    want = g["random_changes_after"]
+    assert all(per_node[v] == want[v] for v in range(n, 2 * n - 3))
+    assert rootc == 11808 - want[n:].sum()
+
+
+@pytest.mark.parametrize("step,prev", [("nni", "random"), ("spr", "nni"), ("tbr", "spr")])
+def test_incremental_program(golden_dir, step, prev):
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n = enc.shape[0]
+    rows = g[f"{prev}_rows_after"].copy()
+    chg = g[f"{prev}_changes_after"]
+    dirty = np.nonzero(g[f"{step}_dirty"])[0]
+    assert dirty.min() >= n
+    topo = Topology(g[f"{step}_left"], g[f"{step}_right"], int(g[f"{step}_root"]), dirty)
+    # score: nothing stored, length = cached counts of clean nodes + recomputed + root step
+    instr, slots = compile_schedule(n, topo, store=False)
+    assert len(instr) == len(dirty) + 2
+    before = rows.copy()
+    total, per_node, rootc = fitch_vm.run_program(instr, rows, n, store=False)
+    assert np.array_equal(rows, before)
+    clean = np.setdiff1d(np.arange(n, 2 * n - 3), dirty)
+    assert chg[clean].sum() + total == int(g[f"{step}_length"])
+    # commit: same program with stores reproduces the reference's rows and counts
+    instr, _ = compile_schedule(n, topo, store=True)
+    total2, per_node2, _ = fitch_vm.run_program(instr, rows, n, store=True)
+    assert total2 == total
+    assert np.array_equal(rows, g[f"{step}_rows_after"])
+    assert all(per_node2[v] == g[f"{step}_changes_after"][v] for v in dirty)
+
+
+def test_proposal_series_scores(golden_dir):
+    """300 reference proposals (nni/spr/tbr, accept-if-not-worse, re-root every 50): score each
+    against the current state, commit the accepted ones; re-rooting recomputes only the nodes
+    whose children changed"""
+    g = load(golden_dir, "proposals.npz")
+    enc = load(golden_dir, "example.npz")["enc"]
+    n = enc.shape[0]
+    B = 2 * n - 3
+    rows = fresh_rows(enc)
+    chg = np.zeros(B, dtype=np.int64)
+    cur_l, cur_r, cur_root = g["start_left"].astype(np.int64), g["start_right"].astype(np.int64), int(g["start_root"])
+    instr, _ = compile_schedule(n, Topology(cur_l, cur_r, cur_root), store=True)
+    _, per_node, _ = fitch_vm.run_program(instr, rows, n, store=True)
+    for v, c in per_node.items():
+        chg[v] = c
+    max_slots = 0
+    for i in range(len(g["length"])):
+        left, right, root = g["left"][i].astype(np.int64), g["right"][i].astype(np.int64), int(g["root"][i])
+        ref_dirty = np.nonzero(g["dirty"][i])[0]
+        # nodes whose children differ from the device's current tree (covers re-rooting, where
+        # the reference dirties everything but only the path between the roots changes)
+        changed = np.nonzero((left != cur_l) | (right != cur_r))[0]
+        changed = changed[changed >= n]
+        if len(ref_dirty) == n - 3:
+            # all-dirty after a re-root: the candidate differs from the current tree along the
+            # re-root path and the proposal's own paths; close the changed set towards the root
+            parent = np.full(B, -1, dtype=np.int64)
+            for v in range(n, B):
+                parent[left[v]] = v
+                parent[right[v]] = v
+            parent[left[root]] = root
+            parent[right[root]] = root
+            dirty = set()
+            for v in changed.tolist():
+                while v >= n and v not in dirty:
+                    dirty.add(v)
+                    v = parent[v]
+            dirty = np.array(sorted(dirty), dtype=np.int64)
+        else:
+            dirty = ref_dirty
+            assert set(changed.tolist()) <= set(dirty.tolist())
+        topo = Topology(left, right, root, dirty)
+        instr, slots = compile_schedule(n, topo, store=False)
+        max_slots = max(max_slots, slots)
+        total, _, _ = fitch_vm.run_program(instr, rows, n, store=False)
+        clean = np.setdiff1d(np.arange(n, B), dirty)
+        assert chg[clean].sum() + total == int(g["length"][i]), i
+        if g["accepted"][i]:
+            instr, _ = compile_schedule(n, topo, store=True)
+            _, per_node, _ = fitch_vm.run_program(instr, rows, n, store=True)
+            for v, c in per_node.items():
+                chg[v] = c
+            cur_l, cur_r, cur_root = left, right, root
+    assert max_slots <= 2  # SPR/TBR: two dirty paths meet once or twice
+
+
+def test_slots_follow_tree_shape():
+    # caterpillar: every internal node has a leaf child -> no stack at all
+    n = 64
+    B = 2 * n - 3
+    left = np.full(B, -1, dtype=np.int64)
+    right = np.full(B, -1, dtype=np.int64)
+    # root 0; internal nodes n..B-1 chained; leaves 1..n-1
+    left[0], right[0] = n, 1
+    leaf = 2
+    for v in range(n, B):
+        if v + 1 < B:
+            left[v], right[v] = v + 1, leaf
+            leaf += 1
+        else:
+            left[v], right[v] = leaf, leaf + 1
+    instr, slots = compile_schedule(n, Topology(left, right, 0), store=True)
+    assert slots == 0 and len(instr) == n - 1
+    # balanced tree over 64 leaves + the root leaf: log2 depth of stack
+    n = 65
+    B = 2 * n - 3
+    left = np.full(B, -1, dtype=np.int64)
+    right = np.full(B, -1, dtype=np.int64)
+    level = list(range(1, n))
+    nxt = n
+    while len(level) > 2:
+        new = []
+        for k in range(0, len(level), 2):
+            left[nxt], right[nxt] = level[k], level[k + 1]
+            new.append(nxt)
+            nxt += 1
+        level = new
+    left[0], right[0] = level
+    assert nxt == B
+    instr, slots = compile_schedule(n, Topology(left, right, 0), store=True)
+    assert slots == 5 and len(instr) == n - 1  # 32 cherries -> ... -> 2 subtrees: depth 5
+
+
+def test_malformed_topologies_are_rejected(golden_dir):
+    g = load(golden_dir, "example.npz")
+    n = g["enc"].shape[0]
+    left, right = g["random_left"].copy(), g["random_right"].copy()
+    with pytest.raises(GpuError):
+        compile_schedule(n, Topology(left, right, n + 1))  # root must be a leaf
+    with pytest.raises(GpuError):
+        compile_schedule(n, Topology(left, right, 0, [3]))  # a leaf cannot be dirty
+    bad = left.copy()
+    bad[n + 5] = n + 5  # self loop
+    with pytest.raises(GpuError):
+        compile_schedule(n, Topology(bad, right, 0))
+    bad = left.copy()
+    v = n + 7
+    bad[v] = right[v]  # both children equal
+    with pytest.raises(GpuError):
+        compile_schedule(n, Topology(bad, right, 0))
+    # a node reachable from two parents
+    bad = left.copy()
+    kids = [int(c) for c in left[n:] if c >= n]
+    bad[n + 1 if left[n + 1] < n else n + 2] = kids[0]
+    with pytest.raises(GpuError):
+        compile_schedule(n, Topology(bad, right, 0))
+
+
+def test_empty_dirty_set_is_just_the_root_step(golden_dir):
+    g = load(golden_dir, "example.npz")
+    n = g["enc"].shape[0]
+    rows = g["random_rows_after"].copy()
+    instr, slots = compile_schedule(n, Topology(g["random_left"], g["random_right"], 0, []), store=False)
+    assert len(instr) == 2 and slots == 0
+    total, _, rootc = fitch_vm.run_program(instr, rows, n, store=False)
+    assert total == rootc == 11808 - g["random_changes_after"][n:].sum()
