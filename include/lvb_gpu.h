@@ -135,6 +135,13 @@ int lvb_gpu_synchronize(lvb_gpu_ctx *ctx);
 int lvb_gpu_compile_schedule(int64_t n, const lvb_gpu_topology *topo, int store, int32_t *instr, int64_t cap,
                              int64_t *n_instr, int64_t *n_slots);
 
+/* Host-only: the same for a store program cut into independent subtrees of about piece_size
+ * nodes (how large commits are spread over the GPU).  pieces receives {instr_begin, n_instr,
+ * level} triples; pieces of one level may run concurrently, levels run in order. */
+int lvb_gpu_compile_pieces(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,
+                           int64_t *n_instr, int64_t *n_slots, int32_t *pieces, int64_t pieces_cap,
+                           int64_t *n_pieces);
+
 #ifdef __cplusplus
 }
 #endif

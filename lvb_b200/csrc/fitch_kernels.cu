@@ -133,7 +133,8 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
 
             uint4 out;
             const unsigned ch = fitch_step(x, y, out);
-            total += ch;
+            if (!PER_NODE)
+                total += ch;
             if (PER_NODE)
             {
                 const unsigned w = __reduce_add_sync(0xffffffffu, ch);
@@ -159,12 +160,14 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
         }
     }
 
+    if (PER_NODE)
+        return; /* store mode: lengths come from the per-instruction counts (commit_finalize) */
     /* per-program length: block reduce, one 64-bit atomic per CTA */
     const unsigned w = __reduce_add_sync(0xffffffffu, total);
     if ((tid & 31) == 0 && w)
         atomicAdd(&s_total, (unsigned long long)w);
     __syncthreads();
-    if (!PER_NODE && cb == 0)
+    if (cb == 0)
     {
         /* score mode: add the part of the length that does not change, once per program:
          * sum of cached counts of clean nodes = sum_chg - sum over recomputed nodes of chg

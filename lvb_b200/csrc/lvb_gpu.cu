@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -115,8 +116,14 @@ struct lvb_gpu_ctx
     std::vector<FitchProgram> prog;
     FitchInstr *d_instr = nullptr, *h_instr = nullptr;
     size_t cap_instr = 0;
-    FitchProgram *d_prog = nullptr, *h_prog = nullptr;
+    FitchProgram *d_prog = nullptr, *h_prog = nullptr; /* pieces, sorted by level */
     size_t cap_prog = 0;
+    std::vector<FitchProgram> cand;                    /* one entry per candidate (all its pieces) */
+    FitchProgram *d_cand = nullptr, *h_cand = nullptr;
+    size_t cap_cand = 0;
+    std::vector<ScheduleCompiler::Piece> pieces;
+    std::vector<std::pair<int32_t, int32_t>> levels;   /* (first piece, count) per launch */
+    int64_t target_warps = 148 * 384;                  /* resident warps wanted per launch */
     unsigned long long *d_totals = nullptr;
     long long *h_totals = nullptr;
     int32_t *d_cnts = nullptr;
@@ -139,8 +146,27 @@ struct lvb_gpu_ctx
     int nranks = 1, rank = 0;
 };
 
-static int ensure_batch_capacity(lvb_gpu_ctx *c, size_t n_instr, size_t n_prog)
+static int ensure_batch_capacity(lvb_gpu_ctx *c, size_t n_instr, size_t n_prog, size_t n_cand)
 {
+    if (n_cand > c->cap_cand)
+    {
+        size_t cap = c->cap_cand ? c->cap_cand : 256;
+        while (cap < n_cand)
+            cap *= 2;
+        if (c->d_cand)
+        {
+            CU(cudaStreamSynchronize(c->stream));
+            CU(cudaFree(c->d_cand));
+            CU(cudaFree(c->d_totals));
+            CU(cudaFreeHost(c->h_cand));
+            CU(cudaFreeHost(c->h_totals));
+        }
+        CU(cudaMalloc(&c->d_cand, cap * sizeof(FitchProgram)));
+        CU(cudaMalloc(&c->d_totals, cap * sizeof(unsigned long long)));
+        CU(cudaMallocHost(&c->h_cand, cap * sizeof(FitchProgram)));
+        CU(cudaMallocHost(&c->h_totals, cap * sizeof(long long)));
+        c->cap_cand = cap;
+    }
     if (n_instr > c->cap_instr)
     {
         size_t cap = c->cap_instr ? c->cap_instr : 4096;
@@ -167,14 +193,10 @@ static int ensure_batch_capacity(lvb_gpu_ctx *c, size_t n_instr, size_t n_prog)
         {
             CU(cudaStreamSynchronize(c->stream));
             CU(cudaFree(c->d_prog));
-            CU(cudaFree(c->d_totals));
             CU(cudaFreeHost(c->h_prog));
-            CU(cudaFreeHost(c->h_totals));
         }
         CU(cudaMalloc(&c->d_prog, cap * sizeof(FitchProgram)));
-        CU(cudaMalloc(&c->d_totals, cap * sizeof(unsigned long long)));
         CU(cudaMallocHost(&c->h_prog, cap * sizeof(FitchProgram)));
-        CU(cudaMallocHost(&c->h_totals, cap * sizeof(long long)));
         c->cap_prog = cap;
     }
     return 0;
@@ -221,32 +243,36 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     p.ncols = (int32_t)c->stride_u4;
     p.n = (int32_t)c->n;
     p.n_internal = (int32_t)c->I;
-    p.n_prog = (int32_t)K;
     const int block = pick_block(c);
     p.n_colblocks = (int32_t)((c->stride_u4 + block - 1) / block);
     p.n_slots = c->last_slots;
     p.instr = c->d_instr;
-    p.prog = c->d_prog;
     p.totals = c->d_totals;
     p.cnts = c->d_cnts;
     p.chg = c->chg;
     p.sum_chg = c->sum_chg;
-    if ((int64_t)p.n_prog * p.n_colblocks > (int64_t)INT32_MAX)
-        return fail("batch too large: %lld CTAs", (long long)p.n_prog * p.n_colblocks);
 
     if (c->ring_used == lvb_gpu_ctx::kEvRing && drain_kernel_events(c))
         return 1;
     const int slot = c->ring_used++;
     CU(cudaEventRecord(c->ring0[slot], c->stream));
-    CU(launch_fitch_exec(p, store, block, c->stream));
+    /* one launch per dependency level: pieces of a level only read rows stored by earlier levels */
+    for (const auto &lv : c->levels)
+    {
+        p.prog = c->d_prog + lv.first;
+        p.n_prog = lv.second;
+        if ((int64_t)p.n_prog * p.n_colblocks > (int64_t)INT32_MAX)
+            return fail("batch too large: %lld CTAs", (long long)p.n_prog * p.n_colblocks);
+        CU(launch_fitch_exec(p, store, block, c->stream));
+        c->launches++;
+    }
     CU(cudaEventRecord(c->ring1[slot], c->stream));
     c->ev0 = c->ring0[slot];
     c->ev1 = c->ring1[slot];
     c->timed = true;
-    c->launches++;
     if (store)
     {
-        CU(launch_commit_finalize(c->d_instr, c->d_prog, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
+        CU(launch_commit_finalize(c->d_instr, c->d_cand, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
                                   (long long *)c->d_totals, c->stream));
         c->launches++;
     }
@@ -278,8 +304,15 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     c->last_K = 0;
     c->instr.clear();
     c->prog.clear();
+    c->cand.clear();
+    c->levels.clear();
     int n_slots = 0;
     std::string err;
+    /* Large store programs are cut into independent subtrees so that enough warps are resident:
+     * a program owns ceil(cols/32) warps per piece. */
+    const int64_t warps_per_piece = (c->stride_u4 + 31) / 32;
+    const int64_t want_pieces = store ? std::max<int64_t>(1, c->target_warps / (warps_per_piece * K)) : 1;
+    std::vector<std::pair<int32_t, int32_t>> piece_of; /* (level, index into c->prog) */
     for (int64_t k = 0; k < K; k++)
     {
         const int t = trees[k];
@@ -290,12 +323,32 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         if (store && !c->tree_ready[t] && topos[k].n_dirty >= 0)
             return fail("tree %d: first commit must recompute every internal node (n_dirty < 0)", t);
         const size_t begin = c->instr.size();
-        int slots = 0;
-        if (!c->sc->compile(topos[k], store, c->instr, slots, err))
+        int slots = 0, piece_size = 0;
+        if (want_pieces > 1)
+        {
+            const int64_t d = topos[k].n_dirty < 0 ? c->I : topos[k].n_dirty;
+            if (d >= 64) /* not worth a second launch for short programs */
+                piece_size = (int)std::max<int64_t>(4, (d + want_pieces - 1) / want_pieces);
+        }
+        c->pieces.clear();
+        if (!c->sc->compile(topos[k], store, c->instr, slots, err, piece_size, &c->pieces))
             return fail("candidate %lld: %s", (long long)k, err.c_str());
         if (slots > n_slots)
             n_slots = slots;
-        c->prog.push_back(FitchProgram{(int32_t)begin, (int32_t)(c->instr.size() - begin), t, store ? 1 : 0});
+        for (const auto &pc : c->pieces)
+            c->prog.push_back(FitchProgram{pc.instr_begin, pc.n_instr, t, pc.level});
+        c->cand.push_back(FitchProgram{(int32_t)begin, (int32_t)(c->instr.size() - begin), t, store ? 1 : 0});
+    }
+    /* pieces sorted by level; one launch per level */
+    std::stable_sort(c->prog.begin(), c->prog.end(),
+                     [](const FitchProgram &a, const FitchProgram &b) { return a.flags < b.flags; });
+    for (size_t i = 0; i < c->prog.size();)
+    {
+        size_t j = i;
+        while (j < c->prog.size() && c->prog[j].flags == c->prog[i].flags)
+            j++;
+        c->levels.push_back({(int32_t)i, (int32_t)(j - i)});
+        i = j;
     }
     if (store)
     { /* in-place commits of one tree must not share a launch */
@@ -309,15 +362,18 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     }
     if (c->instr.size() > (size_t)INT32_MAX)
         return fail("batch too large: %zu instructions", c->instr.size());
-    if (ensure_batch_capacity(c, c->instr.size(), c->prog.size()))
+    if (ensure_batch_capacity(c, c->instr.size(), c->prog.size(), c->cand.size()))
         return 1;
     /* a previous asynchronous batch may still be reading the pinned staging buffers */
     CU(cudaStreamSynchronize(c->stream));
     memcpy(c->h_instr, c->instr.data(), c->instr.size() * sizeof(FitchInstr));
     memcpy(c->h_prog, c->prog.data(), c->prog.size() * sizeof(FitchProgram));
+    memcpy(c->h_cand, c->cand.data(), c->cand.size() * sizeof(FitchProgram));
     CU(cudaMemcpyAsync(c->d_instr, c->h_instr, c->instr.size() * sizeof(FitchInstr), cudaMemcpyHostToDevice,
                        c->stream));
     CU(cudaMemcpyAsync(c->d_prog, c->h_prog, c->prog.size() * sizeof(FitchProgram), cudaMemcpyHostToDevice,
+                       c->stream));
+    CU(cudaMemcpyAsync(c->d_cand, c->h_cand, c->cand.size() * sizeof(FitchProgram), cudaMemcpyHostToDevice,
                        c->stream));
     if (store)
         for (int64_t k = 0; k < K; k++)
@@ -447,6 +503,9 @@ extern "C"
             CU(cudaEventCreate(&c->ring0[i]));
             CU(cudaEventCreate(&c->ring1[i]));
         }
+        const char *tw = getenv("LVB_GPU_TARGET_WARPS");
+        if (tw && atoll(tw) > 0)
+            c->target_warps = atoll(tw);
         const char *b = getenv("LVB_GPU_BLOCK");
         if (b)
         {
@@ -470,6 +529,8 @@ extern "C"
         cudaFree(c->d_instr);
         cudaFree(c->d_cnts);
         cudaFree(c->d_prog);
+        cudaFree(c->d_cand);
+        cudaFreeHost(c->h_cand);
         cudaFree(c->d_totals);
         cudaFreeHost(c->h_instr);
         cudaFreeHost(c->h_prog);
@@ -726,6 +787,34 @@ extern "C"
             return fail("no Fitch kernel has been launched yet");
         CU(cudaEventSynchronize(c->ev1));
         CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+        return 0;
+    }
+
+    int lvb_gpu_compile_pieces(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,
+                               int64_t *n_instr, int64_t *n_slots, int32_t *pieces, int64_t pieces_cap,
+                               int64_t *n_pieces)
+    {
+        if (!topo || !n_instr || !n_slots || !n_pieces)
+            return fail("lvb_gpu_compile_pieces: null argument");
+        if (n < 3)
+            return fail("lvb_gpu_compile_pieces: n too small");
+        ScheduleCompiler sc(n);
+        std::vector<FitchInstr> out;
+        std::vector<ScheduleCompiler::Piece> pcs;
+        int slots = 0;
+        std::string err;
+        if (!sc.compile(*topo, true, out, slots, err, piece_size, &pcs))
+            return fail("%s", err.c_str());
+        *n_instr = (int64_t)out.size();
+        *n_slots = slots;
+        *n_pieces = (int64_t)pcs.size();
+        if (instr)
+        {
+            if ((int64_t)out.size() > cap || (int64_t)pcs.size() > pieces_cap || !pieces)
+                return fail("buffers too small: need %zu instructions, %zu pieces", out.size(), pcs.size());
+            memcpy(instr, out.data(), out.size() * sizeof(FitchInstr));
+            memcpy(pieces, pcs.data(), pcs.size() * sizeof(ScheduleCompiler::Piece));
+        }
         return 0;
     }
 

@@ -13,13 +13,18 @@ static inline int64_t strided(const int64_t *base, int64_t stride_bytes, int64_t
 
 ScheduleCompiler::ScheduleCompiler(int64_t n)
     : n_(n), B_(2 * n - 3), cur_(0), stamp_(B_ > 0 ? B_ : 0, 0), child_(stamp_.size(), 0), seen_(stamp_.size(), 0),
-      need_(stamp_.size(), 0)
+      cut_(stamp_.size(), 0), need_(stamp_.size(), 0), size_(stamp_.size(), 0), level_(stamp_.size(), 0)
 {
 }
 
 bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::vector<FitchInstr> &out, int &n_slots,
-                               std::string &err)
+                               std::string &err, int piece_size, std::vector<Piece> *pieces)
 {
+    if (piece_size > 0 && (!store || !pieces))
+    {
+        err = "schedule: only store programs can be cut into pieces";
+        return false;
+    }
     if (n_ < 3)
     {
         err = "schedule: need at least 3 leaves";
@@ -30,6 +35,7 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
         std::fill(stamp_.begin(), stamp_.end(), 0u);
         std::fill(child_.begin(), child_.end(), 0u);
         std::fill(seen_.begin(), seen_.end(), 0u);
+        std::fill(cut_.begin(), cut_.end(), 0u);
         cur_ = 1;
     }
     const int64_t root = topo.root;
@@ -126,23 +132,36 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
         err = "schedule: dirty nodes do not form a forest (a node is reachable twice or lies on a cycle)";
         return false;
     }
-    /* stack need: slots in use at the peak while a node's dirty subtree is evaluated */
+    /* bottom-up over the dirty forest: piece cuts, piece levels, stack need.
+     * size: nodes of the current piece under v; a node whose piece reaches piece_size becomes
+     * the root of a piece of its own (its row is stored, the parent reads it from HBM).
+     * need: stack slots in use at the peak while v's part of the piece is evaluated. */
     for (size_t k = order_.size(); k-- > 0;)
     {
         const int32_t v = order_[k];
-        const int64_t l = L(v), r = R(v);
-        const bool dl = is_dirty(l), dr = is_dirty(r);
-        if (dl && dr)
+        const int64_t c[2] = {L(v), R(v)};
+        int32_t sz = 1, lvl = 0, nd[2] = {-1, -1};
+        for (int j = 0; j < 2; j++)
         {
-            const int32_t big = std::max(need_[l], need_[r]), small = std::min(need_[l], need_[r]);
-            need_[v] = std::max(big, small + 1);
+            if (!is_dirty(c[j]))
+                continue;
+            if (cut_[c[j]] == cur_)
+                lvl = std::max(lvl, level_[c[j]] + 1);
+            else
+            {
+                sz += size_[c[j]];
+                lvl = std::max(lvl, level_[c[j]]);
+                nd[j] = need_[c[j]];
+            }
         }
-        else if (dl)
-            need_[v] = need_[l];
-        else if (dr)
-            need_[v] = need_[r];
+        if (nd[0] >= 0 && nd[1] >= 0)
+            need_[v] = std::max(std::max(nd[0], nd[1]), std::min(nd[0], nd[1]) + 1);
         else
-            need_[v] = 0;
+            need_[v] = std::max(0, std::max(nd[0], nd[1]));
+        size_[v] = sz;
+        level_[v] = lvl;
+        if (piece_size > 0 && sz >= piece_size)
+            cut_[v] = cur_;
     }
 
     /* emission */
@@ -161,7 +180,7 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
             switch (f.stage)
             {
             case 0: {
-                const bool dl = is_dirty(l), dr = is_dirty(r);
+                const bool dl = inside(l), dr = inside(r);
                 if (dl && dr)
                 {
                     const bool left_first = need_[l] >= need_[r];
@@ -208,15 +227,47 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
             }
         }
     };
+    auto close_piece = [&](size_t begin, int level) {
+        if (pieces && out.size() > begin)
+            pieces->push_back(Piece{(int32_t)begin, (int32_t)(out.size() - begin), level});
+    };
+    /* pieces cut off below: each is a complete post-order program of its own */
+    int top_level = 0;
+    if (piece_size > 0)
+    {
+        for (size_t k = order_.size(); k-- > 0;)
+        {
+            const int32_t v = order_[k];
+            if (cut_[v] != cur_)
+                continue;
+            const size_t begin = out.size();
+            cut_[v] = 0; /* inside its own piece the root is an ordinary node */
+            emit_from(v);
+            cut_[v] = cur_;
+            close_piece(begin, level_[v]);
+        }
+    }
+    const size_t last_begin = out.size();
+    auto level_above = [&](int64_t v) {
+        if (is_dirty(v))
+            top_level = std::max(top_level, level_[v] + (cut_[v] == cur_ ? 1 : 0));
+    };
     /* dirty subtrees that do not hang under the root's children (only for dirty sets that are
      * not closed towards the root; LVB's operators never produce them, getplen would still
      * recompute them) */
     for (int32_t v : dirty_)
         if (child_[v] != cur_ && v != rl && v != rr)
-            emit_from(v);
+        {
+            level_above(v);
+            if (cut_[v] != cur_)
+                emit_from(v);
+        }
     /* root step, TreeEvaluation.c:238-264 */
+    level_above(rl);
+    level_above(rr);
     emit_from(-1);
     out.push_back(FitchInstr{LVB_OPER_PREV, (int32_t)root, -1, LVB_CTL_COUNT_ONLY});
+    close_piece(last_begin, top_level);
 
     if (peak > LVB_MAX_SLOTS)
     {

@@ -24,11 +24,24 @@ class ScheduleCompiler
     /* n = number of leaves; reusable across calls (O(d) work per compile, no O(n) clearing) */
     explicit ScheduleCompiler(int64_t n);
 
+    /* One independently schedulable part of a program.  Pieces of level L read, as ordinary
+     * HBM rows, the rows stored by pieces of levels < L, so all pieces of one level can run
+     * concurrently and levels run as consecutive launches. */
+    struct Piece
+    {
+        int32_t instr_begin; /* index into `out` */
+        int32_t n_instr;
+        int32_t level;
+    };
+
     /* Appends the program for `topo` to `out`.  store: set LVB_CTL_STORE on every node
      * instruction.  Returns false and sets err on a malformed topology.  n_slots receives the
-     * number of stack slots the program uses. */
+     * number of stack slots the program uses.
+     * piece_size > 0 (store programs only): cut the dirty forest into subtrees of about
+     * piece_size..2*piece_size nodes; `pieces` receives them (the last one holds the root
+     * step).  piece_size == 0: one piece. */
     bool compile(const lvb_gpu_topology &topo, bool store, std::vector<FitchInstr> &out, int &n_slots,
-                 std::string &err);
+                 std::string &err, int piece_size = 0, std::vector<Piece> *pieces = nullptr);
 
     int64_t n() const { return n_; }
 
@@ -40,12 +53,17 @@ class ScheduleCompiler
         int32_t stage;
     };
     bool is_dirty(int64_t v) const { return v >= n_ && v < B_ && stamp_[v] == cur_; }
+    /* dirty and evaluated inside the piece that is being emitted (not the root of another piece) */
+    bool inside(int64_t v) const { return is_dirty(v) && cut_[v] != cur_; }
     int64_t n_, B_;
     uint32_t cur_;
     std::vector<uint32_t> stamp_;   /* dirty marks */
     std::vector<uint32_t> child_;   /* "is a child of a dirty node" marks */
     std::vector<uint32_t> seen_;    /* visited marks (cycle / duplicate guard) */
+    std::vector<uint32_t> cut_;     /* "is the root of a piece of its own" marks */
     std::vector<int32_t> need_;     /* stack need per dirty node */
+    std::vector<int32_t> size_;     /* nodes of the piece hanging under a dirty node */
+    std::vector<int32_t> level_;    /* level of the piece a dirty node belongs to */
     std::vector<int32_t> order_;    /* scratch: discovery order */
     std::vector<int32_t> dirty_;    /* scratch: de-duplicated dirty list */
     std::vector<Frame> frames_;

@@ -71,6 +71,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_rerun_last_batch.argtypes = [vp, C.POINTER(i64)]
     lib.lvb_gpu_synchronize.argtypes = [vp]
     lib.lvb_gpu_compile_schedule.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64)]
+    lib.lvb_gpu_compile_pieces.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64), vp, i64, C.POINTER(i64)]
     _lib = lib
     return lib
 
@@ -120,6 +121,20 @@ def compile_schedule(n: int, topo: Topology, store: bool = False):
     out = np.zeros((k.value, 4), dtype=np.int32)
     _check(lib.lvb_gpu_compile_schedule(n, C.byref(ts), int(store), out.ctypes.data, k.value, C.byref(k), C.byref(slots)))
     return out, int(slots.value)
+
+
+def compile_pieces(n: int, topo: Topology, piece_size: int):
+    """Host-only: a store program cut into pieces: (instr (k,4) int32, pieces (p,3) int32
+    rows {instr_begin, n_instr, level}, slots)."""
+    lib = load_library()
+    ts = topo.as_struct()
+    k, slots, npc = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    _check(lib.lvb_gpu_compile_pieces(n, C.byref(ts), piece_size, None, 0, C.byref(k), C.byref(slots), None, 0, C.byref(npc)))
+    instr = np.zeros((k.value, 4), dtype=np.int32)
+    pieces = np.zeros((npc.value, 3), dtype=np.int32)
+    _check(lib.lvb_gpu_compile_pieces(n, C.byref(ts), piece_size, instr.ctypes.data, k.value, C.byref(k), C.byref(slots),
+                                      pieces.ctypes.data, npc.value, C.byref(npc)))
+    return instr, pieces, int(slots.value)
 
 
 class Engine:

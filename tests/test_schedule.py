@@ -195,3 +195,47 @@ def test_empty_dirty_set_is_just_the_root_step(golden_dir):
     assert len(instr) == 2 and slots == 0
     total, _, rootc = fitch_vm.run_program(instr, rows, n, store=False)
     assert total == rootc == 11808 - g["random_changes_after"][n:].sum()
+
+
+@pytest.mark.parametrize("piece_size", [1, 3, 8, 16, 40, 97, 1000])
+def test_pieces_cover_the_program_and_respect_levels(golden_dir, piece_size):
+    """a store program cut into independent subtrees: every node exactly once, pieces of a
+    level only read rows stored by earlier levels, result identical to the uncut program"""
+    from lvb_b200 import compile_pieces
+
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n = enc.shape[0]
+    topo = Topology(g["tbr_left"], g["tbr_right"], int(g["tbr_root"]))
+    instr, pieces, slots = compile_pieces(n, topo, piece_size)
+    assert len(instr) == n - 1
+    assert pieces[:, 1].sum() == len(instr) and (pieces[:, 1] > 0).all()
+    nodes = instr[:, 2]
+    assert sorted(nodes[nodes >= 0].tolist()) == list(range(n, 2 * n - 3))
+    if piece_size >= n:
+        assert len(pieces) == 1
+    elif piece_size > 1:
+        sizes = pieces[:-1, 1]
+        assert (sizes >= piece_size).all() and (sizes <= 2 * piece_size - 1).all()
+    # run level by level; within a level, pieces may only read leaves and rows of lower levels
+    rows = fresh_rows(enc)
+    stored_level = {}
+    total = 0
+    for lvl in sorted(set(pieces[:, 2].tolist())):
+        wrote = []
+        for begin, cnt, plvl in pieces.tolist():
+            if plvl != lvl:
+                continue
+            part = instr[begin:begin + cnt]
+            for a, b, node, ctl in part.tolist():
+                for op in (a, b):
+                    if op >= n:
+                        assert stored_level[op] < lvl, (op, lvl)
+                if node >= 0:
+                    wrote.append(node)
+            t, _, _ = fitch_vm.run_program(part, rows, n, store=True)
+            total += t
+        for v in wrote:
+            stored_level[v] = lvl
+    assert total == int(g["tbr_length"])
+    assert np.array_equal(rows, g["tbr_rows_after"])
