@@ -1,0 +1,143 @@
+/* device.cpp — binding of an alignment to the GPU engine, and the reference-compatible,
+ * one-tree-per-call getplen() (src/TreeEvaluation.c:49-270) on top of it. */
+#include <cstdlib>
+#include <map>
+
+#include "lvb_host.h"
+
+namespace lvbhost
+{
+
+static void gpu_check(int rc)
+{
+    if (rc != 0)
+        crash("GPU error: %s", lvb_gpu_last_error()); /* errors of the device layer surface as crash(), src/Error.c:49 */
+}
+
+int64_t Device::launches() const { return ctx ? lvb_gpu_launch_count(ctx) : 0; }
+
+/* Main.c:82 lvb_initialize() + Solve.c:516-519 (enc_mat, DNAToBinary): the packed leaf rows
+ * are built once with the reference's layout and live on the device from here on */
+void device_open(Device &dev, int device_index, Dataptr MSA, int max_trees, int64_t word_begin, int64_t word_count)
+{
+    dev.MSA = MSA;
+    gpu_check(lvb_gpu_init(device_index, &dev.ctx));
+    std::vector<Lvb_bit_length> flat((size_t)MSA->n * (size_t)MSA->nwords);
+    std::vector<Lvb_bit_length *> rows((size_t)MSA->n);
+    for (long i = 0; i < MSA->n; i++)
+        rows[(size_t)i] = flat.data() + (size_t)i * (size_t)MSA->nwords;
+    DNAToBinary(MSA, rows.data());
+    if (word_count < 0)
+        word_count = MSA->nwords - word_begin;
+    gpu_check(lvb_gpu_matrix_upload(dev.ctx, MSA->n, MSA->nwords, (const uint64_t *const *)rows.data(), word_begin,
+                                    word_count, max_trees));
+}
+
+void device_close(Device &dev)
+{
+    if (dev.ctx)
+        lvb_gpu_shutdown(dev.ctx);
+    dev.ctx = nullptr;
+}
+
+/* ---- getplen, the compatible route ----
+ * The reference marks what must be recomputed by zeroing sitestate[0] of a node and makes a
+ * proposal by copying the whole current tree, state rows included (treecopy).  The host copy
+ * now moves one flag word per node; a clean flag holds 1 + the number of the device tree
+ * whose row for that node is valid.  getplen(tree):
+ *   - finds the device tree bound to this host array (created on first use),
+ *   - if the clean flags name ANOTHER device tree, the host tree was produced by treecopy from
+ *     that tree: the copy of the rows the reference did on the host is done now, device to
+ *     device (lvb_gpu_tree_copy),
+ *   - recomputes and stores the dirty nodes (lvb_gpu_tree_commit) and returns the length,
+ *   - leaves every flag clean, as the reference does (TreeEvaluation.c:125-130).
+ */
+static Device *g_dev = nullptr;
+static std::map<const TREESTACK_TREE_NODES *, int> g_bound;
+
+void getplen_bind_device(Device *dev)
+{
+    g_dev = dev;
+    g_bound.clear();
+}
+
+long getplen(Dataptr MSA, TREESTACK_TREE_NODES *tree, const Parameters &rc, long root, long *p_todo_arr,
+             long *p_todo_arr_sum_changes, int *p_runs)
+{
+    (void)rc;
+    (void)p_todo_arr;
+    (void)p_todo_arr_sum_changes;
+    (void)p_runs;
+    if (!g_dev || !g_dev->ctx)
+        crash("getplen: no GPU device is bound (there is no CPU path)");
+    const long n = MSA->n, B = MSA->numberofpossiblebranches;
+    int dt;
+    bool fresh = false;
+    auto it = g_bound.find(tree);
+    if (it == g_bound.end())
+    {
+        gpu_check(lvb_gpu_tree_create(g_dev->ctx, &dt));
+        g_bound[tree] = dt;
+        fresh = true;
+    }
+    else
+        dt = it->second;
+    const Lvb_bit_length mine = (Lvb_bit_length)dt + 1;
+    std::vector<int64_t> dirty;
+    Lvb_bit_length foreign = 0;
+    bool mixed = false;
+    for (long v = n; v < B; v++)
+    {
+        const Lvb_bit_length f = tree[v].sitestate[0];
+        if (f == 0)
+            dirty.push_back(v);
+        else if (f != mine)
+        {
+            if (foreign != 0 && foreign != f)
+                mixed = true;
+            foreign = f;
+        }
+    }
+    bool all = (long)dirty.size() == B - n;
+    if (!all && foreign != 0)
+    {
+        const bool known = !mixed && foreign - 1 < (Lvb_bit_length)INT32_MAX;
+        if (known && lvb_gpu_tree_copy(g_dev->ctx, dt, (int)(foreign - 1)) == 0)
+            fresh = false; /* the rows now are those of the source tree */
+        else
+            all = true; /* unknown provenance: recompute everything */
+    }
+    if (fresh && !all)
+        all = true;
+    lvb_gpu_topology tp;
+    tp.left = &tree[0].left;
+    tp.right = &tree[0].right;
+    tp.stride_bytes = (int64_t)sizeof(TREESTACK_TREE_NODES);
+    tp.root = root;
+    tp.dirty = dirty.data();
+    tp.n_dirty = all ? -1 : (int64_t)dirty.size();
+    int64_t length = 0;
+    gpu_check(lvb_gpu_tree_commit(g_dev->ctx, dt, &tp, &length));
+    for (long v = n; v < B; v++)
+        tree[v].sitestate[0] = mine;
+    lvb_assert(length > 0); /* TreeEvaluation.c:267 */
+    return (long)length;
+}
+
+/* src/MemoryOperations.c:120-132: the scratch arrays belong to the CPU algorithm; kept so that
+ * callers compile unchanged */
+void alloc_memory_to_getplen(Dataptr MSA, long **p_todo_arr, long **p_todo_arr_sum_changes, int **p_runs)
+{
+    (void)MSA;
+    *p_todo_arr = nullptr;
+    *p_todo_arr_sum_changes = nullptr;
+    *p_runs = nullptr;
+}
+void free_memory_to_getplen(long **p_todo_arr, long **p_todo_arr_sum_changes, int **p_runs)
+{
+    free(*p_todo_arr);
+    free(*p_todo_arr_sum_changes);
+    free(*p_runs);
+}
+
+} // namespace lvbhost

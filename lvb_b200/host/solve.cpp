@@ -1,0 +1,766 @@
+/* solve.cpp — the simulated-annealing search (src/Solve.c: GetSoln, Anneal;
+ * src/StartingTemperature.c) re-driven in batches for the device.
+ *
+ * The reference evaluates one proposal per getplen() call.  Here every launch scores a batch:
+ *   - across chains: R independent replicates (seeds seed, seed+1, ...) advance in lock-step, and
+ *   - along a chain: up to K proposals are generated speculatively from the SAME current tree,
+ *     each assuming that the ones before it are rejected.
+ * Speculation is exact, not approximate.  Between two proposals the reference touches the
+ * random stream only through (a) the operator choice and the mutate_* draws, which do not
+ * depend on the outcome of earlier proposals as long as the current tree is unchanged, and
+ * (b) one uni() per WORSENING proposal whether or not it is accepted (src/Solve.c:356-376;
+ * src/StartingTemperature.c:147-163).  A rejected proposal is by definition a worsening one,
+ * so "the k earlier proposals were rejected" fixes the stream exactly.  The lengths come back,
+ * acceptance is replayed in order with the recorded draws, and at the first acceptance the
+ * chain resumes from the state snapshot taken at that proposal; the rest of the batch is
+ * discarded.  All counters, the cooling schedule, operator probabilities and stop tests are
+ * advanced by the same code in speculation and in replay (anneal_after / st_after).
+ * Batches end where the reference changes the current tree or the device state must change:
+ * re-rooting (every REROOT_INTERVAL proposals; at the start of every temperature step of
+ * StartingTemperature), the end of a phase, an acceptance.
+ *
+ * Tree lengths are never computed here; they come from lvb_gpu_commit_batch /
+ * lvb_gpu_score_batch (include/lvb_gpu.h).
+ */
+#include <cerrno>
+#include <cfloat>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+
+#include "lvb_host.h"
+
+namespace lvbhost
+{
+
+/* src/MyMaths.c:91-120, 146-170, 203-244: libm with loud failure */
+static double exp_wrapper(double x)
+{
+    const double val = exp(x);
+    if (errno == EDOM)
+        crash("internal error detected in function exp_wrapper():\ndomain error. x is %g", x);
+    else if (val == HUGE_VAL || val == -HUGE_VAL)
+        crash("internal error detected in function exp_wrapper():\nrange error. x is %g", x);
+    else if (val == 0.0)
+        crash("internal error detected in function exp_wrapper():\nunderflow. x is %g", x);
+    return val;
+}
+static double log_wrapper(double x)
+{
+    if (x <= 0.0)
+        crash("internal error detected in function log_wrapper():\ndomain error. x is %g", x);
+    return log(x);
+}
+static double pow_wrapper(double x, double y)
+{
+    if (x < 0.0 || (x == 0.0 && y <= 0.0))
+        crash("internal error detected in function pow_wrapper():\ndomain error. x is %g, y is %g", x, y);
+    return pow(x, y);
+}
+
+enum Phase
+{
+    PH_ST_BEGIN, /* GetSoln: first random tree, StartingTemperature set-up   (Solve.c:537-541) */
+    PH_ST_LOOP,  /* StartingTemperature's sampling loop                     (StartingTemperature.c:106-181) */
+    PH_AN_BEGIN, /* GetSoln: second random tree, Anneal set-up               (Solve.c:543-545, 194-233) */
+    PH_AN_LOOP,  /* Anneal's loop                                            (Solve.c:235-469) */
+    PH_FINISH,   /* GetSoln after Anneal                                     (Solve.c:567-569) */
+    PH_DONE
+};
+enum Outcome
+{
+    REJECT,
+    ACCEPT_LE,   /* not longer than the current tree: accepted, no draw      (Solve.c:307) */
+    ACCEPT_WORSE /* longer, accepted by the Metropolis draw                  (Solve.c:368) */
+};
+
+/* Everything the two loops carry from one proposal to the next, except the tree lengths
+ * (known only after the device answered) and the trees themselves. */
+struct SAState
+{
+    Phase phase = PH_ST_BEGIN;
+    Uni rng;
+    /* Anneal (Solve.c:159-182, 209-212) */
+    long accepted = 0, failedcnt = 0, iter = 0, t_n = 0, proposed = 0, current_iter = 0;
+    double t = 0, t0 = 0;
+    double trops_counter[3] = {1, 1, 1}, trops_probs[3] = {0, 0, 0};
+    long trops_id = 0;
+    long w_changes_prop = 0, w_changes_acc = 0;
+    int op = 0; /* operator of the proposal being handled: 0 NNI, 1 SPR, 2 TBR */
+    /* StartingTemperature (StartingTemperature.c:81-86) */
+    long st_iter = 0;
+    int acc_pos_trans = 0, prop_pos_trans = 0;
+};
+
+struct CommitReq
+{
+    std::vector<TREESTACK_TREE_NODES> topo; /* snapshot: left/right are read from here */
+    std::vector<int64_t> dirty;
+    long root = 0;
+    bool all = false;         /* every internal node */
+    bool want_length = false; /* the chain waits for the length of this commit */
+    bool used = false;
+};
+
+struct Chain
+{
+    Dataptr MSA = nullptr;
+    Parameters rc;
+    int id = 0;
+    int dev_tree = -1;
+    bool log_progress = false;
+    TREESTACK *stack = nullptr;
+    std::vector<TrajectoryRow> *trajectory = nullptr;
+    FILE *tsv = nullptr;
+    FILE *sumfp = nullptr;
+
+    TREESTACK_TREE_NODES *cur = nullptr;
+    long root = 0;
+    long current_len = 0, best_len = 0;
+    bool await_len = false;
+    double tree_minimum_length = 0;
+    double log_eps = 0, log_grad_geom = 0, log_t0 = 0;
+    SAState S;
+
+    int kmax = 32, k_now = 1;
+    struct Spec
+    {
+        SAState mid; /* state after the proposal was generated, before the acceptance draw */
+        double u;    /* the draw a worsening proposal consumes */
+        bool row_valid;
+        TrajectoryRow row; /* log line if rejected (length filled in at replay) */
+    };
+    std::vector<TREESTACK_TREE_NODES *> cand;
+    std::vector<std::vector<int64_t>> cand_dirty;
+    std::vector<Spec> spec;
+    int n_spec = 0;
+    SAState spec_end;
+    CommitReq commits[3];
+    int n_commits = 0;
+
+    SearchResult res;
+
+    ~Chain()
+    {
+        free(cur);
+        for (auto *c : cand)
+            free(c);
+    }
+
+    void init(Dataptr msa, const Parameters &prm, int chain_id, int device_tree, int kmax_)
+    {
+        MSA = msa;
+        rc = prm;
+        id = chain_id;
+        dev_tree = device_tree;
+        kmax = kmax_ > 0 ? kmax_ : 32;
+        k_now = prm.speculation > 0 ? kmax : 1;
+        cur = treealloc(MSA, true);
+        cand.resize((size_t)kmax);
+        for (auto &c : cand)
+            c = treealloc(MSA, true);
+        cand_dirty.resize((size_t)kmax);
+        spec.resize((size_t)kmax);
+        S.rng.rinit(rc.seed + chain_id); /* Main.c:104 */
+        tree_minimum_length = (double)MSA->min_len_tree;
+        log_eps = log_wrapper(LVB_EPS);
+        log_grad_geom = log_wrapper(0.99);
+    }
+
+    CommitReq &new_commit()
+    {
+        lvb_assert(n_commits < 3);
+        CommitReq &c = commits[n_commits++];
+        c.used = true;
+        c.all = false;
+        c.want_length = false;
+        c.dirty.clear();
+        return c;
+    }
+    void snapshot(CommitReq &c, const TREESTACK_TREE_NODES *tree, long r)
+    {
+        c.topo.assign(tree, tree + MSA->numberofpossiblebranches);
+        c.root = r;
+    }
+
+    /* a new random start: PullRandomTree + ss_init (Solve.c:537-538, 543-544), all rows to compute */
+    void fresh_tree()
+    {
+        PullRandomTree(MSA, S.rng, cur);
+        ss_init(MSA, cur);
+        root = 0;
+        CommitReq &c = new_commit();
+        snapshot(c, cur, root);
+        c.all = true;
+        c.want_length = true;
+        await_len = true;
+        mark_all_clean(MSA, cur);
+        res.getplen_calls++;
+    }
+
+    /* arbreroot on the current tree (Solve.c:240; StartingTemperature.c:116-117).  The reference
+     * leaves `current` dirty and pays a full pass per proposal until one is accepted; here the
+     * rows of the nodes between the two roots — the only ones that change — are recomputed once. */
+    void reroot_current()
+    {
+        std::vector<long> path;
+        root = arbreroot(MSA, S.rng, cur, root, &path);
+        mark_all_clean(MSA, cur);
+        CommitReq &c = new_commit();
+        snapshot(c, cur, root);
+        c.dirty.assign(path.begin(), path.end());
+    }
+
+    /* ---- the part of an Anneal iteration before getplen (Solve.c:237-298), without the
+     * re-root: operator choice and mutate.  Returns the operator. ---- */
+    int anneal_propose(SAState &W, TREESTACK_TREE_NODES *dst)
+    {
+        lvb_assert(W.t > DBL_EPSILON);
+        const int a = rc.algorithm_selection;
+        if (a == 2)
+        {
+            const long total = (long)(W.trops_counter[0] + W.trops_counter[1] + W.trops_counter[2]);
+            for (int i = 0; i < 3; i++)
+                W.trops_probs[i] = W.trops_counter[i] / total;
+        }
+        int op;
+        if (a >= 1)
+        {
+            const double r = W.rng.uni();
+            if (r < W.trops_probs[0])
+                op = 0;
+            else if (r < W.trops_probs[0] + W.trops_probs[1])
+                op = 1;
+            else
+                op = 2;
+            if (a == 2)
+                W.trops_id = op;
+        }
+        else
+            op = (W.iter & 1) ? 1 : 0;
+        if (op == 0)
+            mutate_nni(MSA, W.rng, dst, cur, root);
+        else if (op == 1)
+            mutate_spr(MSA, W.rng, dst, cur, root);
+        else
+            mutate_tbr(MSA, W.rng, dst, cur, root);
+        W.op = op;
+        return op;
+    }
+
+    /* ---- the part of an Anneal iteration after getplen (Solve.c:307-468).  `real` is false
+     * while speculating (outcome REJECT only; no tree, stack or length is touched).
+     * Returns false when the loop ends. ---- */
+    bool anneal_after(SAState &W, Outcome out, long len, const TREESTACK_TREE_NODES *proposed, bool real,
+                      TrajectoryRow *row)
+    {
+        const int a = rc.algorithm_selection;
+        int changeAcc = 0;
+        if (out == ACCEPT_LE)
+        {
+            lvb_assert(real);
+            if (len <= best_len)
+            {
+                if (len < best_len)
+                    ClearTreestack(stack);
+                if (CompareTreeToTreestack(MSA, stack, proposed, root) == 1)
+                    W.accepted++;
+            }
+            current_len = len;
+            if (len < best_len)
+                best_len = len;
+            if (a == 1)
+                changeAcc = 1;
+        }
+        else
+        {
+            if (a == 2)
+                W.w_changes_prop++;
+            if (out == ACCEPT_WORSE)
+            {
+                lvb_assert(real);
+                if (a == 2)
+                    W.w_changes_acc++;
+                current_len = len;
+                if (a == 1)
+                    changeAcc = 1;
+            }
+        }
+        W.proposed++;
+
+        bool dect = false;
+        if (W.accepted >= MAXACCEPT_SLOW)
+        {
+            W.failedcnt = 0;
+            dect = true;
+        }
+        else if (W.proposed >= MAXPROPOSE_SLOW)
+        {
+            W.failedcnt++;
+            if (W.failedcnt >= MAXFAIL_SLOW && W.t < FROZEN_T)
+                return false; /* frozen: end of cooling (Solve.c:389-399) */
+            dect = true;
+        }
+        if (dect)
+        {
+            W.t_n++;
+            if (rc.cooling_schedule == 0)
+            {
+                const double ln_t = ((double)W.t_n) * log_grad_geom + log_t0;
+                if (ln_t < log_eps)
+                    W.t = LVB_EPS;
+                else
+                    W.t = pow_wrapper(0.99, (double)W.t_n) * W.t0;
+                if (a == 1)
+                {
+                    W.trops_probs[2] = W.t / W.t0;
+                    W.trops_probs[1] = (1 - W.trops_probs[2]) / 2;
+                    W.trops_probs[0] = W.trops_probs[1];
+                }
+            }
+            else
+            {
+                W.t = W.t0 - (10 * LVB_EPS) * W.t_n;
+                if (W.t < DBL_EPSILON || W.t <= LVB_EPS)
+                    W.t = LVB_EPS;
+            }
+            W.proposed = 0;
+            W.accepted = 0;
+            if (a == 2)
+            {
+                W.w_changes_prop = 0;
+                W.w_changes_acc = 0;
+            }
+        }
+        W.iter++;
+        if (rc.n_number_max_trees > 0 && stack->next >= rc.n_number_max_trees)
+            return false;
+        if (a == 2)
+        {
+            if (changeAcc == 1)
+                W.trops_counter[W.trops_id]++;
+            else
+                for (int i = 0; i < 3; i++)
+                    if (W.trops_id != i)
+                        W.trops_counter[i] += 0.5;
+        }
+        if (row)
+            *row = TrajectoryRow{W.iter, W.op, changeAcc, current_len, W.t, stack->next};
+        if (rc.max_rearrangements > 0 && W.current_iter >= rc.max_rearrangements)
+            return false; /* benchmark cut-off of this build; not in the reference */
+        return true;
+    }
+
+    /* ---- StartingTemperature, after getplen (StartingTemperature.c:135-181).  Returns false when
+     * the starting temperature is found; W.t0 then holds it. ---- */
+    bool st_after(SAState &W, Outcome out, long len, bool real)
+    {
+        if (out == ACCEPT_LE)
+        {
+            lvb_assert(real);
+            current_len = len;
+        }
+        else
+        {
+            W.prop_pos_trans++;
+            if (out == ACCEPT_WORSE)
+            {
+                lvb_assert(real);
+                current_len = len;
+                W.acc_pos_trans++;
+            }
+        }
+        W.st_iter++;
+        if (W.st_iter <= 100) /* sample_size + 1 proposals per temperature (:111) */
+            return true;
+        const double increment_size = 0.00001;
+        const double r_acc_to_prop = (double)W.acc_pos_trans / W.prop_pos_trans; /* 0/0 = NaN ends the loop (:171) */
+        W.t += increment_size;
+        W.st_iter = 0;
+        W.prop_pos_trans = 0;
+        W.acc_pos_trans = 0;
+        if (W.t >= 1 || W.t <= 0)
+        {
+            W.t0 = 1; /* :175-176 */
+            return false;
+        }
+        if (r_acc_to_prop <= 0.65)
+            return true;
+        W.t0 = W.t - increment_size; /* :193 */
+        return false;
+    }
+
+    Outcome decide(const SAState &mid, double u, long len) const
+    {
+        const long change = len - current_len;
+        double deltah = (tree_minimum_length / (double)current_len) - (tree_minimum_length / (double)len);
+        if (deltah > 1.0)
+            deltah = 1.0; /* MinimumTreeLength() problem with ambiguous sites (Solve.c:304-305) */
+        if (change <= 0)
+            return ACCEPT_LE;
+        if (-deltah < mid.t * log_eps)
+            return REJECT; /* pacc taken as 0; the draw is consumed all the same (Solve.c:356-364) */
+        const double pacc = exp_wrapper(-deltah / mid.t);
+        return u < pacc ? ACCEPT_WORSE : REJECT;
+    }
+
+    void emit(const TrajectoryRow &r)
+    {
+        static const char *const names[3] = {"NNI", "SPR", "TBR"};
+        if (trajectory)
+            trajectory->push_back(r);
+        if (tsv)
+            fprintf(tsv, "%ld\t%s\t%d\t%ld\t%lf\t%ld\n", r.iter, names[r.op], r.accepted, r.length, r.t * 10000, r.stack);
+    }
+
+    /* ---- one round, first half: bring the chain to the point where it needs lengths ---- */
+    void advance()
+    {
+        n_spec = 0;
+        if (S.phase == PH_DONE)
+            return;
+        if (S.phase == PH_ST_BEGIN)
+        {
+            fresh_tree();
+            S.t = LVB_EPS; /* StartingTemperature.c:76 */
+            S.st_iter = 0;
+            S.acc_pos_trans = S.prop_pos_trans = 0;
+            S.phase = PH_ST_LOOP;
+        }
+        else if (S.phase == PH_AN_BEGIN)
+        {
+            fresh_tree();
+            /* Anneal set-up, Solve.c:159-233 */
+            S.accepted = S.failedcnt = S.iter = S.t_n = S.proposed = 0;
+            S.t = S.t0;
+            lvb_assert(((float)S.t >= (float)LVB_EPS) && (S.t <= 1.0));
+            log_t0 = log_wrapper(S.t0);
+            for (int i = 0; i < 3; i++)
+            {
+                S.trops_counter[i] = 1;
+                S.trops_probs[i] = 0;
+            }
+            S.trops_id = 0;
+            S.w_changes_prop = S.w_changes_acc = 0;
+            CompareHashTreeToHashstack(MSA, stack, cur, root); /* init. tree initially best (Solve.c:207) */
+            if (log_progress && S.current_iter == 0)
+            {
+                printf("\n--------------------------------------------------------");
+                printf("\n  Temperature:   Rearrangement: TreeStack size: Length:\n");
+                printf("--------------------------------------------------------\n");
+            }
+            if (tsv)
+                fprintf(tsv, "Iteration\tAlgorithm\tAccepted\tLength\tTemperature\tTreestack Size\n");
+            S.phase = PH_AN_LOOP;
+        }
+        else if (S.phase == PH_FINISH)
+        {
+            /* Solve.c:567-569: pop the last best tree and push it back through the hash path */
+            TREESTACK_TREE_NODES *tmp = treealloc(MSA, true);
+            long r = 0;
+            PullTreefromTreestack(MSA, tmp, &r, stack);
+            CompareHashTreeToHashstack(MSA, stack, tmp, r);
+            free(tmp);
+            res.final_length = best_len;
+            res.rearrangements = S.current_iter;
+            res.start_temperature = S.t0;
+            S.phase = PH_DONE;
+            return;
+        }
+
+        const bool annealing = S.phase == PH_AN_LOOP;
+        /* the first proposal of the batch may begin with a re-root of the current tree */
+        if (annealing)
+        {
+            S.current_iter++;
+            if (S.current_iter % REROOT_INTERVAL == 0)
+            {
+                reroot_current();
+                if (log_progress && S.current_iter % STAT_LOG_INTERVAL == 0 && !await_len)
+                    printf("  %-15.8f%-15ld%-16ld%-15ld\n", S.t, S.current_iter, stack->next, current_len); /* lenlog */
+            }
+        }
+        else if (S.st_iter % REROOT_INTERVAL == 0)
+            reroot_current();
+
+        SAState W = S;
+        const int want = k_now;
+        while (n_spec < want)
+        {
+            if (n_spec > 0)
+            { /* later proposals: stop in front of a re-root */
+                if (annealing)
+                {
+                    if ((W.current_iter + 1) % REROOT_INTERVAL == 0)
+                        break;
+                    W.current_iter++;
+                }
+                else if (W.st_iter % REROOT_INTERVAL == 0)
+                    break;
+            }
+            Spec &sp = spec[(size_t)n_spec];
+            TREESTACK_TREE_NODES *dst = cand[(size_t)n_spec];
+            if (annealing)
+                anneal_propose(W, dst);
+            else
+            {
+                lvb_assert(W.t > DBL_EPSILON);
+                W.op = (W.st_iter & 1) ? 1 : 0; /* StartingTemperature.c:123-126 */
+                if (W.op)
+                    mutate_spr(MSA, W.rng, dst, cur, root);
+                else
+                    mutate_nni(MSA, W.rng, dst, cur, root);
+            }
+            collect_dirty(MSA, dst, cand_dirty[(size_t)n_spec]);
+            sp.mid = W;
+            sp.u = W.rng.uni();
+            sp.row_valid = false;
+            bool go_on;
+            if (annealing)
+            {
+                go_on = anneal_after(W, REJECT, 0, nullptr, false, &sp.row);
+                sp.row_valid = go_on; /* the iteration that ends the loop writes no line (Solve.c:394) */
+                if (!go_on)
+                    W.phase = PH_FINISH;
+            }
+            else
+            {
+                go_on = st_after(W, REJECT, 0, false);
+                if (!go_on)
+                    W.phase = PH_AN_BEGIN;
+            }
+            n_spec++;
+            if (!go_on)
+                break;
+        }
+        spec_end = W;
+        res.getplen_calls += n_spec;
+    }
+
+    /* ---- one round, second half: lengths are known ---- */
+    void resolve(const int64_t *commit_len, const int64_t *lens)
+    {
+        if (await_len)
+        {
+            lvb_assert(commit_len != nullptr);
+            current_len = (long)*commit_len;
+            await_len = false;
+            if (S.phase == PH_AN_LOOP)
+            {
+                best_len = current_len; /* Solve.c:205 */
+                res.initial_length = current_len;
+                if (sumfp)
+                    fprintf(sumfp, "%d\t%d\t%ld\t", 0, 0, current_len); /* Solve.c:558-559 */
+            }
+        }
+        n_commits = 0;
+        if (n_spec == 0)
+            return;
+        const bool annealing = S.phase == PH_AN_LOOP;
+        int taken = -1;
+        for (int k = 0; k < n_spec; k++)
+        {
+            Spec &sp = spec[(size_t)k];
+            const long len = (long)lens[k];
+            lvb_assert(len >= 1L);
+            const Outcome out = decide(sp.mid, sp.u, len);
+            if (out == REJECT)
+            {
+                if (sp.row_valid)
+                {
+                    sp.row.length = current_len;
+                    emit(sp.row);
+                }
+                continue;
+            }
+            /* accepted: resume from the snapshot of this proposal */
+            taken = k;
+            S = sp.mid;
+            if (out == ACCEPT_WORSE)
+                (void)S.rng.uni();
+            bool go_on;
+            if (annealing)
+            {
+                TrajectoryRow row;
+                go_on = anneal_after(S, out, len, cand[(size_t)k], true, &row);
+                if (go_on)
+                    emit(row);
+                else
+                    S.phase = PH_FINISH;
+            }
+            else
+            {
+                go_on = st_after(S, out, len, true);
+                if (!go_on)
+                    S.phase = PH_AN_BEGIN;
+            }
+            /* SwapTrees (Solve.c:323, 370): the proposal becomes the current tree; on the device
+             * only its dirty rows are rewritten */
+            treecopy(MSA, cur, cand[(size_t)k], true);
+            mark_all_clean(MSA, cur);
+            if (go_on)
+            {
+                CommitReq &c = new_commit();
+                snapshot(c, cur, root);
+                c.dirty = cand_dirty[(size_t)k];
+            }
+            break;
+        }
+        if (taken < 0)
+            S = spec_end;
+        if (S.phase == PH_AN_BEGIN && log_progress)
+            printf("  SA Starting Temperature: %-.8f\n", S.t0);
+        /* speculation depth for the next round */
+        if (rc.speculation > 0)
+            k_now = kmax;
+        else if (taken < 0)
+            k_now = std::min(kmax, k_now * 2);
+        else
+            k_now = std::max(1, std::min(kmax, (k_now + 2 * (taken + 1)) / 2));
+    }
+};
+
+static void gpu_check(int rc_)
+{
+    if (rc_ != 0)
+        crash("GPU error: %s", lvb_gpu_last_error());
+}
+
+/* src/Solve.c:481-609 for R chains at once */
+void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicates, std::vector<TREESTACK> &stacks,
+                    std::vector<SearchResult> &results, std::vector<TrajectoryRow> *trajectory, FILE *tsv)
+{
+    const auto t_start = std::chrono::steady_clock::now();
+    const int R = replicates;
+    stacks.assign((size_t)R, TREESTACK());
+    results.assign((size_t)R, SearchResult());
+    std::vector<Chain> chains((size_t)R);
+    FILE *sumfp = nullptr;
+    if (rc.verbose)
+    {
+        sumfp = fopen("sum", "w");
+        if (sumfp)
+            fprintf(sumfp, "StartNo\tCycleNo\tCycInit\tCycBest\tCycTrees\n");
+    }
+    for (int r = 0; r < R; r++)
+    {
+        int t = -1;
+        gpu_check(lvb_gpu_tree_create(dev.ctx, &t));
+        chains[(size_t)r].init(MSA, rc, r, t, rc.speculation);
+        chains[(size_t)r].stack = &stacks[(size_t)r];
+        if (r == 0)
+        {
+            chains[0].log_progress = true;
+            chains[0].trajectory = trajectory;
+            chains[0].tsv = tsv;
+            chains[0].sumfp = sumfp;
+        }
+    }
+    std::vector<int> trees;
+    std::vector<lvb_gpu_topology> topos;
+    std::vector<int64_t> lens, clen((size_t)R, 0);
+    std::vector<int> owner;
+    long score_launches = 0;
+    const size_t stride = sizeof(TREESTACK_TREE_NODES);
+    for (;;)
+    {
+        bool alive = false;
+        for (auto &c : chains)
+        {
+            c.advance();
+            alive = alive || c.S.phase != PH_DONE;
+        }
+        /* commits, in waves so that no tree appears twice in one launch */
+        for (int wave = 0; wave < 3; wave++)
+        {
+            trees.clear();
+            topos.clear();
+            owner.clear();
+            bool want = false;
+            for (int r = 0; r < R; r++)
+            {
+                Chain &c = chains[(size_t)r];
+                if (wave >= c.n_commits)
+                    continue;
+                const CommitReq &q = c.commits[wave];
+                lvb_gpu_topology tp;
+                tp.left = &q.topo[0].left;
+                tp.right = &q.topo[0].right;
+                tp.stride_bytes = (int64_t)stride;
+                tp.root = q.root;
+                tp.dirty = q.dirty.data();
+                tp.n_dirty = q.all ? -1 : (int64_t)q.dirty.size();
+                trees.push_back(c.dev_tree);
+                topos.push_back(tp);
+                owner.push_back(r);
+                want = want || q.want_length;
+            }
+            if (trees.empty())
+                break;
+            lens.resize(trees.size());
+            gpu_check(lvb_gpu_commit_batch(dev.ctx, (int64_t)trees.size(), trees.data(), topos.data(),
+                                           want ? lens.data() : nullptr));
+            if (want)
+                for (size_t i = 0; i < owner.size(); i++)
+                    if (chains[(size_t)owner[i]].commits[wave].want_length)
+                        clen[(size_t)owner[i]] = lens[i];
+        }
+        if (!alive)
+            break;
+        /* proposals of all chains in one launch */
+        trees.clear();
+        topos.clear();
+        for (int r = 0; r < R; r++)
+        {
+            Chain &c = chains[(size_t)r];
+            for (int k = 0; k < c.n_spec; k++)
+            {
+                lvb_gpu_topology tp;
+                tp.left = &c.cand[(size_t)k][0].left;
+                tp.right = &c.cand[(size_t)k][0].right;
+                tp.stride_bytes = (int64_t)stride;
+                tp.root = c.root;
+                tp.dirty = c.cand_dirty[(size_t)k].data();
+                tp.n_dirty = (int64_t)c.cand_dirty[(size_t)k].size();
+                trees.push_back(c.dev_tree);
+                topos.push_back(tp);
+            }
+        }
+        lens.resize(trees.size());
+        if (!trees.empty())
+        {
+            gpu_check(lvb_gpu_score_batch(dev.ctx, (int64_t)trees.size(), trees.data(), topos.data(), lens.data()));
+            score_launches++;
+        }
+        size_t off = 0;
+        for (int r = 0; r < R; r++)
+        {
+            Chain &c = chains[(size_t)r];
+            c.resolve(&clen[(size_t)r], lens.data() + off);
+            off += (size_t)c.n_spec;
+        }
+    }
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
+    for (int r = 0; r < R; r++)
+    {
+        results[(size_t)r] = chains[(size_t)r].res;
+        results[(size_t)r].launches_scored = score_launches;
+        results[(size_t)r].seconds = secs;
+        gpu_check(lvb_gpu_tree_destroy(dev.ctx, chains[(size_t)r].dev_tree));
+    }
+    if (sumfp)
+    {
+        /* Solve.c:579-585: the trees of this cycle, then the summary line */
+        FILE *resfp = fopen("res_start0_cycle0", "w");
+        long treec = 0;
+        if (resfp)
+        {
+            treec = PrintTreestack(MSA, &stacks[0], resfp);
+            fclose(resfp);
+        }
+        fprintf(sumfp, "%ld\t%ld\n", results[0].final_length, treec);
+        fclose(sumfp);
+    }
+}
+
+} // namespace lvbhost

@@ -1,0 +1,195 @@
+/* tests/mock_gpu.c — TEST INFRASTRUCTURE ONLY.
+ *
+ * A stand-in for liblvbgpu.so on machines without a GPU: the entry points of include/lvb_gpu.h
+ * that the host layer (lvb_b200/host/) calls, answered by the CPU oracle (oracle/fitch_oracle.c).
+ * tests/test_host_search.py loads it with RTLD_GLOBAL BEFORE liblvbhost.so, so that the host
+ * layer's unresolved lvb_gpu_* symbols bind here; the product libraries contain no seam, switch
+ * or fallback for this, and nothing under lvb_b200/ refers to this file.  It lets the `-m "not
+ * gpu"` suite check the host logic (speculative batching, acceptance replay, cooling, tree
+ * stack) against trajectories recorded from the reference; the `-m gpu` suite runs the same
+ * checks on the real library.
+ */
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/lvb_gpu.h"
+#include "../oracle/fitch_oracle.h"
+
+struct lvb_gpu_ctx
+{
+    long n, nwords, B, I, max_trees;
+    uint64_t *leaves;   /* n x nwords */
+    uint64_t **rows;    /* per tree: B x nwords (leaf rows included) */
+    long **changes;     /* per tree: B */
+    char *used, *ready;
+    long *left, *right; /* scratch topology */
+    uint64_t *scratch;
+    long *scratch_chg;
+    int64_t launches;
+};
+
+static char g_err[512];
+static int fail(const char *msg)
+{
+    snprintf(g_err, sizeof g_err, "mock: %s", msg);
+    return 1;
+}
+
+const char *lvb_gpu_last_error(void) { return g_err; }
+int lvb_gpu_device_count(int *count)
+{
+    *count = 1;
+    return 0;
+}
+int lvb_gpu_init(int device, lvb_gpu_ctx **ctx)
+{
+    (void)device;
+    *ctx = (lvb_gpu_ctx *)calloc(1, sizeof(lvb_gpu_ctx));
+    return 0;
+}
+int lvb_gpu_shutdown(lvb_gpu_ctx *c)
+{
+    if (!c)
+        return 0;
+    for (long t = 0; t < c->max_trees; t++)
+    {
+        free(c->rows[t]);
+        free(c->changes[t]);
+    }
+    free(c->rows);
+    free(c->changes);
+    free(c->leaves);
+    free(c->used);
+    free(c->ready);
+    free(c->left);
+    free(c->right);
+    free(c->scratch);
+    free(c->scratch_chg);
+    free(c);
+    return 0;
+}
+
+int lvb_gpu_matrix_upload(lvb_gpu_ctx *c, int64_t n, int64_t nwords, const uint64_t *const *enc_rows, int64_t word_begin,
+                          int64_t word_count, int64_t max_trees)
+{
+    if (word_begin != 0 || word_count != nwords)
+        return fail("site blocks are not mocked");
+    c->n = n;
+    c->nwords = nwords;
+    c->B = 2 * n - 3;
+    c->I = n - 3;
+    c->max_trees = max_trees;
+    c->leaves = (uint64_t *)malloc((size_t)n * nwords * 8);
+    for (long i = 0; i < n; i++)
+        memcpy(c->leaves + i * nwords, enc_rows[i], (size_t)nwords * 8);
+    c->rows = (uint64_t **)calloc((size_t)max_trees, sizeof(uint64_t *));
+    c->changes = (long **)calloc((size_t)max_trees, sizeof(long *));
+    c->used = (char *)calloc((size_t)max_trees, 1);
+    c->ready = (char *)calloc((size_t)max_trees, 1);
+    c->left = (long *)malloc((size_t)c->B * sizeof(long));
+    c->right = (long *)malloc((size_t)c->B * sizeof(long));
+    c->scratch = (uint64_t *)malloc((size_t)c->B * nwords * 8);
+    c->scratch_chg = (long *)malloc((size_t)c->B * sizeof(long));
+    return 0;
+}
+
+int lvb_gpu_tree_create(lvb_gpu_ctx *c, int *tree)
+{
+    for (long t = 0; t < c->max_trees; t++)
+        if (!c->used[t])
+        {
+            c->used[t] = 1;
+            c->ready[t] = 0;
+            if (!c->rows[t])
+            {
+                c->rows[t] = (uint64_t *)calloc((size_t)c->B * c->nwords, 8);
+                c->changes[t] = (long *)calloc((size_t)c->B, sizeof(long));
+            }
+            memcpy(c->rows[t], c->leaves, (size_t)c->n * c->nwords * 8);
+            *tree = (int)t;
+            return 0;
+        }
+    return fail("all device trees are in use");
+}
+
+int lvb_gpu_tree_destroy(lvb_gpu_ctx *c, int tree)
+{
+    c->used[tree] = 0;
+    return 0;
+}
+
+int lvb_gpu_tree_copy(lvb_gpu_ctx *c, int dst, int src)
+{
+    memcpy(c->rows[dst], c->rows[src], (size_t)c->B * c->nwords * 8);
+    memcpy(c->changes[dst], c->changes[src], (size_t)c->B * sizeof(long));
+    c->ready[dst] = c->ready[src];
+    return 0;
+}
+
+static long strided(const int64_t *base, int64_t stride, long i)
+{
+    return (long)*(const int64_t *)((const char *)base + i * stride);
+}
+
+/* evaluate topo against `rows`/`chg` (modified in place) */
+static long evaluate(lvb_gpu_ctx *c, const lvb_gpu_topology *tp, uint64_t *rows, long *chg)
+{
+    for (long v = 0; v < c->B; v++)
+    {
+        c->left[v] = strided(tp->left, tp->stride_bytes, v);
+        c->right[v] = strided(tp->right, tp->stride_bytes, v);
+    }
+    if (tp->n_dirty < 0)
+        for (long v = c->n; v < c->B; v++)
+            rows[v * c->nwords] = 0;
+    else
+        for (long k = 0; k < tp->n_dirty; k++)
+            rows[tp->dirty[k] * c->nwords] = 0;
+    c->launches++;
+    return oracle_getplen(c->n, c->nwords, c->left, c->right, (long)tp->root, rows, chg);
+}
+
+int lvb_gpu_commit_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                         int64_t *lengths)
+{
+    for (int64_t k = 0; k < n_cand; k++)
+    {
+        const int t = trees[k];
+        if (!c->ready[t] && topos[k].n_dirty >= 0)
+            return fail("first commit must recompute every internal node");
+        const long len = evaluate(c, &topos[k], c->rows[t], c->changes[t]);
+        c->ready[t] = 1;
+        if (lengths)
+            lengths[k] = len;
+    }
+    return 0;
+}
+
+int lvb_gpu_tree_commit(lvb_gpu_ctx *c, int tree, const lvb_gpu_topology *topo, int64_t *length)
+{
+    return lvb_gpu_commit_batch(c, 1, &tree, topo, length);
+}
+
+int lvb_gpu_score_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                        int64_t *lengths)
+{
+    for (int64_t k = 0; k < n_cand; k++)
+    {
+        const int t = trees[k];
+        if (!c->ready[t])
+            return fail("tree has never been evaluated");
+        memcpy(c->scratch, c->rows[t], (size_t)c->B * c->nwords * 8);
+        memcpy(c->scratch_chg, c->changes[t], (size_t)c->B * sizeof(long));
+        lengths[k] = evaluate(c, &topos[k], c->scratch, c->scratch_chg);
+    }
+    return 0;
+}
+
+int64_t lvb_gpu_launch_count(lvb_gpu_ctx *c) { return c ? c->launches : 0; }
+int lvb_gpu_synchronize(lvb_gpu_ctx *c)
+{
+    (void)c;
+    return 0;
+}
