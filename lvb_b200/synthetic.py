@@ -94,3 +94,30 @@ def random_topology(n: int, seed: int = 1):
         leaves.append(w)
     assert next_int == B
     return left, right, 0
+
+
+def survey_alignment(n: int, m: int, seed: int = 1, p: float = 0.05) -> np.ndarray:
+    """The exact generator of SURVEY.md appendix A (float64 draws), n x m uint8 states 0..3 in
+    file order.  `survey_alignment(100, 10000, 1, 0.05)` written by `write_phylip` is the file
+    whose reference run is recorded there (md5 a11fa9393aaf6c6b8150b4491e8a4d90)."""
+    rng = np.random.default_rng(seed)
+    seqs = [rng.integers(0, 4, size=m, dtype=np.uint8)]
+    while len(seqs) < n:
+        parent = seqs.pop(int(rng.integers(0, len(seqs))))
+        for _ in range(2):
+            child = parent.copy()
+            mask = rng.random(m) < p
+            child[mask] = (child[mask] + rng.integers(1, 4, size=int(mask.sum()), dtype=np.uint8)) % 4
+            seqs.append(child)
+    order = rng.permutation(n)
+    return np.stack([seqs[i] for i in order])
+
+
+def write_phylip(path: str, st: np.ndarray) -> None:
+    """PHYLIP sequential, one line per taxon, names T<k> left-justified to 10 characters."""
+    n, m = st.shape
+    lut = np.frombuffer(b"ACGT", dtype=np.uint8)
+    with open(path, "wb") as f:
+        f.write(f" {n} {m}\n".encode())
+        for k in range(n):
+            f.write(f"T{k:<9d}".encode() + bytes(lut[st[k]]) + b"\n")

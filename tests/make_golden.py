@@ -196,11 +196,104 @@ def gen_sa_runs():
     json.dump(runs, open(os.path.join(OUT, "sa_runs.json"), "w"), indent=1)
 
 
+def run_reference_cli(infile_bytes: bytes, flags, fmt_flags=()):
+    """the reference binary in a directory of its own, verbose (-v writes changeAccepted.tsv and sum)"""
+    with tempfile.TemporaryDirectory() as td:
+        open(os.path.join(td, "infile"), "wb").write(infile_bytes)
+        p = subprocess.run([oracles.REF_BIN, *flags, "-v"], cwd=td, capture_output=True, text=True, check=True)
+        o = p.stdout
+        tsv = open(os.path.join(td, "changeAccepted.tsv")).read().splitlines()
+        return dict(
+            score=int(re.search(r"Tree score: +(\d+)", o).group(1)),
+            topologies=int(re.search(r"Topologies recovered: +(\d+)", o).group(1)),
+            rearrangements=int(re.search(r"Rearrangements evaluated: +(\d+)", o).group(1)),
+            start_temp=re.search(r"Starting Temperature: +([0-9.]+)", o).group(1),
+            outtree_md5=hashlib.md5(open(os.path.join(td, "outtree"), "rb").read()).hexdigest(),
+            outtree=open(os.path.join(td, "outtree")).read() if os.path.getsize(os.path.join(td, "outtree")) < 20000 else None,
+            tsv_md5=hashlib.md5(("\n".join(tsv) + "\n").encode()).hexdigest(),
+            tsv_rows=len(tsv) - 1,
+            init_len=int(open(os.path.join(td, "sum")).read().splitlines()[1].split("\t")[2]),
+            flags=list(flags),
+        )
+
+
+# the reference's executable tests that pin the path (SURVEY.md §4): directory -> (flags of its runtest, pinned regexes)
+CLI_CASES = {
+    "test_treelength_1": ([], {"score": 1}),
+    "test_treelength_2": ([], {"score": 5}),
+    "test_treelength_2_a1": (["-a1"], {"score": 5}),
+    "test_treelength_2_a2": (["-a2"], {"score": 5}),
+    "test_treelength_3": ([], {"score": 4}),
+    "test_treelength_4": ([], {"score": 9}),
+    "test_treelength_5_thread_2": (["-s", "509739986", "-p", "2"], {"score": 1846}),
+    "test_treelength_6_thread_2": (["-p", "2", "-s", "509739986"], {"score": 1628}),
+    "test_treelength_6_thread_3": (["-p", "3", "-s", "465380177"], {"score": 297}),
+    "test_treelength_7_thread_2": (["-p", "2"], {"score": 1006}),
+    "test_trees_recovered_1": ([], {"topologies": 15}),
+    "test_trees_recovered_2": ([], {"topologies": 3}),
+    "test_trees_recovered_3": ([], {"topologies": 1}),
+    "test_trees_recovered_4": ([], {"topologies": 105}),
+    "test_trees_recovered_6": ([], {"topologies": 1}),
+    "test_trees_recovered_7": ([], {"topologies": 1}),
+}
+
+
+def gen_cli_cases():
+    """Inputs of the reference's own executable tests + what the unmodified reference prints and
+    writes for them; seed-free tests are recorded at seeds 1 and 2 (their pins hold for any seed)."""
+    inputs, runs = {}, {}
+    for d, (flags, pins) in CLI_CASES.items():
+        raw = open(f"{REF}/test/src/COMMON/{d}/infile", "rb").read()
+        inputs[d] = np.frombuffer(raw, dtype=np.uint8)
+        seeded = "-s" in flags
+        for seed in ([None] if seeded else [1, 2]):
+            fl = list(flags) + ([] if seeded else ["-s", str(seed)])
+            r = run_reference_cli(raw, fl)
+            for k, v in pins.items():
+                assert r[k] == v, (d, k, r[k], v)
+            r["pins"] = pins
+            runs[d + ("" if seeded else f"@{seed}")] = r
+            print(d, fl, {k: r[k] for k in ("score", "topologies", "rearrangements", "start_temp")})
+    np.savez_compressed(os.path.join(OUT, "cli_inputs.npz"), **inputs)
+    json.dump(runs, open(os.path.join(OUT, "cli_runs.json"), "w"), indent=1)
+
+
+def gen_config2():
+    """BASELINE.json configs[1]: synthetic 100 x 10k (SURVEY.md appendix A generator), reference run"""
+    sys.path.insert(0, os.path.dirname(OUT.rstrip("/")).rsplit("/tests", 1)[0])
+    from lvb_b200 import synthetic
+
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "c2.phy")
+        synthetic.write_phylip(path, synthetic.survey_alignment(100, 10000, 1, 0.05))
+        raw = open(path, "rb").read()
+    assert hashlib.md5(raw).hexdigest() == "a11fa9393aaf6c6b8150b4491e8a4d90"
+    r = run_reference_cli(raw, ["-s", "12345", "-a", "1", "-p", "1"])
+    r["input_md5"] = hashlib.md5(raw).hexdigest()
+    assert r["score"] == 96403 and r["rearrangements"] == 241917, r
+    runs = json.load(open(os.path.join(OUT, "sa_runs.json")))
+    runs["config2_a1"] = r
+    json.dump(runs, open(os.path.join(OUT, "sa_runs.json"), "w"), indent=1)
+    print("config 2:", {k: v for k, v in r.items() if k not in ("outtree",)})
+
+
+def gen_example_raw():
+    raw = open(EXAMPLE, "rb").read()
+    np.savez_compressed(os.path.join(OUT, "example_phy.npz"), raw=np.frombuffer(raw, dtype=np.uint8))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1:
+        for fn in sys.argv[1:]:
+            globals()[fn]()
+        sys.exit(0)
     assert oracles.have_ref(), "build the reference first: make -C oracle ref"
     gen_example()
     gen_proposals()
     gen_treelength()
     gen_rng()
     gen_sa_runs()
+    gen_example_raw()
+    gen_cli_cases()
+    gen_config2()
