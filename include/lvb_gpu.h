@@ -44,6 +44,13 @@ typedef struct lvb_gpu_topology
     int64_t root;          /* leaf index */
     const int64_t *dirty;  /* internal node numbers, any order; ignored if n_dirty < 0 */
     int64_t n_dirty;       /* < 0: every internal node (what ss_init / lvb_reroot leave) */
+    /* Optional overlay: the tree is left/right with the child links of n_mod nodes replaced.
+     * A proposal then is "the current tree + the handful of links mutate_* rewired" and the
+     * host need not materialise (treecopy, TreeOperations.c:737-773) a tree per proposal. */
+    const int64_t *mod_node;
+    const int64_t *mod_left;
+    const int64_t *mod_right;
+    int64_t n_mod;         /* 0: no overlay */
 } lvb_gpu_topology;
 
 /* ---- device / context:  Main.c:82 lvb_initialize() gains device init ---- */
@@ -114,6 +121,9 @@ int lvb_gpu_comm_unique_id(void *id128);
 int lvb_gpu_comm_init(lvb_gpu_ctx *ctx, int nranks, int rank, const void *id128);
 
 /* ---- introspection for tests and bench ---- */
+/* record CUDA events around the Fitch kernels (needed by lvb_gpu_last_kernel_ms / lvb_gpu_kernel_time;
+ * off by default: two event records per call are not free on the latency-bound SA path) */
+int lvb_gpu_set_timing(lvb_gpu_ctx *ctx, int on);
 /* number of kernel launches issued by this context so far */
 int64_t lvb_gpu_launch_count(lvb_gpu_ctx *ctx);
 /* device time (ms) of the Fitch kernel of the most recent commit/score_batch call, measured

@@ -188,8 +188,20 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
         if (tid == 0)
             s_total += (unsigned long long)p.sum_chg[prog.tree];
     }
-    if (tid == 0 && s_total)
-        atomicAdd(&p.totals[prog_id], s_total);
+    if (tid == 0)
+    {
+        /* the column block that finishes last publishes the length and leaves totals/done zero
+         * for the next batch: no memset before and no copy after the launch */
+        if (s_total)
+            atomicAdd(&p.totals[prog_id], s_total);
+        __threadfence();
+        if (atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u)
+        {
+            __threadfence();
+            p.out[prog_id] = (long long)atomicExch(&p.totals[prog_id], 0ull);
+            p.done[prog_id] = 0u;
+        }
+    }
 }
 
 cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cudaStream_t stream)
@@ -218,7 +230,7 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
 
 /* one CTA per program of a store-mode batch */
 __global__ void __launch_bounds__(128) fitch_commit_finalize_kernel(const FitchInstr *instr, const FitchProgram *progs,
-                                                                    const int32_t *cnts, int32_t *chg,
+                                                                    int32_t *cnts, int32_t *chg,
                                                                     long long *sum_chg, int n, int n_internal,
                                                                     long long *lengths)
 {
@@ -236,6 +248,7 @@ __global__ void __launch_bounds__(128) fitch_commit_finalize_kernel(const FitchI
     {
         const int node = instr[prog.instr_begin + i].node;
         const int c = cnts[prog.instr_begin + i];
+        cnts[prog.instr_begin + i] = 0; /* ready for the next store batch */
         if (node >= 0)
         {
             delta += (long long)c - tchg[node - n];
@@ -263,7 +276,7 @@ __global__ void __launch_bounds__(128) fitch_commit_finalize_kernel(const FitchI
     }
 }
 
-cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, const int32_t *cnts,
+cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
                                    cudaStream_t stream)
 {

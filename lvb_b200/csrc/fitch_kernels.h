@@ -23,8 +23,11 @@ struct ExecParams
     int32_t n_slots;             /* stack slots of the deepest program in the batch */
     const FitchInstr *instr;
     const FitchProgram *prog;
-    unsigned long long *totals;  /* [n_prog] += change counts (and base length in score mode) */
-    int32_t *cnts;               /* [n_instr of batch] per-instruction counts (store mode) */
+    unsigned long long *totals;  /* [n_prog] score mode: partial sums of the column blocks; left zero by the kernel */
+    unsigned *done;              /* [n_prog] score mode: column blocks finished; left zero by the kernel */
+    long long *out;              /* [n_prog] score mode: the length, written by the last column block
+                                  * (pinned host memory mapped into the device, or device memory) */
+    int32_t *cnts;               /* [n_instr of batch] per-instruction counts (store mode); zeroed by finalize */
     const int32_t *chg;          /* [trees][I] cached per-node change counts */
     const long long *sum_chg;    /* [trees] sum of chg over internal nodes */
 };
@@ -35,7 +38,7 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
 
 /* After a store-mode batch: chg[tree][node] <- new count, sum_chg[tree] += delta,
  * lengths[p] <- sum_chg[tree] + root step counts.  Trees of the batch must be distinct. */
-cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, const int32_t *cnts,
+cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
                                    cudaStream_t stream);
 

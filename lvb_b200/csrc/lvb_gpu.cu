@@ -14,6 +14,9 @@
  */
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include <algorithm>
 #include <cstdarg>
@@ -96,12 +99,26 @@ static int nccl_load()
     return 0;
 }
 
+/* One in-flight batch: pinned host staging + its device copy + where the kernels leave the
+ * lengths (pinned, device-mapped: no device-to-host copy is enqueued) */
+struct Staging
+{
+    unsigned char *h = nullptr, *d = nullptr;
+    size_t cap = 0;
+    long long *h_len = nullptr; /* pinned, mapped */
+    long long *d_len = nullptr; /* device alias of h_len */
+    size_t cap_len = 0;
+    cudaEvent_t done = nullptr; /* recorded after the last kernel that reads this slot */
+    bool pending = false;
+};
+
 struct lvb_gpu_ctx
 {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
+    bool timing = false; /* record CUDA events around the Fitch kernels (lvb_gpu_set_timing) */
 
     int64_t n = 0, nwords = 0, word_begin = 0, word_count = 0, B = 0, I = 0;
     int64_t stride_u4 = 0, max_trees = 0;
@@ -109,32 +126,35 @@ struct lvb_gpu_ctx
     int32_t *chg = nullptr;
     long long *sum_chg = nullptr;
     std::vector<uint8_t> tree_used, tree_ready;
-    ScheduleCompiler *sc = nullptr;
+    std::vector<ScheduleCompiler *> sc; /* one per host thread that compiles */
 
     /* batch staging */
-    std::vector<FitchInstr> instr;
-    std::vector<FitchProgram> prog;
-    FitchInstr *d_instr = nullptr, *h_instr = nullptr;
-    size_t cap_instr = 0;
-    FitchProgram *d_prog = nullptr, *h_prog = nullptr; /* pieces, sorted by level */
-    size_t cap_prog = 0;
-    std::vector<FitchProgram> cand;                    /* one entry per candidate (all its pieces) */
-    FitchProgram *d_cand = nullptr, *h_cand = nullptr;
-    size_t cap_cand = 0;
-    std::vector<ScheduleCompiler::Piece> pieces;
+    static const int kRing = 4;
+    Staging ring[kRing];
+    int ring_next = 0;
+    std::vector<std::vector<FitchInstr>> c_instr;              /* per candidate */
+    std::vector<std::vector<ScheduleCompiler::Piece>> c_pieces; /* per candidate */
+    std::vector<int> c_slots;
+    std::vector<std::string> c_err;
+    std::vector<FitchProgram> prog;                    /* pieces, sorted by level */
     std::vector<std::pair<int32_t, int32_t>> levels;   /* (first piece, count) per launch */
     int64_t target_warps = 148 * 384;                  /* resident warps wanted per launch */
-    unsigned long long *d_totals = nullptr;
-    long long *h_totals = nullptr;
-    int32_t *d_cnts = nullptr;
+    unsigned long long *d_totals = nullptr;            /* [cap_tot] per-program sums; zero between batches */
+    unsigned *d_done = nullptr;                        /* [cap_tot] CTAs finished per program; zero between batches */
+    long long *d_lengths = nullptr;                    /* [cap_tot] lengths on the device (site-block mode: all-reduced here) */
+    size_t cap_tot = 0;
+    int32_t *d_cnts = nullptr;                         /* [cap_cnts] per-instruction counts; zero between batches */
+    size_t cap_cnts = 0;
     int block_override = 0;
 
     int64_t launches = 0;
 
-    /* the batch that is resident in d_instr/d_prog (for lvb_gpu_rerun_last_batch) */
+    /* the batch that is resident on the device (for lvb_gpu_rerun_last_batch) */
     int64_t last_K = 0;
     bool last_store = false;
     int last_slots = 0;
+    int last_slot = -1;
+    size_t last_n_instr = 0, last_n_prog = 0;
     /* device time of the Fitch kernel, accumulated over launches (events on the stream) */
     static const int kEvRing = 32;
     cudaEvent_t ring0[kEvRing] = {}, ring1[kEvRing] = {};
@@ -146,59 +166,77 @@ struct lvb_gpu_ctx
     int nranks = 1, rank = 0;
 };
 
-static int ensure_batch_capacity(lvb_gpu_ctx *c, size_t n_instr, size_t n_prog, size_t n_cand)
+static size_t grow(size_t have, size_t need, size_t start)
 {
-    if (n_cand > c->cap_cand)
+    size_t cap = have ? have : start;
+    while (cap < need)
+        cap *= 2;
+    return cap;
+}
+
+/* device arrays indexed by program / instruction: grown with the stream idle, zero-filled */
+static int ensure_device_arrays(lvb_gpu_ctx *c, size_t n_instr, size_t n_cand)
+{
+    if (n_cand > c->cap_tot)
     {
-        size_t cap = c->cap_cand ? c->cap_cand : 256;
-        while (cap < n_cand)
-            cap *= 2;
-        if (c->d_cand)
-        {
-            CU(cudaStreamSynchronize(c->stream));
-            CU(cudaFree(c->d_cand));
-            CU(cudaFree(c->d_totals));
-            CU(cudaFreeHost(c->h_cand));
-            CU(cudaFreeHost(c->h_totals));
-        }
-        CU(cudaMalloc(&c->d_cand, cap * sizeof(FitchProgram)));
+        const size_t cap = grow(c->cap_tot, n_cand, 256);
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_totals);
+        cudaFree(c->d_done);
+        cudaFree(c->d_lengths);
         CU(cudaMalloc(&c->d_totals, cap * sizeof(unsigned long long)));
-        CU(cudaMallocHost(&c->h_cand, cap * sizeof(FitchProgram)));
-        CU(cudaMallocHost(&c->h_totals, cap * sizeof(long long)));
-        c->cap_cand = cap;
+        CU(cudaMalloc(&c->d_done, cap * sizeof(unsigned)));
+        CU(cudaMalloc(&c->d_lengths, cap * sizeof(long long)));
+        CU(cudaMemsetAsync(c->d_totals, 0, cap * sizeof(unsigned long long), c->stream));
+        CU(cudaMemsetAsync(c->d_done, 0, cap * sizeof(unsigned), c->stream));
+        c->cap_tot = cap;
     }
-    if (n_instr > c->cap_instr)
+    if (n_instr > c->cap_cnts)
     {
-        size_t cap = c->cap_instr ? c->cap_instr : 4096;
-        while (cap < n_instr)
-            cap *= 2;
-        if (c->d_instr)
-        {
-            CU(cudaStreamSynchronize(c->stream));
-            CU(cudaFree(c->d_instr));
-            CU(cudaFree(c->d_cnts));
-            CU(cudaFreeHost(c->h_instr));
-        }
-        CU(cudaMalloc(&c->d_instr, cap * sizeof(FitchInstr)));
+        const size_t cap = grow(c->cap_cnts, n_instr, 4096);
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_cnts);
         CU(cudaMalloc(&c->d_cnts, cap * sizeof(int32_t)));
-        CU(cudaMallocHost(&c->h_instr, cap * sizeof(FitchInstr)));
-        c->cap_instr = cap;
+        CU(cudaMemsetAsync(c->d_cnts, 0, cap * sizeof(int32_t), c->stream));
+        c->cap_cnts = cap;
     }
-    if (n_prog > c->cap_prog)
+    return 0;
+}
+
+/* next staging slot, large enough; waits only if the batch that used it 4 calls ago is still running */
+static int acquire_slot(lvb_gpu_ctx *c, size_t bytes, size_t n_cand, int *slot_out)
+{
+    const int slot = c->ring_next;
+    c->ring_next = (c->ring_next + 1) % lvb_gpu_ctx::kRing;
+    Staging &st = c->ring[slot];
+    if (st.pending)
     {
-        size_t cap = c->cap_prog ? c->cap_prog : 256;
-        while (cap < n_prog)
-            cap *= 2;
-        if (c->d_prog)
-        {
-            CU(cudaStreamSynchronize(c->stream));
-            CU(cudaFree(c->d_prog));
-            CU(cudaFreeHost(c->h_prog));
-        }
-        CU(cudaMalloc(&c->d_prog, cap * sizeof(FitchProgram)));
-        CU(cudaMallocHost(&c->h_prog, cap * sizeof(FitchProgram)));
-        c->cap_prog = cap;
+        CU(cudaEventSynchronize(st.done));
+        st.pending = false;
     }
+    if (bytes > st.cap)
+    {
+        const size_t cap = grow(st.cap, bytes, 64 << 10);
+        if (st.h)
+            CU(cudaFreeHost(st.h));
+        if (st.d)
+            CU(cudaFree(st.d));
+        CU(cudaMallocHost(&st.h, cap));
+        CU(cudaMalloc(&st.d, cap));
+        st.cap = cap;
+    }
+    if (n_cand > st.cap_len)
+    {
+        const size_t cap = grow(st.cap_len, n_cand, 256);
+        if (st.h_len)
+            CU(cudaFreeHost(st.h_len));
+        CU(cudaHostAlloc(&st.h_len, cap * sizeof(long long), cudaHostAllocMapped));
+        CU(cudaHostGetDevicePointer(&st.d_len, st.h_len, 0));
+        st.cap_len = cap;
+    }
+    if (!st.done)
+        CU(cudaEventCreateWithFlags(&st.done, cudaEventDisableTiming));
+    *slot_out = slot;
     return 0;
 }
 
@@ -228,14 +266,18 @@ static int drain_kernel_events(lvb_gpu_ctx *c)
     return 0;
 }
 
-/* launch the batch that is resident in d_instr/d_prog */
+/* launch the batch that is resident in staging slot c->last_slot */
 static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
 {
     const int64_t K = c->last_K;
     const bool store = c->last_store;
-    CU(cudaMemsetAsync(c->d_totals, 0, K * sizeof(unsigned long long), c->stream));
-    if (store)
-        CU(cudaMemsetAsync(c->d_cnts, 0, c->instr.size() * sizeof(int32_t), c->stream));
+    Staging &st = c->ring[c->last_slot];
+    const FitchProgram *d_prog = reinterpret_cast<const FitchProgram *>(st.d);
+    const FitchProgram *d_cand = d_prog + c->last_n_prog;
+    const FitchInstr *d_instr = reinterpret_cast<const FitchInstr *>(d_cand + K);
+    /* where the lengths go: straight to pinned host memory, or to the device when they still
+     * have to be summed over the ranks */
+    long long *out = c->comm ? c->d_lengths : st.d_len;
 
     ExecParams p;
     p.pool = c->pool;
@@ -246,48 +288,61 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     const int block = pick_block(c);
     p.n_colblocks = (int32_t)((c->stride_u4 + block - 1) / block);
     p.n_slots = c->last_slots;
-    p.instr = c->d_instr;
+    p.instr = d_instr;
     p.totals = c->d_totals;
+    p.done = c->d_done;
+    p.out = out;
     p.cnts = c->d_cnts;
     p.chg = c->chg;
     p.sum_chg = c->sum_chg;
 
-    if (c->ring_used == lvb_gpu_ctx::kEvRing && drain_kernel_events(c))
-        return 1;
-    const int slot = c->ring_used++;
-    CU(cudaEventRecord(c->ring0[slot], c->stream));
+    int slot = -1;
+    if (c->timing)
+    {
+        if (c->ring_used == lvb_gpu_ctx::kEvRing && drain_kernel_events(c))
+            return 1;
+        slot = c->ring_used++;
+        CU(cudaEventRecord(c->ring0[slot], c->stream));
+    }
     /* one launch per dependency level: pieces of a level only read rows stored by earlier levels */
     for (const auto &lv : c->levels)
     {
-        p.prog = c->d_prog + lv.first;
+        p.prog = d_prog + lv.first;
         p.n_prog = lv.second;
         if ((int64_t)p.n_prog * p.n_colblocks > (int64_t)INT32_MAX)
             return fail("batch too large: %lld CTAs", (long long)p.n_prog * p.n_colblocks);
         CU(launch_fitch_exec(p, store, block, c->stream));
         c->launches++;
     }
-    CU(cudaEventRecord(c->ring1[slot], c->stream));
-    c->ev0 = c->ring0[slot];
-    c->ev1 = c->ring1[slot];
-    c->timed = true;
+    if (c->timing)
+    {
+        CU(cudaEventRecord(c->ring1[slot], c->stream));
+        c->ev0 = c->ring0[slot];
+        c->ev1 = c->ring1[slot];
+        c->timed = true;
+    }
     if (store)
     {
-        CU(launch_commit_finalize(c->d_instr, c->d_cand, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
-                                  (long long *)c->d_totals, c->stream));
+        CU(launch_commit_finalize(d_instr, d_cand, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I, out,
+                                  c->stream));
         c->launches++;
     }
     if (c->comm && (lengths || !store))
     {
-        int r = g_nccl.AllReduce(c->d_totals, c->d_totals, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
+        int r = g_nccl.AllReduce(c->d_lengths, c->d_lengths, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
         if (r != 0)
             return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+        if (lengths)
+            CU(cudaMemcpyAsync(st.h_len, c->d_lengths, K * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
     }
+    CU(cudaEventRecord(st.done, c->stream));
+    st.pending = true;
     if (lengths)
     {
-        CU(cudaMemcpyAsync(c->h_totals, c->d_totals, K * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaEventSynchronize(st.done));
+        st.pending = false;
         for (int64_t k = 0; k < K; k++)
-            lengths[k] = (int64_t)c->h_totals[k];
+            lengths[k] = (int64_t)st.h_len[k];
     }
     return 0;
 }
@@ -302,17 +357,10 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         return 0;
     CU(cudaSetDevice(c->device));
     c->last_K = 0;
-    c->instr.clear();
-    c->prog.clear();
-    c->cand.clear();
-    c->levels.clear();
-    int n_slots = 0;
-    std::string err;
     /* Large store programs are cut into independent subtrees so that enough warps are resident:
      * a program owns ceil(cols/32) warps per piece. */
     const int64_t warps_per_piece = (c->stride_u4 + 31) / 32;
     const int64_t want_pieces = store ? std::max<int64_t>(1, c->target_warps / (warps_per_piece * K)) : 1;
-    std::vector<std::pair<int32_t, int32_t>> piece_of; /* (level, index into c->prog) */
     for (int64_t k = 0; k < K; k++)
     {
         const int t = trees[k];
@@ -322,33 +370,6 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
             return fail("candidate %lld: tree %d has never been evaluated (commit it first)", (long long)k, t);
         if (store && !c->tree_ready[t] && topos[k].n_dirty >= 0)
             return fail("tree %d: first commit must recompute every internal node (n_dirty < 0)", t);
-        const size_t begin = c->instr.size();
-        int slots = 0, piece_size = 0;
-        if (want_pieces > 1)
-        {
-            const int64_t d = topos[k].n_dirty < 0 ? c->I : topos[k].n_dirty;
-            if (d >= 64) /* not worth a second launch for short programs */
-                piece_size = (int)std::max<int64_t>(4, (d + want_pieces - 1) / want_pieces);
-        }
-        c->pieces.clear();
-        if (!c->sc->compile(topos[k], store, c->instr, slots, err, piece_size, &c->pieces))
-            return fail("candidate %lld: %s", (long long)k, err.c_str());
-        if (slots > n_slots)
-            n_slots = slots;
-        for (const auto &pc : c->pieces)
-            c->prog.push_back(FitchProgram{pc.instr_begin, pc.n_instr, t, pc.level});
-        c->cand.push_back(FitchProgram{(int32_t)begin, (int32_t)(c->instr.size() - begin), t, store ? 1 : 0});
-    }
-    /* pieces sorted by level; one launch per level */
-    std::stable_sort(c->prog.begin(), c->prog.end(),
-                     [](const FitchProgram &a, const FitchProgram &b) { return a.flags < b.flags; });
-    for (size_t i = 0; i < c->prog.size();)
-    {
-        size_t j = i;
-        while (j < c->prog.size() && c->prog[j].flags == c->prog[i].flags)
-            j++;
-        c->levels.push_back({(int32_t)i, (int32_t)(j - i)});
-        i = j;
     }
     if (store)
     { /* in-place commits of one tree must not share a launch */
@@ -360,27 +381,116 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
             seen[trees[k]] = 1;
         }
     }
-    if (c->instr.size() > (size_t)INT32_MAX)
-        return fail("batch too large: %zu instructions", c->instr.size());
-    if (ensure_batch_capacity(c, c->instr.size(), c->prog.size(), c->cand.size()))
+    if ((size_t)K > c->c_instr.size())
+    {
+        c->c_instr.resize((size_t)K);
+        c->c_pieces.resize((size_t)K);
+        c->c_slots.resize((size_t)K);
+        c->c_err.resize((size_t)K);
+    }
+    /* host compile, one candidate at a time; spread over host threads when the batch is large */
+    int nthreads = 1;
+#ifdef _OPENMP
+    if (K >= 64)
+        nthreads = std::min<int>({(int)c->sc.size(), omp_get_max_threads(), (int)(K / 16)});
+#endif
+    bool bad = false;
+    auto compile_one = [&](int64_t k, ScheduleCompiler *sc) {
+        int piece_size = 0;
+        if (want_pieces > 1)
+        {
+            const int64_t d = topos[k].n_dirty < 0 ? c->I : topos[k].n_dirty;
+            if (d >= 64) /* not worth a second launch for short programs */
+                piece_size = (int)std::max<int64_t>(4, (d + want_pieces - 1) / want_pieces);
+        }
+        c->c_instr[k].clear();
+        c->c_pieces[k].clear();
+        c->c_err[k].clear();
+        int slots = 0;
+        if (!sc->compile(topos[k], store, c->c_instr[k], slots, c->c_err[k], piece_size, &c->c_pieces[k]))
+            bad = true;
+        c->c_slots[k] = slots;
+    };
+    if (nthreads > 1)
+    {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+        for (int64_t k = 0; k < K; k++)
+            compile_one(k, c->sc[omp_get_thread_num()]);
+#endif
+    }
+    else
+        for (int64_t k = 0; k < K; k++)
+            compile_one(k, c->sc[0]);
+    if (bad)
+        for (int64_t k = 0; k < K; k++)
+            if (!c->c_err[k].empty())
+                return fail("candidate %lld: %s", (long long)k, c->c_err[k].c_str());
+
+    /* lay the batch out: [pieces sorted by level][one record per candidate][instructions] */
+    size_t n_instr = 0, n_prog = 0;
+    int n_slots = 0;
+    bool multilevel = false;
+    for (int64_t k = 0; k < K; k++)
+    {
+        n_instr += c->c_instr[k].size();
+        n_prog += c->c_pieces[k].size();
+        n_slots = std::max(n_slots, c->c_slots[k]);
+    }
+    if (n_instr > (size_t)INT32_MAX)
+        return fail("batch too large: %zu instructions", n_instr);
+    if (ensure_device_arrays(c, n_instr, (size_t)K))
         return 1;
-    /* a previous asynchronous batch may still be reading the pinned staging buffers */
-    CU(cudaStreamSynchronize(c->stream));
-    memcpy(c->h_instr, c->instr.data(), c->instr.size() * sizeof(FitchInstr));
-    memcpy(c->h_prog, c->prog.data(), c->prog.size() * sizeof(FitchProgram));
-    memcpy(c->h_cand, c->cand.data(), c->cand.size() * sizeof(FitchProgram));
-    CU(cudaMemcpyAsync(c->d_instr, c->h_instr, c->instr.size() * sizeof(FitchInstr), cudaMemcpyHostToDevice,
-                       c->stream));
-    CU(cudaMemcpyAsync(c->d_prog, c->h_prog, c->prog.size() * sizeof(FitchProgram), cudaMemcpyHostToDevice,
-                       c->stream));
-    CU(cudaMemcpyAsync(c->d_cand, c->h_cand, c->cand.size() * sizeof(FitchProgram), cudaMemcpyHostToDevice,
-                       c->stream));
+    const size_t bytes = (n_prog + (size_t)K) * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr);
+    int slot;
+    if (acquire_slot(c, bytes, (size_t)K, &slot))
+        return 1;
+    Staging &st = c->ring[slot];
+    FitchProgram *h_prog = reinterpret_cast<FitchProgram *>(st.h);
+    FitchProgram *h_cand = h_prog + n_prog;
+    FitchInstr *h_instr = reinterpret_cast<FitchInstr *>(h_cand + K);
+    c->prog.clear();
+    size_t off = 0;
+    for (int64_t k = 0; k < K; k++)
+    {
+        const auto &ins = c->c_instr[k];
+        memcpy(h_instr + off, ins.data(), ins.size() * sizeof(FitchInstr));
+        for (const auto &pc : c->c_pieces[k])
+        {
+            c->prog.push_back(FitchProgram{(int32_t)(off + pc.instr_begin), pc.n_instr, trees[k], pc.level});
+            multilevel = multilevel || pc.level != 0;
+        }
+        h_cand[k] = FitchProgram{(int32_t)off, (int32_t)ins.size(), trees[k], store ? 1 : 0};
+        off += ins.size();
+    }
+    /* pieces sorted by level; one launch per level */
+    c->levels.clear();
+    if (multilevel)
+    {
+        std::stable_sort(c->prog.begin(), c->prog.end(),
+                         [](const FitchProgram &a, const FitchProgram &b) { return a.flags < b.flags; });
+        for (size_t i = 0; i < c->prog.size();)
+        {
+            size_t j = i;
+            while (j < c->prog.size() && c->prog[j].flags == c->prog[i].flags)
+                j++;
+            c->levels.push_back({(int32_t)i, (int32_t)(j - i)});
+            i = j;
+        }
+    }
+    else
+        c->levels.push_back({0, (int32_t)c->prog.size()});
+    memcpy(h_prog, c->prog.data(), c->prog.size() * sizeof(FitchProgram));
+    CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
     if (store)
         for (int64_t k = 0; k < K; k++)
             c->tree_ready[trees[k]] = 1;
     c->last_K = K;
     c->last_store = store;
     c->last_slots = n_slots;
+    c->last_slot = slot;
+    c->last_n_instr = n_instr;
+    c->last_n_prog = n_prog;
     return launch_resident(c, lengths);
 }
 
@@ -392,8 +502,9 @@ static void free_matrix(lvb_gpu_ctx *c)
     c->pool = nullptr;
     c->chg = nullptr;
     c->sum_chg = nullptr;
-    delete c->sc;
-    c->sc = nullptr;
+    for (auto *s : c->sc)
+        delete s;
+    c->sc.clear();
 }
 
 static int alloc_matrix(lvb_gpu_ctx *c, int64_t n, int64_t nwords, int64_t word_begin, int64_t word_count,
@@ -433,7 +544,12 @@ static int alloc_matrix(lvb_gpu_ctx *c, int64_t n, int64_t nwords, int64_t word_
     CU(cudaMemsetAsync(c->sum_chg, 0, (size_t)max_trees * sizeof(long long), c->stream));
     c->tree_used.assign(max_trees, 0);
     c->tree_ready.assign(max_trees, 0);
-    c->sc = new ScheduleCompiler(n);
+    int nsc = 1;
+#ifdef _OPENMP
+    nsc = std::max(1, std::min(16, omp_get_max_threads()));
+#endif
+    for (int i = 0; i < nsc; i++)
+        c->sc.push_back(new ScheduleCompiler(n));
     return 0;
 }
 
@@ -526,15 +642,18 @@ extern "C"
         if (c->comm && g_nccl.CommDestroy)
             g_nccl.CommDestroy(c->comm);
         free_matrix(c);
-        cudaFree(c->d_instr);
         cudaFree(c->d_cnts);
-        cudaFree(c->d_prog);
-        cudaFree(c->d_cand);
-        cudaFreeHost(c->h_cand);
         cudaFree(c->d_totals);
-        cudaFreeHost(c->h_instr);
-        cudaFreeHost(c->h_prog);
-        cudaFreeHost(c->h_totals);
+        cudaFree(c->d_done);
+        cudaFree(c->d_lengths);
+        for (auto &st : c->ring)
+        {
+            cudaFreeHost(st.h);
+            cudaFree(st.d);
+            cudaFreeHost(st.h_len);
+            if (st.done)
+                cudaEventDestroy(st.done);
+        }
         for (int i = 0; i < lvb_gpu_ctx::kEvRing; i++)
         {
             cudaEventDestroy(c->ring0[i]);
@@ -779,12 +898,20 @@ extern "C"
 
     int64_t lvb_gpu_launch_count(lvb_gpu_ctx *c) { return c ? c->launches : 0; }
 
+    int lvb_gpu_set_timing(lvb_gpu_ctx *c, int on)
+    {
+        if (!c)
+            return fail("lvb_gpu_set_timing: null argument");
+        c->timing = on != 0;
+        return 0;
+    }
+
     int lvb_gpu_last_kernel_ms(lvb_gpu_ctx *c, float *ms)
     {
         if (!c || !ms)
             return fail("lvb_gpu_last_kernel_ms: null argument");
         if (!c->timed)
-            return fail("no Fitch kernel has been launched yet");
+            return fail("no Fitch kernel has been timed yet (lvb_gpu_set_timing)");
         CU(cudaEventSynchronize(c->ev1));
         CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
         return 0;
@@ -825,6 +952,12 @@ extern "C"
         if (c->last_K <= 0)
             return fail("no batch is resident on the device");
         CU(cudaSetDevice(c->device));
+        Staging &st = c->ring[c->last_slot];
+        if (st.pending)
+        {
+            CU(cudaEventSynchronize(st.done));
+            st.pending = false;
+        }
         return launch_resident(c, lengths);
     }
 

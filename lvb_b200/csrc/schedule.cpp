@@ -13,7 +13,8 @@ static inline int64_t strided(const int64_t *base, int64_t stride_bytes, int64_t
 
 ScheduleCompiler::ScheduleCompiler(int64_t n)
     : n_(n), B_(2 * n - 3), cur_(0), stamp_(B_ > 0 ? B_ : 0, 0), child_(stamp_.size(), 0), seen_(stamp_.size(), 0),
-      cut_(stamp_.size(), 0), need_(stamp_.size(), 0), size_(stamp_.size(), 0), level_(stamp_.size(), 0)
+      cut_(stamp_.size(), 0), need_(stamp_.size(), 0), size_(stamp_.size(), 0), level_(stamp_.size(), 0),
+      mod_(stamp_.size(), 0), mod_at_(stamp_.size(), 0)
 {
 }
 
@@ -36,6 +37,7 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
         std::fill(child_.begin(), child_.end(), 0u);
         std::fill(seen_.begin(), seen_.end(), 0u);
         std::fill(cut_.begin(), cut_.end(), 0u);
+        std::fill(mod_.begin(), mod_.end(), 0u);
         cur_ = 1;
     }
     const int64_t root = topo.root;
@@ -44,8 +46,20 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
         err = "schedule: root " + std::to_string(root) + " is not a leaf";
         return false;
     }
-    auto L = [&](int64_t v) { return strided(topo.left, topo.stride_bytes, v); };
-    auto R = [&](int64_t v) { return strided(topo.right, topo.stride_bytes, v); };
+    /* child links: the overlay wins over the base arrays */
+    for (int64_t i = 0; i < topo.n_mod; i++)
+    {
+        const int64_t v = topo.mod_node[i];
+        if (v < 0 || v >= B_)
+        {
+            err = "schedule: overlay names node " + std::to_string(v);
+            return false;
+        }
+        mod_[v] = cur_;
+        mod_at_[v] = (int32_t)i;
+    }
+    auto L = [&](int64_t v) { return mod_[v] == cur_ ? topo.mod_left[mod_at_[v]] : strided(topo.left, topo.stride_bytes, v); };
+    auto R = [&](int64_t v) { return mod_[v] == cur_ ? topo.mod_right[mod_at_[v]] : strided(topo.right, topo.stride_bytes, v); };
 
     /* the dirty set, de-duplicated */
     dirty_.clear();

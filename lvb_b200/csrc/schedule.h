@@ -61,6 +61,8 @@ class ScheduleCompiler
     std::vector<uint32_t> child_;   /* "is a child of a dirty node" marks */
     std::vector<uint32_t> seen_;    /* visited marks (cycle / duplicate guard) */
     std::vector<uint32_t> cut_;     /* "is the root of a piece of its own" marks */
+    std::vector<uint32_t> mod_;     /* "child links come from the overlay" marks */
+    std::vector<int32_t> mod_at_;   /* index into the overlay arrays */
     std::vector<int32_t> need_;     /* stack need per dirty node */
     std::vector<int32_t> size_;     /* nodes of the piece hanging under a dirty node */
     std::vector<int32_t> level_;    /* level of the piece a dirty node belongs to */

@@ -27,6 +27,10 @@ class _Topo(C.Structure):
         ("root", C.c_int64),
         ("dirty", C.c_void_p),
         ("n_dirty", C.c_int64),
+        ("mod_node", C.c_void_p),
+        ("mod_left", C.c_void_p),
+        ("mod_right", C.c_void_p),
+        ("n_mod", C.c_int64),
     ]
 
 
@@ -64,6 +68,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_tree_changes.argtypes = [vp, C.c_int, vp]
     lib.lvb_gpu_comm_unique_id.argtypes = [vp]
     lib.lvb_gpu_comm_init.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.lvb_gpu_set_timing.argtypes = [vp, C.c_int]
     lib.lvb_gpu_launch_count.restype = i64
     lib.lvb_gpu_launch_count.argtypes = [vp]
     lib.lvb_gpu_last_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -88,10 +93,12 @@ class Topology:
     ``dirty`` is None for "every internal node".  Arrays are kept alive by this object.
     """
 
-    def __init__(self, left, right, root: int, dirty: Optional[Iterable[int]] = None):
+    def __init__(self, left, right, root: int, dirty: Optional[Iterable[int]] = None, overlay=None):
         self.left = np.ascontiguousarray(left, dtype=np.int64)
         self.right = np.ascontiguousarray(right, dtype=np.int64)
         self.root = int(root)
+        # overlay = (nodes, lefts, rights): child links that replace those of left/right
+        self.overlay = None if overlay is None else tuple(np.ascontiguousarray(a, dtype=np.int64) for a in overlay)
         self.dirty = None if dirty is None else np.ascontiguousarray(list(dirty) if not isinstance(dirty, np.ndarray) else dirty, dtype=np.int64)
 
     def fill(self, t: _Topo) -> None:
@@ -105,6 +112,12 @@ class Topology:
         else:
             t.dirty = self.dirty.ctypes.data if self.dirty.size else None
             t.n_dirty = int(self.dirty.size)
+        if self.overlay is None or self.overlay[0].size == 0:
+            t.mod_node = t.mod_left = t.mod_right = None
+            t.n_mod = 0
+        else:
+            t.mod_node, t.mod_left, t.mod_right = (a.ctypes.data for a in self.overlay)
+            t.n_mod = int(self.overlay[0].size)
 
     def as_struct(self) -> _Topo:
         t = _Topo()
@@ -144,6 +157,7 @@ class Engine:
         self.lib = load_library()
         self.ctx = C.c_void_p()
         _check(self.lib.lvb_gpu_init(device, C.byref(self.ctx)))
+        _check(self.lib.lvb_gpu_set_timing(self.ctx, 1))  # tests and bench read kernel times
         self.n = self.nwords = self.word_count = 0
 
     def close(self) -> None:

@@ -109,7 +109,7 @@ long getplen(Dataptr MSA, TREESTACK_TREE_NODES *tree, const Parameters &rc, long
     }
     if (fresh && !all)
         all = true;
-    lvb_gpu_topology tp;
+    lvb_gpu_topology tp = lvb_gpu_topology();
     tp.left = &tree[0].left;
     tp.right = &tree[0].right;
     tp.stride_bytes = (int64_t)sizeof(TREESTACK_TREE_NODES);

@@ -155,6 +155,26 @@ void PullRandomTree(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *tree);         
 void SwapTrees(TREESTACK_TREE_NODES **t1, long *r1, TREESTACK_TREE_NODES **t2, long *r2); /* :1062-1080 */
 void ss_init(Dataptr MSA, TREESTACK_TREE_NODES *tree);                                    /* :1500-1513 (flags only; leaf rows live on the device) */
 void lvb_treeprint(Dataptr MSA, FILE *stream, const TREESTACK_TREE_NODES *tree, long root); /* :1144-1220 */
+/* ---- proposals without treecopy (additions of this build; see tree.cpp:propose) ---- */
+struct Proposal
+{
+    int op = 0;                                  /* 0 NNI, 1 SPR, 2 TBR */
+    std::vector<long> node;                      /* nodes the operator touched */
+    std::vector<TREESTACK_TREE_NODES> after;     /* their records in the proposed tree */
+    std::vector<int64_t> dirty;                  /* internal nodes to recompute (flag 0 in the proposed tree) */
+    std::vector<int64_t> mod_node, mod_left, mod_right; /* child links that differ from the current tree */
+};
+struct ProposalScratch
+{
+    std::vector<uint32_t> stamp;
+    uint32_t cur = 0;
+    std::vector<long> node;
+    std::vector<TREESTACK_TREE_NODES> before;
+    std::vector<Lvb_bit_length> flag_before;
+};
+void propose(Dataptr MSA, Uni &rng, int op, TREESTACK_TREE_NODES *current, long root, ProposalScratch &scratch,
+             Proposal &out);
+void apply_proposal(TREESTACK_TREE_NODES *current, const Proposal &p);
 /* internal nodes whose flag word is 0 (the first loop of getplen, src/TreeEvaluation.c:191-202) */
 void collect_dirty(const Dataptr MSA, const TREESTACK_TREE_NODES *tree, std::vector<int64_t> &out);
 void mark_all_clean(Dataptr MSA, TREESTACK_TREE_NODES *tree);
@@ -226,6 +246,8 @@ struct SearchResult
     long getplen_calls = 0;   /* trees scored (proposals + initial passes) */
     long launches_scored = 0; /* score launches */
     double seconds = 0;
+    double prof[4] = {0, 0, 0, 0}; /* seconds in: proposal generation, commit calls, score calls, acceptance replay */
+    long rounds = 0;
 };
 struct Chain; /* one SA replicate: solve.cpp */
 

@@ -215,6 +215,8 @@ int main(int argc, char **argv)
                results[(size_t)r].final_length, (long)stacks[(size_t)r].next, results[(size_t)r].rearrangements);
     printf("  Wall time of the search:  %.3lf s; trees scored: %ld in %ld launches; kernel launches: %ld\n",
            results[0].seconds, results[0].getplen_calls, results[0].launches_scored, (long)dev.launches());
+    printf("  Host time split (s):      propose %.3f, commit calls %.3f, score calls %.3f, replay %.3f; %ld rounds\n",
+           results[0].prof[0], results[0].prof[1], results[0].prof[2], results[0].prof[3], results[0].rounds);
     printf("\nAll topologies written to '%s'\n", rc.file_name_out.c_str());
     device_close(dev);
     return fflush(stdout) == 0 ? EXIT_SUCCESS : EXIT_FAILURE;

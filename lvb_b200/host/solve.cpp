@@ -26,6 +26,7 @@
 #include <cfloat>
 #include <chrono>
 #include <cmath>
+#include <algorithm>
 #include <cstring>
 
 #include "lvb_host.h"
@@ -92,11 +93,14 @@ struct SAState
     int acc_pos_trans = 0, prop_pos_trans = 0;
 };
 
+/* What the device tree of a chain still has to be told before the next proposals are scored:
+ * the rows to recompute, on the chain's current topology at flush time.  An acceptance, a
+ * re-root and both together collapse into one request (the union of their dirty sets is
+ * closed towards the root and covers every node whose subtree changed); a fresh random tree
+ * replaces whatever was pending. */
 struct CommitReq
 {
-    std::vector<TREESTACK_TREE_NODES> topo; /* snapshot: left/right are read from here */
     std::vector<int64_t> dirty;
-    long root = 0;
     bool all = false;         /* every internal node */
     bool want_length = false; /* the chain waits for the length of this commit */
     bool used = false;
@@ -130,22 +134,16 @@ struct Chain
         bool row_valid;
         TrajectoryRow row; /* log line if rejected (length filled in at replay) */
     };
-    std::vector<TREESTACK_TREE_NODES *> cand;
-    std::vector<std::vector<int64_t>> cand_dirty;
+    std::vector<Proposal> cand;
+    ProposalScratch scratch;
     std::vector<Spec> spec;
     int n_spec = 0;
     SAState spec_end;
-    CommitReq commits[3];
-    int n_commits = 0;
+    CommitReq commit;
 
     SearchResult res;
 
-    ~Chain()
-    {
-        free(cur);
-        for (auto *c : cand)
-            free(c);
-    }
+    ~Chain() { free(cur); }
 
     void init(Dataptr msa, const Parameters &prm, int chain_id, int device_tree, int kmax_)
     {
@@ -157,9 +155,6 @@ struct Chain
         k_now = prm.speculation > 0 ? kmax : 1;
         cur = treealloc(MSA, true);
         cand.resize((size_t)kmax);
-        for (auto &c : cand)
-            c = treealloc(MSA, true);
-        cand_dirty.resize((size_t)kmax);
         spec.resize((size_t)kmax);
         S.rng.rinit(rc.seed + chain_id); /* Main.c:104 */
         tree_minimum_length = (double)MSA->min_len_tree;
@@ -167,20 +162,12 @@ struct Chain
         log_grad_geom = log_wrapper(0.99);
     }
 
-    CommitReq &new_commit()
+    template <class It>
+    void request_rows(It first, It last)
     {
-        lvb_assert(n_commits < 3);
-        CommitReq &c = commits[n_commits++];
-        c.used = true;
-        c.all = false;
-        c.want_length = false;
-        c.dirty.clear();
-        return c;
-    }
-    void snapshot(CommitReq &c, const TREESTACK_TREE_NODES *tree, long r)
-    {
-        c.topo.assign(tree, tree + MSA->numberofpossiblebranches);
-        c.root = r;
+        commit.used = true;
+        if (!commit.all)
+            commit.dirty.insert(commit.dirty.end(), first, last);
     }
 
     /* a new random start: PullRandomTree + ss_init (Solve.c:537-538, 543-544), all rows to compute */
@@ -189,10 +176,10 @@ struct Chain
         PullRandomTree(MSA, S.rng, cur);
         ss_init(MSA, cur);
         root = 0;
-        CommitReq &c = new_commit();
-        snapshot(c, cur, root);
-        c.all = true;
-        c.want_length = true;
+        commit.used = true;
+        commit.all = true;
+        commit.want_length = true;
+        commit.dirty.clear();
         await_len = true;
         mark_all_clean(MSA, cur);
         res.getplen_calls++;
@@ -206,14 +193,12 @@ struct Chain
         std::vector<long> path;
         root = arbreroot(MSA, S.rng, cur, root, &path);
         mark_all_clean(MSA, cur);
-        CommitReq &c = new_commit();
-        snapshot(c, cur, root);
-        c.dirty.assign(path.begin(), path.end());
+        request_rows(path.begin(), path.end());
     }
 
     /* ---- the part of an Anneal iteration before getplen (Solve.c:237-298), without the
      * re-root: operator choice and mutate.  Returns the operator. ---- */
-    int anneal_propose(SAState &W, TREESTACK_TREE_NODES *dst)
+    int anneal_propose(SAState &W, Proposal &dst)
     {
         lvb_assert(W.t > DBL_EPSILON);
         const int a = rc.algorithm_selection;
@@ -238,12 +223,7 @@ struct Chain
         }
         else
             op = (W.iter & 1) ? 1 : 0;
-        if (op == 0)
-            mutate_nni(MSA, W.rng, dst, cur, root);
-        else if (op == 1)
-            mutate_spr(MSA, W.rng, dst, cur, root);
-        else
-            mutate_tbr(MSA, W.rng, dst, cur, root);
+        propose(MSA, W.rng, op, cur, root, scratch, dst); /* mutate_nni / _spr / _tbr, in place and undone */
         W.op = op;
         return op;
     }
@@ -499,19 +479,15 @@ struct Chain
                     break;
             }
             Spec &sp = spec[(size_t)n_spec];
-            TREESTACK_TREE_NODES *dst = cand[(size_t)n_spec];
+            Proposal &dst = cand[(size_t)n_spec];
             if (annealing)
                 anneal_propose(W, dst);
             else
             {
                 lvb_assert(W.t > DBL_EPSILON);
                 W.op = (W.st_iter & 1) ? 1 : 0; /* StartingTemperature.c:123-126 */
-                if (W.op)
-                    mutate_spr(MSA, W.rng, dst, cur, root);
-                else
-                    mutate_nni(MSA, W.rng, dst, cur, root);
+                propose(MSA, W.rng, W.op, cur, root, scratch, dst);
             }
-            collect_dirty(MSA, dst, cand_dirty[(size_t)n_spec]);
             sp.mid = W;
             sp.u = W.rng.uni();
             sp.row_valid = false;
@@ -553,7 +529,6 @@ struct Chain
                     fprintf(sumfp, "%d\t%d\t%ld\t", 0, 0, current_len); /* Solve.c:558-559 */
             }
         }
-        n_commits = 0;
         if (n_spec == 0)
             return;
         const bool annealing = S.phase == PH_AN_LOOP;
@@ -578,11 +553,14 @@ struct Chain
             S = sp.mid;
             if (out == ACCEPT_WORSE)
                 (void)S.rng.uni();
+            /* SwapTrees (Solve.c:323, 370): the proposal becomes the current tree; on the device
+             * only its dirty rows are rewritten */
+            apply_proposal(cur, cand[(size_t)k]);
             bool go_on;
             if (annealing)
             {
                 TrajectoryRow row;
-                go_on = anneal_after(S, out, len, cand[(size_t)k], true, &row);
+                go_on = anneal_after(S, out, len, cur, true, &row);
                 if (go_on)
                     emit(row);
                 else
@@ -594,16 +572,8 @@ struct Chain
                 if (!go_on)
                     S.phase = PH_AN_BEGIN;
             }
-            /* SwapTrees (Solve.c:323, 370): the proposal becomes the current tree; on the device
-             * only its dirty rows are rewritten */
-            treecopy(MSA, cur, cand[(size_t)k], true);
-            mark_all_clean(MSA, cur);
             if (go_on)
-            {
-                CommitReq &c = new_commit();
-                snapshot(c, cur, root);
-                c.dirty = cand_dirty[(size_t)k];
-            }
+                request_rows(cand[(size_t)k].dirty.begin(), cand[(size_t)k].dirty.end());
             break;
         }
         if (taken < 0)
@@ -660,53 +630,82 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
     std::vector<lvb_gpu_topology> topos;
     std::vector<int64_t> lens, clen((size_t)R, 0);
     std::vector<int> owner;
+    std::vector<size_t> offsets;
+    const int host_threads = std::max(1, std::min(R, rc.n_processors_available));
     long score_launches = 0;
     const size_t stride = sizeof(TREESTACK_TREE_NODES);
+    double prof[4] = {0, 0, 0, 0};
+    long rounds = 0;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto since = [](std::chrono::steady_clock::time_point a) {
+        return std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
+    };
     for (;;)
     {
         bool alive = false;
-        for (auto &c : chains)
+        auto tp0 = now();
+        /* chains are independent between device calls: spread them over the host threads (-p) */
+        std::string failure;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(host_threads) if (host_threads > 1)
+        for (int r = 0; r < R; r++)
         {
-            c.advance();
-            alive = alive || c.S.phase != PH_DONE;
-        }
-        /* commits, in waves so that no tree appears twice in one launch */
-        for (int wave = 0; wave < 3; wave++)
-        {
-            trees.clear();
-            topos.clear();
-            owner.clear();
-            bool want = false;
-            for (int r = 0; r < R; r++)
+            try
             {
-                Chain &c = chains[(size_t)r];
-                if (wave >= c.n_commits)
-                    continue;
-                const CommitReq &q = c.commits[wave];
-                lvb_gpu_topology tp;
-                tp.left = &q.topo[0].left;
-                tp.right = &q.topo[0].right;
-                tp.stride_bytes = (int64_t)stride;
-                tp.root = q.root;
-                tp.dirty = q.dirty.data();
-                tp.n_dirty = q.all ? -1 : (int64_t)q.dirty.size();
-                trees.push_back(c.dev_tree);
-                topos.push_back(tp);
-                owner.push_back(r);
-                want = want || q.want_length;
+                chains[(size_t)r].advance();
             }
-            if (trees.empty())
-                break;
+            catch (const LvbError &e)
+            {
+#pragma omp critical
+                failure = e.message;
+            }
+        }
+        if (!failure.empty())
+            crash("%s", failure.c_str());
+        for (auto &c : chains)
+            alive = alive || c.S.phase != PH_DONE;
+        prof[0] += since(tp0);
+        rounds++;
+        tp0 = now();
+        /* what the device trees must catch up with (at most one request per chain), one launch */
+        trees.clear();
+        topos.clear();
+        owner.clear();
+        bool want = false;
+        for (int r = 0; r < R; r++)
+        {
+            Chain &c = chains[(size_t)r];
+            if (!c.commit.used)
+                continue;
+            lvb_gpu_topology tp = lvb_gpu_topology();
+            tp.left = &c.cur[0].left;
+            tp.right = &c.cur[0].right;
+            tp.stride_bytes = (int64_t)stride;
+            tp.root = c.root;
+            tp.dirty = c.commit.dirty.data();
+            tp.n_dirty = c.commit.all ? -1 : (int64_t)c.commit.dirty.size();
+            trees.push_back(c.dev_tree);
+            topos.push_back(tp);
+            owner.push_back(r);
+            want = want || c.commit.want_length;
+        }
+        if (!trees.empty())
+        {
             lens.resize(trees.size());
             gpu_check(lvb_gpu_commit_batch(dev.ctx, (int64_t)trees.size(), trees.data(), topos.data(),
                                            want ? lens.data() : nullptr));
-            if (want)
-                for (size_t i = 0; i < owner.size(); i++)
-                    if (chains[(size_t)owner[i]].commits[wave].want_length)
-                        clen[(size_t)owner[i]] = lens[i];
+            for (size_t i = 0; i < owner.size(); i++)
+            {
+                Chain &c = chains[(size_t)owner[i]];
+                if (c.commit.want_length)
+                    clen[(size_t)owner[i]] = lens[i];
+                c.commit.used = c.commit.all = c.commit.want_length = false;
+                c.commit.dirty.clear();
+            }
         }
+        prof[1] += since(tp0);
         if (!alive)
             break;
+        tp0 = now();
         /* proposals of all chains in one launch */
         trees.clear();
         topos.clear();
@@ -715,13 +714,18 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             Chain &c = chains[(size_t)r];
             for (int k = 0; k < c.n_spec; k++)
             {
-                lvb_gpu_topology tp;
-                tp.left = &c.cand[(size_t)k][0].left;
-                tp.right = &c.cand[(size_t)k][0].right;
+                const Proposal &pr = c.cand[(size_t)k];
+                lvb_gpu_topology tp = lvb_gpu_topology();
+                tp.left = &c.cur[0].left; /* the current tree ... */
+                tp.right = &c.cur[0].right;
                 tp.stride_bytes = (int64_t)stride;
                 tp.root = c.root;
-                tp.dirty = c.cand_dirty[(size_t)k].data();
-                tp.n_dirty = (int64_t)c.cand_dirty[(size_t)k].size();
+                tp.dirty = pr.dirty.data();
+                tp.n_dirty = (int64_t)pr.dirty.size();
+                tp.mod_node = pr.mod_node.data(); /* ... with the links this proposal rewired */
+                tp.mod_left = pr.mod_left.data();
+                tp.mod_right = pr.mod_right.data();
+                tp.n_mod = (int64_t)pr.mod_node.size();
                 trees.push_back(c.dev_tree);
                 topos.push_back(tp);
             }
@@ -732,13 +736,31 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             gpu_check(lvb_gpu_score_batch(dev.ctx, (int64_t)trees.size(), trees.data(), topos.data(), lens.data()));
             score_launches++;
         }
+        prof[2] += since(tp0);
+        tp0 = now();
+        offsets.resize((size_t)R);
         size_t off = 0;
         for (int r = 0; r < R; r++)
         {
-            Chain &c = chains[(size_t)r];
-            c.resolve(&clen[(size_t)r], lens.data() + off);
-            off += (size_t)c.n_spec;
+            offsets[(size_t)r] = off;
+            off += (size_t)chains[(size_t)r].n_spec;
         }
+#pragma omp parallel for schedule(dynamic, 1) num_threads(host_threads) if (host_threads > 1)
+        for (int r = 0; r < R; r++)
+        {
+            try
+            {
+                chains[(size_t)r].resolve(&clen[(size_t)r], lens.data() + offsets[(size_t)r]);
+            }
+            catch (const LvbError &e)
+            {
+#pragma omp critical
+                failure = e.message;
+            }
+        }
+        if (!failure.empty())
+            crash("%s", failure.c_str());
+        prof[3] += since(tp0);
     }
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
     for (int r = 0; r < R; r++)
@@ -746,6 +768,9 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         results[(size_t)r] = chains[(size_t)r].res;
         results[(size_t)r].launches_scored = score_launches;
         results[(size_t)r].seconds = secs;
+        results[(size_t)r].rounds = rounds;
+        for (int i = 0; i < 4; i++)
+            results[(size_t)r].prof[i] = prof[i];
         gpu_check(lvb_gpu_tree_destroy(dev.ctx, chains[(size_t)r].dev_tree));
     }
     if (sumfp)

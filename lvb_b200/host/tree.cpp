@@ -17,6 +17,22 @@ namespace lvbhost
 
 static const Lvb_bit_length CLEAN = ~(Lvb_bit_length)0; /* any non-zero word means "clean" */
 
+/* While a ProposalScratch is installed, every node record is saved the first time an operator
+ * is about to change it, so that the operator can run directly on the current tree and be
+ * undone afterwards (propose()).  No journal: the operators behave exactly as before. */
+static thread_local ProposalScratch *tl_journal = nullptr;
+
+static inline void jt(TREESTACK_TREE_NODES *tree, long v)
+{
+    ProposalScratch *j = tl_journal;
+    if (!j || j->stamp[(size_t)v] == j->cur)
+        return;
+    j->stamp[(size_t)v] = j->cur;
+    j->node.push_back(v);
+    j->before.push_back(tree[v]);
+    j->flag_before.push_back(tree[v].sitestate[0]);
+}
+
 /* src/TreeOperations.c:914-955: one block, freed with a single free() */
 TREESTACK_TREE_NODES *treealloc(Dataptr MSA, bool b_with_sitestate)
 {
@@ -56,6 +72,7 @@ void treecopy(Dataptr MSA, TREESTACK_TREE_NODES *dest, const TREESTACK_TREE_NODE
 /* src/TreeOperations.c:49-59 */
 void nodeclear(TREESTACK_TREE_NODES *tree, long brnch)
 {
+    jt(tree, brnch);
     tree[brnch].left = tree[brnch].right = tree[brnch].parent = tree[brnch].changes = UNSET;
     tree[brnch].sitestate[0] = 0;
 }
@@ -96,6 +113,7 @@ static void make_dirty_below(Dataptr MSA, TREESTACK_TREE_NODES *tree, long node)
     lvb_assert(tree[node].parent != UNSET);
     do
     {
+        jt(tree, node);
         tree[node].sitestate[0] = 0;
         node = tree[node].parent;
     } while (tree[node].parent != UNSET);
@@ -111,6 +129,11 @@ static void nni_at(Dataptr MSA, TREESTACK_TREE_NODES *tree, long u, bool move_ri
     const long c = u_is_left ? tree[v].right : tree[v].left;
     const long moved = move_right_child ? b : a;
     const long kept = move_right_child ? a : b;
+    jt(tree, v);
+    jt(tree, u);
+    jt(tree, kept);
+    jt(tree, c);
+    jt(tree, moved);
     if (u_is_left)
         tree[v].right = moved;
     else
@@ -132,13 +155,18 @@ void mutate_deterministic(Dataptr MSA, TREESTACK_TREE_NODES *dest, const TREESTA
     nni_at(MSA, dest, p, !left);
 }
 
+static void nni_inplace(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *tree)
+{
+    const long u = rng.randpint(MSA->numberofpossiblebranches - MSA->n - 1) + MSA->n;
+    nni_at(MSA, tree, u, rng.uni() < 0.5);
+}
+
 /* src/TreeOperations.c:160-209: two draws, the branch then the side */
 void mutate_nni(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTACK_TREE_NODES *src, long root)
 {
     (void)root;
     treecopy(MSA, dest, src, true);
-    const long u = rng.randpint(MSA->numberofpossiblebranches - MSA->n - 1) + MSA->n;
-    nni_at(MSA, dest, u, rng.uni() < 0.5);
+    nni_inplace(MSA, rng, dest);
 }
 
 /* src/TreeOperations.c:211-234 */
@@ -175,6 +203,12 @@ static Prune prune_and_open(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *tree, l
            is_descendant(tree, p.src, p.dest));
 
     /* excise */
+    jt(tree, src_parent);
+    jt(tree, p.src);
+    jt(tree, tree[src_parent].parent);
+    jt(tree, src_sister);
+    jt(tree, tree[p.dest].parent);
+    jt(tree, p.dest);
     if (tree[src_parent].left == p.src)
         tree[src_parent].left = UNSET;
     else if (tree[src_parent].right == p.src)
@@ -207,15 +241,20 @@ static Prune prune_and_open(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *tree, l
 }
 
 /* src/TreeOperations.c:236-335 */
+static void spr_inplace(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *tree, long root)
+{
+    const Prune p = prune_and_open(MSA, rng, tree, root);
+    tree[p.excess].right = p.src;
+    tree[p.src].parent = p.excess;
+    make_dirty_below(MSA, tree, p.excess);
+    if (p.parents_par != root)
+        make_dirty_below(MSA, tree, p.parents_par);
+}
+
 void mutate_spr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTACK_TREE_NODES *src, long root)
 {
     treecopy(MSA, dest, src, true);
-    const Prune p = prune_and_open(MSA, rng, dest, root);
-    dest[p.excess].right = p.src;
-    dest[p.src].parent = p.excess;
-    make_dirty_below(MSA, dest, p.excess);
-    if (p.parents_par != root)
-        make_dirty_below(MSA, dest, p.parents_par);
+    spr_inplace(MSA, rng, dest, root);
 }
 
 /* leaves under `top` in left-first depth-first order (count + addtoarray,
@@ -244,10 +283,8 @@ static void subtree_leaves(const TREESTACK_TREE_NODES *tree, long top, std::vect
 
 /* src/TreeOperations.c:337-541: SPR whose pruned subtree is first re-rooted on the edge above
  * a random one of its leaves (when it has more than two) */
-void mutate_tbr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTACK_TREE_NODES *src_tree, long root)
+static void tbr_inplace(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *tree, long root)
 {
-    TREESTACK_TREE_NODES *tree = dest;
-    treecopy(MSA, tree, src_tree, true);
     const Prune p = prune_and_open(MSA, rng, tree, root);
     long src = p.src;
 
@@ -271,6 +308,8 @@ void mutate_tbr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTA
             up.push_back(v);
         up.push_back(oldroot);
 
+        for (long v : up)
+            jt(tree, v);
         /* newroot's parent becomes the top of the subtree: children (its old parent, newroot) */
         const long first = up[0];
         long carried = tree[first].left == newroot ? tree[first].right : tree[first].left; /* newroot's sister */
@@ -289,6 +328,7 @@ void mutate_tbr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTA
             else if (tree[cur].right == previous)
                 other = tree[cur].left;
             lvb_assert(other != UNSET);
+            jt(tree, carried);
             tree[cur].right = carried;
             tree[cur].parent = previous;
             tree[cur].left = above;
@@ -304,10 +344,12 @@ void mutate_tbr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTA
             tree[oldroot].left = carried;
         else if (tree[oldroot].right == previous)
             tree[oldroot].right = carried;
+        jt(tree, carried);
         tree[carried].parent = oldroot;
         src = tree[newroot].parent;
     }
 
+    jt(tree, src);
     tree[p.excess].right = src;
     tree[src].parent = p.excess;
 
@@ -321,6 +363,83 @@ void mutate_tbr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTA
     make_dirty_below(MSA, tree, p.excess);
     if (p.parents_par != root)
         make_dirty_below(MSA, tree, p.parents_par);
+}
+
+void mutate_tbr(Dataptr MSA, Uni &rng, TREESTACK_TREE_NODES *dest, const TREESTACK_TREE_NODES *src_tree, long root)
+{
+    treecopy(MSA, dest, src_tree, true);
+    tbr_inplace(MSA, rng, dest, root);
+}
+
+/* A proposal without the whole-tree copy: run the operator on the current tree itself with
+ * the journal on, keep what it changed (records, child links that differ, nodes to recompute),
+ * put the tree back.  Cost is O(nodes touched), not O(n).  `current` must be all clean. */
+void propose(Dataptr MSA, Uni &rng, int op, TREESTACK_TREE_NODES *current, long root, ProposalScratch &scratch,
+             Proposal &out)
+{
+    if (scratch.stamp.size() != (size_t)MSA->numberofpossiblebranches)
+    {
+        scratch.stamp.assign((size_t)MSA->numberofpossiblebranches, 0);
+        scratch.cur = 0;
+    }
+    if (++scratch.cur == 0)
+    {
+        std::fill(scratch.stamp.begin(), scratch.stamp.end(), 0u);
+        scratch.cur = 1;
+    }
+    scratch.node.clear();
+    scratch.before.clear();
+    scratch.flag_before.clear();
+    tl_journal = &scratch;
+    try
+    {
+        if (op == 0)
+            nni_inplace(MSA, rng, current);
+        else if (op == 1)
+            spr_inplace(MSA, rng, current, root);
+        else
+            tbr_inplace(MSA, rng, current, root);
+    }
+    catch (...)
+    {
+        tl_journal = nullptr;
+        throw;
+    }
+    tl_journal = nullptr;
+    out.op = op;
+    out.node = scratch.node;
+    out.after.clear();
+    out.dirty.clear();
+    out.mod_node.clear();
+    out.mod_left.clear();
+    out.mod_right.clear();
+    for (size_t i = 0; i < scratch.node.size(); i++)
+    {
+        const long v = scratch.node[i];
+        const TREESTACK_TREE_NODES &was = scratch.before[i];
+        out.after.push_back(current[v]);
+        if (current[v].left != was.left || current[v].right != was.right)
+        {
+            out.mod_node.push_back(v);
+            out.mod_left.push_back(current[v].left);
+            out.mod_right.push_back(current[v].right);
+        }
+        if (current[v].sitestate[0] == 0 && v >= MSA->n)
+            out.dirty.push_back(v);
+        current[v] = was;
+        current[v].sitestate[0] = scratch.flag_before[i];
+    }
+}
+
+/* the accepted proposal becomes the current tree (SwapTrees, src/TreeOperations.c:1062-1080); flags stay clean */
+void apply_proposal(TREESTACK_TREE_NODES *current, const Proposal &p)
+{
+    for (size_t i = 0; i < p.node.size(); i++)
+    {
+        Lvb_bit_length *keep = current[p.node[i]].sitestate;
+        current[p.node[i]] = p.after[i];
+        current[p.node[i]].sitestate = keep;
+    }
 }
 
 /* src/TreeOperations.c:576-637.  Walking from the new root leaf up to the old one, every

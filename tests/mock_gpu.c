@@ -141,6 +141,11 @@ static long evaluate(lvb_gpu_ctx *c, const lvb_gpu_topology *tp, uint64_t *rows,
         c->left[v] = strided(tp->left, tp->stride_bytes, v);
         c->right[v] = strided(tp->right, tp->stride_bytes, v);
     }
+    for (long k = 0; k < tp->n_mod; k++)
+    {
+        c->left[tp->mod_node[k]] = (long)tp->mod_left[k];
+        c->right[tp->mod_node[k]] = (long)tp->mod_right[k];
+    }
     if (tp->n_dirty < 0)
         for (long v = c->n; v < c->B; v++)
             rows[v * c->nwords] = 0;

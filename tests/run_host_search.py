@@ -3,7 +3,7 @@ its own and print one JSON line.  With --mock the lvb_gpu_* entry points are ans
 tests/mock_gpu.c (CPU oracle) — for the `-m "not gpu"` suite; without it the real
 liblvbgpu.so and a GPU are used.
 
-usage: run_host_search.py [--mock] <alignment.npz key | path.phy> seed algorithm [speculation] [replicates] [max_rearr]
+usage: run_host_search.py [--mock] <alignment.npz key | path.phy> seed algorithm [speculation] [replicates] [max_rearr] [host_threads]
 """
 import ctypes as C
 import hashlib
@@ -49,6 +49,7 @@ def main():
     spec = int(args[3]) if len(args) > 3 else 0
     reps = int(args[4]) if len(args) > 4 else 1
     max_rearr = int(args[5]) if len(args) > 5 else 0
+    threads = int(args[6]) if len(args) > 6 else 1
     if src.endswith(".phy"):
         msa = host.HostMSA.load(src)
     else:
@@ -57,7 +58,7 @@ def main():
         msa = host.HostMSA.from_rows([bytes(r) for r in g[key]])
     with tempfile.TemporaryDirectory() as d:
         tsv, out = os.path.join(d, "t.tsv"), os.path.join(d, "outtree")
-        res = msa.search(seed, algorithm=algo, speculation=spec, replicates=reps, max_rearrangements=max_rearr,
+        res = msa.search(seed, algorithm=algo, speculation=spec, replicates=reps, max_rearrangements=max_rearr, host_threads=threads,
                          tsv_path=tsv, outtree_path=out)
         line = {"mock": mock, "results": res, "tsv_md5": md5(tsv), "outtree_md5": md5(out),
                 "tsv_head": open(tsv).read().split("\n")[:41],

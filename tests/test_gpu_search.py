@@ -66,7 +66,7 @@ def test_replicates_on_gpu():
     """BASELINE.json configs[4] in small: 8 chains in lock-step batches == 8 single-chain runs"""
     def run(seed, reps):
         p = subprocess.run([sys.executable, os.path.join(HERE, "run_host_search.py"), "example.npz:text", str(seed), "1",
-                            "0", str(reps), "30000"], capture_output=True, text=True, timeout=900)
+                            "0", str(reps), "30000", "4"], capture_output=True, text=True, timeout=900)
         assert p.returncode == 0, p.stderr[-2000:]
         return json.loads(p.stdout.strip().splitlines()[-1])
 

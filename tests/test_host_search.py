@@ -56,7 +56,7 @@ def test_speculation_depth_does_not_change_the_result(k):
 def test_replicates_are_independent_chains():
     """-R 3: chain r is the single-chain run with seed s + r (BASELINE.json configs[4] in small)"""
     p = subprocess.run([sys.executable, os.path.join(HERE, "run_host_search.py"), "--mock", "treelength.npz:tl5_thread_2_text",
-                        "1", "1", "0", "3"], capture_output=True, text=True, timeout=900)
+                        "1", "1", "0", "3", "0", "3"], capture_output=True, text=True, timeout=900)  # 3 host threads
     assert p.returncode == 0, p.stderr[-2000:]
     multi = json.loads(p.stdout.strip().splitlines()[-1])
     for r in range(3):
