@@ -21,14 +21,75 @@
 namespace lvbgpu
 {
 
-#define LVB_CHUNK 256 /* instructions staged in shared memory at a time */
+#define LVB_CHUNK 128 /* instructions staged in shared memory at a time */
 
-__device__ __forceinline__ uint4 ld_row(const uint4 *p)
+/* An instruction as the inner loop wants it (decoded once per CTA while the chunk is staged):
+ *   x = operand a: pool ROW number (tree offset applied); ignored if D_APREV (a = previous result)
+ *   y = operand b: pool row, or if D_BSLOT the byte offset of the stack slot in the per-thread stack
+ *   z = pool row the result is stored to (D_STORE)
+ *   w = D_* flags in bits 0..3 | byte offset of the stack slot to push the result to (D_PUSH)
+ * Fitch's step is symmetric in its operands, so the host's (slot, prev) becomes (prev, slot). */
+#define D_STORE 0x1u
+#define D_APREV 0x2u
+#define D_BSLOT 0x4u
+#define D_PUSH 0x8u
+
+/* The inner loop is written with explicit PTX for its memory operations: nvcc otherwise
+ * re-derives the shared-memory window base and the operand initialisers on every trip. */
+__device__ __forceinline__ unsigned long long row_addr(unsigned row, unsigned stride_b, unsigned long long colbase)
 {
-    /* rows read as operands are never written in the same launch: non-coherent path */
-    return __ldg(p);
+    unsigned long long d;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(d) : "r"(row), "r"(stride_b), "l"(colbase));
+    return d;
+}
+/* predicated 16-byte load through the non-coherent path; v keeps its old value when !pred.
+ * Rows read as operands are never written in the same launch. */
+__device__ __forceinline__ void ldg_if(uint4 &v, unsigned long long ptr, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
+                 : "l"(ptr), "r"(pred));
+}
+__device__ __forceinline__ void stg_if(unsigned long long ptr, const uint4 &v, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p st.global.v4.u32 [%4], {%0,%1,%2,%3};\n\t}"
+                 :
+                 : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(ptr), "r"(pred)
+                 : "memory");
+}
+__device__ __forceinline__ uint4 lds128(unsigned addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void lds128_if(uint4 &v, unsigned addr, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
+                 : "r"(addr), "r"(pred));
+}
+__device__ __forceinline__ void sts128_if(unsigned addr, const uint4 &v, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p st.shared.v4.u32 [%4], {%0,%1,%2,%3};\n\t}"
+                 :
+                 : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(addr), "r"(pred)
+                 : "memory");
+}
+__device__ __forceinline__ void sts32_if(unsigned addr, unsigned v, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t"
+                 "@p st.shared.u32 [%1], %0;\n\t}"
+                 :
+                 : "r"(v), "r"(addr), "r"(pred)
+                 : "memory");
 }
 
+/* one 32-bit lane (8 sites): e8 has bit 3 of a nibble set <=> the intersection is EMPTY */
 __device__ __forceinline__ unsigned fitch_lane(unsigned x, unsigned y, unsigned &out)
 {
     const unsigned t = x & y;
@@ -39,124 +100,149 @@ __device__ __forceinline__ unsigned fitch_lane(unsigned x, unsigned y, unsigned 
     return s;
 }
 
-/* returns the number of changes (0..32) of this 32-site column */
+/* returns the flag word of this 32-site column: one bit per site whose intersection is empty */
 __device__ __forceinline__ unsigned fitch_step(const uint4 &x, const uint4 &y, uint4 &out)
 {
     const unsigned s0 = fitch_lane(x.x, y.x, out.x);
     const unsigned s1 = fitch_lane(x.y, y.y, out.y);
     const unsigned s2 = fitch_lane(x.z, y.z, out.z);
     const unsigned s3 = fitch_lane(x.w, y.w, out.w);
-    /* the four flag words occupy bit 0 of each nibble: interleave them and count once */
-    return __popc(s0 + 2u * s1 + 4u * s2 + 8u * s3);
+    /* the four flag words occupy bit 0 of each nibble: interleave them, count once */
+    return s0 + 2u * s1 + 4u * s2 + 8u * s3;
 }
 
 template <bool PER_NODE>
 __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
 {
     extern __shared__ uint4 smem_u4[];
-    FitchInstr *s_instr = reinterpret_cast<FitchInstr *>(smem_u4);             /* LVB_CHUNK x 16 B */
-    int *s_cnt = reinterpret_cast<int *>(smem_u4 + LVB_CHUNK);                 /* LVB_CHUNK ints   */
-    uint4 *s_stack = smem_u4 + LVB_CHUNK + LVB_CHUNK / 4;                      /* n_slots x blockDim */
+    uint4 *s_instr = smem_u4;                                          /* LVB_CHUNK + 2 decoded instructions */
+    int *s_cnt = reinterpret_cast<int *>(smem_u4 + LVB_CHUNK + 2);     /* PER_NODE: [LVB_CHUNK][warps] */
+    uint4 *s_stack = smem_u4 + LVB_CHUNK + 2 + (PER_NODE ? LVB_CHUNK * 8 / 4 : 0); /* n_slots x blockDim */
     __shared__ unsigned long long s_total;
 
     const int tid = threadIdx.x;
     const int nthr = blockDim.x;
+    const int nwarps = nthr >> 5;
     /* column-block-major: CTAs of different programs over the same columns run together,
      * so rows shared between candidates of one tree are served from L2 */
     const int prog_id = blockIdx.x % p.n_prog;
     const int cb = blockIdx.x / p.n_prog;
     const FitchProgram prog = p.prog[prog_id];
     const int col = cb * nthr + tid;
-    const bool active = col < p.ncols;
-    const int64_t tree_off = (int64_t)prog.tree * p.n_internal; /* internal node v lives in row v + tree_off */
-    const uint4 *pool = p.pool;
+    const unsigned active = col < p.ncols ? 1u : 0u;
+    const unsigned amask = active ? ~0u : 0u;
+    const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal; /* internal node v lives in row v + tree_off */
     const FitchInstr *gi = p.instr + prog.instr_begin;
+    /* threads past the end of the row (last column block only) redo the last column; their
+     * counts are masked and their stores suppressed */
+    const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
+    const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
+    const unsigned slot_bytes = (unsigned)nthr * 16u;
+    const unsigned sa_instr = (unsigned)__cvta_generic_to_shared(s_instr);
+    const unsigned sa_stack = (unsigned)__cvta_generic_to_shared(s_stack + tid);
+    const unsigned sa_cnt = (unsigned)__cvta_generic_to_shared(s_cnt + (tid >> 5));
+    const unsigned cnt_step = (unsigned)nwarps * 4u;
+    const unsigned lane0 = (tid & 31) == 0 ? 1u : 0u;
 
     if (tid == 0)
         s_total = 0ull;
 
-    const uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
-    uint4 acc = ones;
+    uint4 acc = make_uint4(~0u, ~0u, ~0u, ~0u);
     unsigned total = 0;
 
     for (int base = 0; base < prog.n_instr; base += LVB_CHUNK)
     {
         const int m = min(LVB_CHUNK, prog.n_instr - base);
         __syncthreads();
-        for (int i = tid; i < m; i += nthr)
+        for (int i = tid; i <= m + 1; i += nthr)
         {
-            s_instr[i] = gi[base + i];
-            if (PER_NODE)
-                s_cnt[i] = 0;
+            uint4 d = make_uint4(0u, 0u, 0u, D_APREV | D_BSLOT); /* sentinels after the last one: no loads */
+            if (i < m)
+            {
+                const FitchInstr in = gi[base + i];
+                int a = in.a, b = in.b;
+                if (LVB_OPER_IS_SLOT(a) || b == LVB_OPER_PREV)
+                {
+                    const int t = a;
+                    a = b;
+                    b = t;
+                }
+                unsigned w = in.ctl & LVB_CTL_STORE ? D_STORE : 0u;
+                const unsigned push = (in.ctl & LVB_CTL_PUSH_MASK) >> LVB_CTL_PUSH_SHIFT;
+                if (push)
+                    w |= D_PUSH | ((push - 1u) * slot_bytes);
+                if (a < 0)
+                {
+                    w |= D_APREV;
+                    a = 0;
+                }
+                else if (a >= p.n)
+                    a += tree_off;
+                if (b < 0)
+                {
+                    w |= D_BSLOT;
+                    b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
+                }
+                else if (b >= p.n)
+                    b += tree_off;
+                d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
+            }
+            s_instr[i] = d;
         }
         __syncthreads();
 
-        /* software pipeline, depth 1: the HBM operands of instruction i+1 are requested
-         * before instruction i is computed */
-        FitchInstr cur = s_instr[0];
-        uint4 ga = ones, gb = ones;
-        if (active)
-        {
-            if (cur.a >= 0)
-                ga = ld_row(pool + (cur.a + (cur.a >= p.n ? tree_off : 0)) * p.stride_u4 + col);
-            if (cur.b >= 0)
-                gb = ld_row(pool + (cur.b + (cur.b >= p.n ? tree_off : 0)) * p.stride_u4 + col);
-        }
-        for (int i = 0; i < m; i++)
-        {
-            FitchInstr nxt = cur;
-            uint4 na = ones, nb = ones;
-            if (i + 1 < m)
-            {
-                nxt = s_instr[i + 1];
-                if (active)
-                {
-                    if (nxt.a >= 0)
-                        na = ld_row(pool + (nxt.a + (nxt.a >= p.n ? tree_off : 0)) * p.stride_u4 + col);
-                    if (nxt.b >= 0)
-                        nb = ld_row(pool + (nxt.b + (nxt.b >= p.n ? tree_off : 0)) * p.stride_u4 + col);
-                }
-            }
-            uint4 x, y;
-            if (cur.a >= 0)
-                x = ga;
-            else if (cur.a == LVB_OPER_PREV)
-                x = acc;
-            else
-                x = s_stack[LVB_OPER_SLOT_INDEX(cur.a) * nthr + tid];
-            if (cur.b >= 0)
-                y = gb;
-            else if (cur.b == LVB_OPER_PREV)
-                y = acc;
-            else
-                y = s_stack[LVB_OPER_SLOT_INDEX(cur.b) * nthr + tid];
+        /* software pipeline, depth 1, two instructions per trip (registers ping-pong, no moves):
+         * the HBM operands of instruction i+1 are requested before instruction i is computed */
+        uint4 c0 = lds128(sa_instr), c1;
+        uint4 a0 = acc, b0 = acc, a1 = acc, b1 = acc;
+        ldg_if(a0, row_addr(c0.x, stride_b, colbase), !(c0.w & D_APREV));
+        ldg_if(b0, row_addr(c0.y, stride_b, colbase), !(c0.w & D_BSLOT));
 
-            uint4 out;
-            const unsigned ch = fitch_step(x, y, out);
-            if (!PER_NODE)
-                total += ch;
-            if (PER_NODE)
-            {
-                const unsigned w = __reduce_add_sync(0xffffffffu, ch);
-                if ((tid & 31) == 0 && w)
-                    atomicAdd(&s_cnt[i], (int)w);
-            }
-            if ((cur.ctl & LVB_CTL_STORE) && active)
-                p.pool[(cur.node + tree_off) * p.stride_u4 + col] = out;
-            const unsigned push = (cur.ctl & LVB_CTL_PUSH_MASK) >> LVB_CTL_PUSH_SHIFT;
-            if (push)
-                s_stack[(push - 1) * nthr + tid] = out;
-            acc = out;
-            cur = nxt;
-            ga = na;
-            gb = nb;
+#define LVB_STEP(IADDR, CADDR, CI, GA, GB, NI, NA, NB)                                                                \
+    {                                                                                                                 \
+        NI = lds128(IADDR);                                                                                           \
+        ldg_if(NA, row_addr(NI.x, stride_b, colbase), !(NI.w & D_APREV));                                             \
+        ldg_if(NB, row_addr(NI.y, stride_b, colbase), !(NI.w & D_BSLOT));                                             \
+        const bool ap = CI.w & D_APREV;                                                                               \
+        uint4 x;                                                                                                      \
+        x.x = ap ? acc.x : GA.x;                                                                                      \
+        x.y = ap ? acc.y : GA.y;                                                                                      \
+        x.z = ap ? acc.z : GA.z;                                                                                      \
+        x.w = ap ? acc.w : GA.w;                                                                                      \
+        lds128_if(GB, sa_stack + CI.y, CI.w & D_BSLOT);                                                               \
+        const unsigned f = fitch_step(x, GB, acc) & amask;                                                            \
+        if (PER_NODE)                                                                                                 \
+            sts32_if(CADDR, __reduce_add_sync(0xffffffffu, __popc(f)), lane0);                                        \
+        else                                                                                                          \
+            total += __popc(f);                                                                                       \
+        stg_if(row_addr(CI.z, stride_b, colbase), acc, (CI.w & D_STORE) & active);                                    \
+        sts128_if(sa_stack + (CI.w & ~15u), acc, CI.w & D_PUSH);                                                      \
+    }
+
+        unsigned ia = sa_instr + 16u, ca = sa_cnt;
+        int i = 0;
+        for (; i + 1 < m; i += 2)
+        {
+            LVB_STEP(ia, ca, c0, a0, b0, c1, a1, b1)
+            LVB_STEP(ia + 16u, ca + cnt_step, c1, a1, b1, c0, a0, b0)
+            ia += 32u;
+            ca += 2u * cnt_step;
         }
+        if (i < m)
+            LVB_STEP(ia, ca, c0, a0, b0, c1, a1, b1)
+#undef LVB_STEP
+
         if (PER_NODE)
         {
             __syncthreads();
-            for (int i = tid; i < m; i += nthr)
-                if (s_cnt[i])
-                    atomicAdd(&p.cnts[prog.instr_begin + base + i], s_cnt[i]);
+            for (int k = tid; k < m; k += nthr)
+            {
+                int sum = 0;
+                for (int w = 0; w < nwarps; w++)
+                    sum += s_cnt[k * nwarps + w];
+                if (sum)
+                    atomicAdd(&p.cnts[prog.instr_begin + base + k], sum);
+            }
         }
     }
 
@@ -204,9 +290,14 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
     }
 }
 
+static size_t exec_smem_bytes(bool per_node, int n_slots, int block)
+{
+    return (size_t)(LVB_CHUNK + 2 + (per_node ? LVB_CHUNK * 8 / 4 : 0) + (size_t)n_slots * block) * sizeof(uint4);
+}
+
 cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cudaStream_t stream)
 {
-    const size_t smem = (size_t)(LVB_CHUNK + LVB_CHUNK / 4 + (size_t)p.n_slots * block) * sizeof(uint4);
+    const size_t smem = exec_smem_bytes(per_node, p.n_slots, block);
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
     cudaError_t e;
     if (per_node)
