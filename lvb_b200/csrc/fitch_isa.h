@@ -47,7 +47,11 @@ typedef struct FitchProgram
     int32_t instr_begin; /* index of the first instruction in the batch's instruction buffer */
     int32_t n_instr;
     int32_t tree;        /* device tree the internal operands/stores refer to */
-    int32_t flags;       /* bit 0: per-node counts wanted (store programs) */
+    int32_t flags;       /* bit 0: per-node counts wanted (store programs); pieces: their level */
+    int32_t parent;      /* piece (index into the launch's program array) that reads the row this piece's
+                          * top node stores, -1 if none */
+    int32_t n_wait;      /* number of pieces of the same launch whose stored rows this piece reads */
+    int32_t pad0, pad1;
 } FitchProgram;
 
 #endif

@@ -44,12 +44,21 @@ __device__ __forceinline__ unsigned long long row_addr(unsigned row, unsigned st
 }
 /* predicated 16-byte load through the non-coherent path; v keeps its old value when !pred.
  * Rows read as operands are never written in the same launch. */
+template <bool NC>
 __device__ __forceinline__ void ldg_if(uint4 &v, unsigned long long ptr, unsigned pred)
 {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
-                 "@p ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
-                 : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
-                 : "l"(ptr), "r"(pred));
+    if (NC)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                     "@p ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                     : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
+                     : "l"(ptr), "r"(pred));
+    else /* store mode: a row may have been written by another CTA of this launch (dependent
+          * pieces), so it is read at L2, never through the non-coherent L1 path */
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                     "@p ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                     : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
+                     : "l"(ptr), "r"(pred)
+                     : "memory");
 }
 __device__ __forceinline__ void stg_if(unsigned long long ptr, const uint4 &v, unsigned pred)
 {
@@ -112,7 +121,7 @@ __device__ __forceinline__ unsigned fitch_step(const uint4 &x, const uint4 &y, u
 }
 
 template <bool PER_NODE>
-__global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
+__global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
 {
     extern __shared__ uint4 smem_u4[];
     uint4 *s_instr = smem_u4;                                          /* LVB_CHUNK + 2 decoded instructions */
@@ -123,11 +132,42 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
     const int tid = threadIdx.x;
     const int nthr = blockDim.x;
     const int nwarps = nthr >> 5;
-    /* column-block-major: CTAs of different programs over the same columns run together,
-     * so rows shared between candidates of one tree are served from L2 */
-    const int prog_id = blockIdx.x % p.n_prog;
-    const int cb = blockIdx.x / p.n_prog;
+    unsigned vb = blockIdx.x;
+    if (PER_NODE && p.dep)
+    {
+        /* dependent pieces in one launch: a piece waits for the pieces below it, so CTAs are
+         * numbered in the order they START (children are sorted before their parents) */
+        __shared__ unsigned s_vb;
+        if (tid == 0)
+        {
+            const unsigned t = atomicAdd(p.ticket, 1u);
+            if (t == gridDim.x - 1)
+                *p.ticket = 0u; /* every ticket is taken: ready for the next launch */
+            s_vb = t;
+        }
+        __syncthreads();
+        vb = s_vb;
+    }
+    /* independent programs: column-block-major, CTAs of different programs over the same columns
+     * run together, so rows shared between candidates of one tree are served from L2.
+     * dependent pieces: piece-major (pieces are sorted by level), so that by the time a piece
+     * starts the pieces below it have normally finished — a soft barrier between levels */
+    const bool piece_major = PER_NODE && p.dep;
+    const int prog_id = piece_major ? vb / p.n_colblocks : vb % p.n_prog;
+    const int cb = piece_major ? vb % p.n_colblocks : vb / p.n_prog;
     const FitchProgram prog = p.prog[prog_id];
+    if (PER_NODE && p.dep && prog.n_wait > 0)
+    {
+        if (tid == 0)
+        {
+            volatile unsigned *f = p.dep + (size_t)prog_id * p.n_colblocks + cb;
+            while (*f < (unsigned)prog.n_wait)
+                __nanosleep(100);
+            *f = 0u;
+            __threadfence();
+        }
+        __syncthreads();
+    }
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
@@ -195,14 +235,14 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
          * the HBM operands of instruction i+1 are requested before instruction i is computed */
         uint4 c0 = lds128(sa_instr), c1;
         uint4 a0 = acc, b0 = acc, a1 = acc, b1 = acc;
-        ldg_if(a0, row_addr(c0.x, stride_b, colbase), !(c0.w & D_APREV));
-        ldg_if(b0, row_addr(c0.y, stride_b, colbase), !(c0.w & D_BSLOT));
+        ldg_if<!PER_NODE>(a0, row_addr(c0.x, stride_b, colbase), !(c0.w & D_APREV));
+        ldg_if<!PER_NODE>(b0, row_addr(c0.y, stride_b, colbase), !(c0.w & D_BSLOT));
 
 #define LVB_STEP(IADDR, CADDR, CI, GA, GB, NI, NA, NB)                                                                \
     {                                                                                                                 \
         NI = lds128(IADDR);                                                                                           \
-        ldg_if(NA, row_addr(NI.x, stride_b, colbase), !(NI.w & D_APREV));                                             \
-        ldg_if(NB, row_addr(NI.y, stride_b, colbase), !(NI.w & D_BSLOT));                                             \
+        ldg_if<!PER_NODE>(NA, row_addr(NI.x, stride_b, colbase), !(NI.w & D_APREV));                                             \
+        ldg_if<!PER_NODE>(NB, row_addr(NI.y, stride_b, colbase), !(NI.w & D_BSLOT));                                             \
         const bool ap = CI.w & D_APREV;                                                                               \
         uint4 x;                                                                                                      \
         x.x = ap ? acc.x : GA.x;                                                                                      \
@@ -247,7 +287,18 @@ __global__ void __launch_bounds__(256) fitch_exec_kernel(const ExecParams p)
     }
 
     if (PER_NODE)
-        return; /* store mode: lengths come from the per-instruction counts (commit_finalize) */
+    { /* store mode: lengths come from the per-instruction counts (commit_finalize) */
+        if (p.dep && prog.parent >= 0)
+        {
+            __syncthreads(); /* every thread's row stores are ordered before the release below */
+            if (tid == 0)
+            {
+                __threadfence();
+                atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
+            }
+        }
+        return;
+    }
     /* per-program length: block reduce, one 64-bit atomic per CTA */
     const unsigned w = __reduce_add_sync(0xffffffffu, total);
     if ((tid & 31) == 0 && w)

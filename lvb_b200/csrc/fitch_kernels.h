@@ -28,6 +28,9 @@ struct ExecParams
     long long *out;              /* [n_prog] score mode: the length, written by the last column block
                                   * (pinned host memory mapped into the device, or device memory) */
     int32_t *cnts;               /* [n_instr of batch] per-instruction counts (store mode); zeroed by finalize */
+    unsigned *ticket;            /* store mode, dependent pieces: CTA start-order counter (left zero by the kernel) */
+    unsigned *dep;               /* store mode: [n_prog][n_colblocks] finished child pieces per column block
+                                  * (left zero by the kernel); NULL: pieces of the launch are independent */
     const int32_t *chg;          /* [trees][I] cached per-node change counts */
     const long long *sum_chg;    /* [trees] sum of chg over internal nodes */
 };

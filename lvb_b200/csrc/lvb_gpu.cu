@@ -143,6 +143,12 @@ struct lvb_gpu_ctx
     unsigned *d_done = nullptr;                        /* [cap_tot] CTAs finished per program; zero between batches */
     long long *d_lengths = nullptr;                    /* [cap_tot] lengths on the device (site-block mode: all-reduced here) */
     size_t cap_tot = 0;
+    unsigned *d_dep = nullptr;                         /* [cap_dep] + 1 ticket: dependency counters of one store launch; zero between */
+    size_t cap_dep = 0;
+    bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
+    bool last_dep = false;
+    std::vector<int32_t> owner_stamp, owner_piece;     /* (tree, node) -> piece that stores it in the current batch */
+    int32_t owner_cur = 0;
     int32_t *d_cnts = nullptr;                         /* [cap_cnts] per-instruction counts; zero between batches */
     size_t cap_cnts = 0;
     int block_override = 0;
@@ -293,6 +299,8 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     p.done = c->d_done;
     p.out = out;
     p.cnts = c->d_cnts;
+    p.ticket = c->last_dep ? c->d_dep + c->cap_dep : nullptr;
+    p.dep = c->last_dep ? c->d_dep : nullptr;
     p.chg = c->chg;
     p.sum_chg = c->sum_chg;
 
@@ -457,25 +465,93 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         memcpy(h_instr + off, ins.data(), ins.size() * sizeof(FitchInstr));
         for (const auto &pc : c->c_pieces[k])
         {
-            c->prog.push_back(FitchProgram{(int32_t)(off + pc.instr_begin), pc.n_instr, trees[k], pc.level});
+            c->prog.push_back(FitchProgram{(int32_t)(off + pc.instr_begin), pc.n_instr, trees[k], pc.level, -1, 0, 0, 0});
             multilevel = multilevel || pc.level != 0;
         }
-        h_cand[k] = FitchProgram{(int32_t)off, (int32_t)ins.size(), trees[k], store ? 1 : 0};
+        h_cand[k] = FitchProgram{(int32_t)off, (int32_t)ins.size(), trees[k], store ? 1 : 0, -1, 0, 0, 0};
         off += ins.size();
     }
-    /* pieces sorted by level; one launch per level */
+    /* pieces sorted by level.  Either one launch per level, or (default) ONE launch in which a
+     * piece waits, per column block, for the pieces whose stored rows it reads. */
     c->levels.clear();
+    c->last_dep = false;
     if (multilevel)
     {
         std::stable_sort(c->prog.begin(), c->prog.end(),
                          [](const FitchProgram &a, const FitchProgram &b) { return a.flags < b.flags; });
-        for (size_t i = 0; i < c->prog.size();)
+        if (c->level_launches)
         {
-            size_t j = i;
-            while (j < c->prog.size() && c->prog[j].flags == c->prog[i].flags)
-                j++;
-            c->levels.push_back({(int32_t)i, (int32_t)(j - i)});
-            i = j;
+            for (size_t i = 0; i < c->prog.size();)
+            {
+                size_t j = i;
+                while (j < c->prog.size() && c->prog[j].flags == c->prog[i].flags)
+                    j++;
+                c->levels.push_back({(int32_t)i, (int32_t)(j - i)});
+                i = j;
+            }
+        }
+        else
+        {
+            /* who stores which row: (tree, node) -> piece; then every internal-row operand that a
+             * piece of this batch stores is a dependency of the piece that reads it */
+            const size_t slots = (size_t)c->max_trees * (size_t)c->I;
+            if (c->owner_stamp.size() != slots)
+            {
+                c->owner_stamp.assign(slots, 0);
+                c->owner_piece.assign(slots, 0);
+                c->owner_cur = 0;
+            }
+            if (++c->owner_cur == INT32_MAX)
+            {
+                std::fill(c->owner_stamp.begin(), c->owner_stamp.end(), 0);
+                c->owner_cur = 1;
+            }
+            for (size_t q = 0; q < c->prog.size(); q++)
+            {
+                const FitchProgram &pg = c->prog[q];
+                const size_t tb = (size_t)pg.tree * (size_t)c->I;
+                for (int32_t i = 0; i < pg.n_instr; i++)
+                {
+                    const FitchInstr &in = h_instr[pg.instr_begin + i];
+                    if (in.node >= 0 && (in.ctl & LVB_CTL_STORE))
+                    {
+                        c->owner_stamp[tb + (in.node - c->n)] = c->owner_cur;
+                        c->owner_piece[tb + (in.node - c->n)] = (int32_t)q;
+                    }
+                }
+            }
+            for (size_t q = 0; q < c->prog.size(); q++)
+            {
+                FitchProgram &pg = c->prog[q];
+                const size_t tb = (size_t)pg.tree * (size_t)c->I;
+                for (int32_t i = 0; i < pg.n_instr; i++)
+                {
+                    const FitchInstr &in = h_instr[pg.instr_begin + i];
+                    const int32_t ops[2] = {in.a, in.b};
+                    for (int32_t v : ops)
+                        if (v >= c->n && c->owner_stamp[tb + (v - c->n)] == c->owner_cur)
+                        {
+                            const int32_t child = c->owner_piece[tb + (v - c->n)];
+                            if ((size_t)child >= q)
+                                return fail("internal error: piece %zu reads a row stored by piece %d", q, child);
+                            c->prog[child].parent = (int32_t)q;
+                            pg.n_wait++;
+                        }
+                }
+            }
+            const size_t n_cb = (size_t)((c->stride_u4 + pick_block(c) - 1) / pick_block(c));
+            const size_t need = c->prog.size() * n_cb;
+            if (need > c->cap_dep)
+            {
+                const size_t cap = grow(c->cap_dep, need, 1 << 16);
+                CU(cudaStreamSynchronize(c->stream));
+                cudaFree(c->d_dep);
+                CU(cudaMalloc(&c->d_dep, (cap + 1) * sizeof(unsigned)));
+                CU(cudaMemsetAsync(c->d_dep, 0, (cap + 1) * sizeof(unsigned), c->stream));
+                c->cap_dep = cap;
+            }
+            c->last_dep = true;
+            c->levels.push_back({0, (int32_t)c->prog.size()});
         }
     }
     else
@@ -622,6 +698,8 @@ extern "C"
         const char *tw = getenv("LVB_GPU_TARGET_WARPS");
         if (tw && atoll(tw) > 0)
             c->target_warps = atoll(tw);
+        const char *ll = getenv("LVB_GPU_LEVEL_LAUNCHES");
+        c->level_launches = ll && atoi(ll) != 0;
         const char *b = getenv("LVB_GPU_BLOCK");
         if (b)
         {
@@ -643,6 +721,7 @@ extern "C"
             g_nccl.CommDestroy(c->comm);
         free_matrix(c);
         cudaFree(c->d_cnts);
+        cudaFree(c->d_dep);
         cudaFree(c->d_totals);
         cudaFree(c->d_done);
         cudaFree(c->d_lengths);
