@@ -45,8 +45,8 @@ UNIT = "node*site updates/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="replicas", choices=["replicas", "siteblock"])
     ap.add_argument("--taxa", type=int, default=2000)
@@ -64,8 +64,19 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def traffic_from_profile():
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/ncu_traffic.json, written by tools/ncu_summary.py); None if there is none."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    d = json.load(open(p))
+    return d.get("dram_bytes_per_pass"), d.get("source")
+
+
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING the timed regions."""
+    """SM clock and throttle reasons sampled DURING the timed regions (NVML, every 20 ms;
+    nvidia-smi as a fallback)."""
 
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -73,8 +84,38 @@ class ClockSampler:
     def __init__(self, index: int):
         self.index, self.samples, self.stop = index, [], threading.Event()
         self.thread = threading.Thread(target=self.run, daemon=True)
+        self.nvml = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            # NVML indexes physical devices; honour CUDA_VISIBLE_DEVICES when it lists indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = index
+            if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                phys = int(vis.split(",")[index])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
 
     def run(self):
+        if self.nvml is not None:
+            nv = self.nvml
+            bits = [("hw_slowdown", nv.nvmlClocksThrottleReasonHwSlowdown),
+                    ("hw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                    ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap)]
+            while not self.stop.is_set():
+                try:
+                    sm = nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                    self.samples.append([str(sm), str(self.max_sm)] + ["Active" if r & b else "Not Active" for _, b in bits])
+                except Exception:
+                    pass
+                self.stop.wait(0.02)
+            return
         while not self.stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
@@ -95,12 +136,12 @@ class ClockSampler:
 
     def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock samples"]}
         sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [nm for k, nm in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.samples[0][1]),
-                "reasons": reasons, "samples": len(self.samples)}
+                "reasons": reasons, "samples": len(self.samples), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def unpack_text(enc: np.ndarray, sites: int):
@@ -263,21 +304,25 @@ def main():
     algo_bytes_per_pass = (3 * n - 6) * 8 * my_words  # 24 B per node-word update, SURVEY.md §8(d)
 
     length0 = eng.commit(tree, topo)
-    for _ in range(max(3, args.warmup)):
+    warm = max(3, args.warmup)
+    for _ in range(warm):
         eng.rerun_last_batch()
     eng.synchronize()
 
     with ClockSampler(local_rank) as clocks:
-        # ---- region A: device-resident ----
+        # ---- region A: device-resident; CUDA events on the engine's own stream ----
+        ext = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = eng.launches
         eng.kernel_time(reset=True)
         barrier()
-        t0 = time.perf_counter()
+        ev0.record(ext)
         for _ in range(args.steps):
             eng.rerun_last_batch()
+        ev1.record(ext)
         eng.synchronize()
         barrier()
-        wall_a = max_over_ranks(time.perf_counter() - t0)
+        wall_a = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
         k_ms, k_launch = eng.kernel_time()
         gpu_launches = eng.launches - l0
         kernel_ms = max_over_ranks(k_ms / max(1, k_launch))
@@ -320,8 +365,9 @@ def main():
     achieved = algo_bytes_per_pass / (kernel_ms * 1e-3) / 1e9
     instr_bytes = (n - 1) * 16
 
+    traffic, traffic_src = traffic_from_profile()
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
         "ms_per_step": wall_a / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong" if siteblock else "weak", "vs_baseline": None, "dtype": "u64 (4-bit state sets, 32-bit lanes)",
         "data": "synthetic",
@@ -338,7 +384,9 @@ def main():
                 "api": "lvb_gpu_tree_commit(host left/right/root -> length), a different random tree every step"},
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "fitch_exec_kernel<true> (all levels of one pass)",
+                     "traffic": traffic, "traffic_source": traffic_src, "traffic_unit": "DRAM bytes per pass (ncu)",
+                     "peak_source": peak_src, "kernel": "fitch_exec_kernel<true> (one launch per pass)",
+                     "timing": "CUDA events on the engine's stream around each launch, averaged over the timed steps",
                      "kernel_ms_per_pass": kernel_ms,
                      "algorithmic_bytes_per_pass": algo_bytes_per_pass,
                      "note": "algorithmic = 24 B per node-word update (2 reads + 1 write); the kernel keeps "

@@ -371,7 +371,7 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
 }
 
 /* one CTA per program of a store-mode batch */
-__global__ void __launch_bounds__(128) fitch_commit_finalize_kernel(const FitchInstr *instr, const FitchProgram *progs,
+__global__ void __launch_bounds__(1024) fitch_commit_finalize_kernel(const FitchInstr *instr, const FitchProgram *progs,
                                                                     int32_t *cnts, int32_t *chg,
                                                                     long long *sum_chg, int n, int n_internal,
                                                                     long long *lengths)
@@ -420,9 +420,12 @@ __global__ void __launch_bounds__(128) fitch_commit_finalize_kernel(const FitchI
 
 cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
-                                   cudaStream_t stream)
+                                   int max_instr, cudaStream_t stream)
 {
-    fitch_commit_finalize_kernel<<<n_prog, 128, 0, stream>>>(instr, prog, cnts, chg, sum_chg, n, n_internal, lengths);
+    /* one thread per instruction of the longest program where possible: the loads are dependent
+     * (instruction -> count, cached count), so width, not work, sets the duration */
+    const int threads = max_instr >= 1024 ? 1024 : max_instr <= 128 ? 128 : (max_instr + 31) / 32 * 32;
+    fitch_commit_finalize_kernel<<<n_prog, threads, 0, stream>>>(instr, prog, cnts, chg, sum_chg, n, n_internal, lengths);
     return cudaGetLastError();
 }
 

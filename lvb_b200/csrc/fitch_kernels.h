@@ -43,7 +43,7 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
  * lengths[p] <- sum_chg[tree] + root step counts.  Trees of the batch must be distinct. */
 cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
-                                   cudaStream_t stream);
+                                   int max_instr, cudaStream_t stream);
 
 /* DNAToBinary on the device (reference: src/DataOperations.c:164-249).  text: n x m bytes
  * row-major; writes words [word_begin, word_begin + word_count) of each leaf row into the pool;

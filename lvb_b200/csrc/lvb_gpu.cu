@@ -161,6 +161,7 @@ struct lvb_gpu_ctx
     int last_slots = 0;
     int last_slot = -1;
     size_t last_n_instr = 0, last_n_prog = 0;
+    int last_max_instr = 0;
     /* device time of the Fitch kernel, accumulated over launches (events on the stream) */
     static const int kEvRing = 32;
     cudaEvent_t ring0[kEvRing] = {}, ring1[kEvRing] = {};
@@ -332,7 +333,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     if (store)
     {
         CU(launch_commit_finalize(d_instr, d_cand, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I, out,
-                                  c->stream));
+                                  c->last_max_instr, c->stream));
         c->launches++;
     }
     if (c->comm && (lengths || !store))
@@ -566,6 +567,9 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     c->last_slots = n_slots;
     c->last_slot = slot;
     c->last_n_instr = n_instr;
+    c->last_max_instr = 0;
+    for (int64_t k = 0; k < K; k++)
+        c->last_max_instr = std::max(c->last_max_instr, (int)c->c_instr[k].size());
     c->last_n_prog = n_prog;
     return launch_resident(c, lengths);
 }
