@@ -341,6 +341,188 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
     }
 }
 
+/* ---- score mode, deep pipeline -------------------------------------------------------------
+ * A proposal's program is a short chain (its dirty path): every instruction needs the result of
+ * the one before, but NONE of its HBM operands depends on a result — all addresses are known
+ * when the CTA starts.  With one instruction of look-ahead a CTA pays one memory latency per
+ * node, which is what a small batch (an SA chain scoring a few proposals per launch) is made
+ * of.  Here every thread streams its own 16-byte column of the operand rows through a private
+ * ring in shared memory with cp.async (LDGSTS), LVB_PF instructions ahead of the arithmetic;
+ * no cross-thread synchronisation is needed because a thread only ever reads what it fetched. */
+#define LVB_PF 3          /* instructions in flight ahead of the one being computed */
+#define LVB_RING 4        /* ring slots (LVB_PF + 1: a slot is refilled one step after it was read) */
+#define D_NOP 0x10000000u /* padding up to a multiple of LVB_RING (bit outside the slot-offset range) */
+
+__device__ __forceinline__ void cp_async16_if(unsigned dst, unsigned long long src, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t"
+                 "@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}"
+                 :
+                 : "r"(dst), "l"(src), "r"(pred)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
+{
+    extern __shared__ uint4 smem_u4[];
+    uint4 *s_instr = smem_u4; /* LVB_CHUNK + 2 * LVB_RING decoded instructions */
+    const int tid = threadIdx.x;
+    const int nthr = blockDim.x;
+    uint4 *s_ring = smem_u4 + LVB_CHUNK + 2 * LVB_RING; /* [LVB_RING][2][nthr] */
+    uint4 *s_stack = s_ring + LVB_RING * 2 * nthr;     /* [n_slots][nthr] */
+    __shared__ unsigned long long s_total;
+
+    /* column-block-major: CTAs of different programs over the same columns run together, so
+     * rows shared between candidates of one tree are served from L2 */
+    const int prog_id = blockIdx.x % p.n_prog;
+    const int cb = blockIdx.x / p.n_prog;
+    const FitchProgram prog = p.prog[prog_id];
+    const int col = cb * nthr + tid;
+    const unsigned amask = col < p.ncols ? ~0u : 0u;
+    const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
+    const FitchInstr *gi = p.instr + prog.instr_begin;
+    const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
+    const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
+    const unsigned slot_bytes = (unsigned)nthr * 16u;
+    const unsigned sa_instr = (unsigned)__cvta_generic_to_shared(s_instr);
+    const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
+    const unsigned sa_stack = (unsigned)__cvta_generic_to_shared(s_stack + tid);
+
+    if (tid == 0)
+        s_total = 0ull;
+    uint4 acc = make_uint4(~0u, ~0u, ~0u, ~0u);
+    unsigned total = 0;
+
+    for (int base = 0; base < prog.n_instr; base += LVB_CHUNK)
+    {
+        const int m = min(LVB_CHUNK, prog.n_instr - base);
+        const int m_pad = (m + LVB_RING - 1) / LVB_RING * LVB_RING;
+        __syncthreads();
+        for (int i = tid; i < m_pad + LVB_RING; i += nthr)
+        {
+            uint4 d = make_uint4(0u, 0u, 0u, D_APREV | D_NOP); /* padding: no loads, no arithmetic */
+            if (i < m)
+            {
+                const FitchInstr in = gi[base + i];
+                int a = in.a, b = in.b;
+                if (LVB_OPER_IS_SLOT(a) || b == LVB_OPER_PREV)
+                {
+                    const int t = a;
+                    a = b;
+                    b = t;
+                }
+                unsigned w = 0u;
+                const unsigned push = (in.ctl & LVB_CTL_PUSH_MASK) >> LVB_CTL_PUSH_SHIFT;
+                if (push)
+                    w |= D_PUSH | ((push - 1u) * slot_bytes);
+                if (a < 0)
+                {
+                    w |= D_APREV;
+                    a = 0;
+                }
+                else if (a >= p.n)
+                    a += tree_off;
+                if (b < 0)
+                {
+                    w |= D_BSLOT;
+                    b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
+                }
+                else if (b >= p.n)
+                    b += tree_off;
+                d = make_uint4((unsigned)a, (unsigned)b, 0u, w);
+            }
+            s_instr[i] = d;
+        }
+        __syncthreads();
+
+#define LVB_ISSUE(J, S)                                                                                               \
+    {                                                                                                                 \
+        const uint4 ni = lds128(sa_instr + (unsigned)(J) * 16u);                                                      \
+        cp_async16_if(sa_ring + (2u * (S)) * slot_bytes, row_addr(ni.x, stride_b, colbase), !(ni.w & D_APREV));       \
+        cp_async16_if(sa_ring + (2u * (S) + 1u) * slot_bytes, row_addr(ni.y, stride_b, colbase),            \
+                      !(ni.w & (D_BSLOT | D_NOP)));                                                                   \
+        cp_async_commit();                                                                                            \
+    }
+#define LVB_SCORE_STEP(J, S)                                                                                          \
+    {                                                                                                                 \
+        cp_async_wait<LVB_PF - 1>(); /* this thread's operands of instruction J have landed */                        \
+        const uint4 ci = lds128(sa_instr + (unsigned)(J) * 16u);                                                      \
+        uint4 y;                                                                                                      \
+        /* operand a: the previous result stays in acc, or acc is replaced by the fetched row */                      \
+        lds128_if(acc, sa_ring + (2u * (S)) * slot_bytes, !(ci.w & D_APREV));                                         \
+        y = lds128((ci.w & D_BSLOT) ? sa_stack + ci.y : sa_ring + (2u * (S) + 1u) * slot_bytes);                      \
+        LVB_ISSUE((J) + LVB_PF, ((S) + LVB_PF) % LVB_RING) /* refills the slot read one step ago */                   \
+        if (!(ci.w & D_NOP))                                                                                          \
+        {                                                                                                             \
+            const unsigned f = fitch_step(acc, y, acc) & amask;                                                       \
+            total += __popc(f);                                                                                       \
+            sts128_if(sa_stack + (ci.w & 0x0ffffff0u), acc, ci.w & D_PUSH);                                           \
+        }                                                                                                             \
+    }
+
+        LVB_ISSUE(0, 0)
+        LVB_ISSUE(1, 1)
+        LVB_ISSUE(2, 2)
+        for (int i = 0; i < m_pad; i += LVB_RING)
+        {
+            LVB_SCORE_STEP(i, 0)
+            LVB_SCORE_STEP(i + 1, 1)
+            LVB_SCORE_STEP(i + 2, 2)
+            LVB_SCORE_STEP(i + 3, 3)
+        }
+        cp_async_wait<0>();
+#undef LVB_SCORE_STEP
+#undef LVB_ISSUE
+    }
+
+    /* per-program length: block reduce, one 64-bit atomic per CTA */
+    const unsigned w = __reduce_add_sync(0xffffffffu, total);
+    if ((tid & 31) == 0 && w)
+        atomicAdd(&s_total, (unsigned long long)w);
+    __syncthreads();
+    if (cb == 0)
+    {
+        /* add the part of the length that does not change, once per program: sum of cached
+         * counts of clean nodes = sum_chg - sum over recomputed nodes of chg
+         * (reference: TreeEvaluation.c:191-202 adds .changes of every clean node) */
+        long long basev = 0;
+        const int32_t *chg = p.chg + (int64_t)prog.tree * p.n_internal;
+        for (int i = tid; i < prog.n_instr; i += nthr)
+        {
+            const int node = gi[i].node;
+            if (node >= 0)
+                basev -= chg[node - p.n];
+        }
+        for (int o = 16; o > 0; o >>= 1)
+            basev += __shfl_xor_sync(0xffffffffu, basev, o);
+        if ((tid & 31) == 0 && basev)
+            atomicAdd(&s_total, (unsigned long long)basev);
+        __syncthreads();
+        if (tid == 0)
+            s_total += (unsigned long long)p.sum_chg[prog.tree];
+    }
+    if (tid == 0)
+    {
+        /* the column block that finishes last publishes the length and leaves totals/done zero
+         * for the next batch: no memset before and no copy after the launch */
+        if (s_total)
+            atomicAdd(&p.totals[prog_id], s_total);
+        __threadfence();
+        if (atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u)
+        {
+            __threadfence();
+            p.out[prog_id] = (long long)atomicExch(&p.totals[prog_id], 0ull);
+            p.done[prog_id] = 0u;
+        }
+    }
+}
+
 static size_t exec_smem_bytes(bool per_node, int n_slots, int block)
 {
     return (size_t)(LVB_CHUNK + 2 + (per_node ? LVB_CHUNK * 8 / 4 : 0) + (size_t)n_slots * block) * sizeof(uint4);
@@ -359,13 +541,23 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
             return e;
         fitch_exec_kernel<true><<<grid, block, smem, stream>>>(p);
     }
-    else
+    else if (p.score_v1)
     {
         if (smem > 48 * 1024 &&
             (e = cudaFuncSetAttribute(fitch_exec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem)) != cudaSuccess)
             return e;
         fitch_exec_kernel<false><<<grid, block, smem, stream>>>(p);
+    }
+    else
+    {
+        const size_t smem2 =
+            (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(2 * LVB_RING + p.n_slots) * block) * sizeof(uint4);
+        if (smem2 > 48 * 1024 &&
+            (e = cudaFuncSetAttribute(fitch_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)) !=
+                cudaSuccess)
+            return e;
+        fitch_score_kernel<<<grid, block, smem2, stream>>>(p);
     }
     return cudaGetLastError();
 }

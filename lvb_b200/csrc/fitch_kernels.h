@@ -21,6 +21,7 @@ struct ExecParams
     int32_t n_prog;
     int32_t n_colblocks;
     int32_t n_slots;             /* stack slots of the deepest program in the batch */
+    int32_t score_v1;            /* score mode: use the one-instruction-look-ahead kernel (A/B switch) */
     const FitchInstr *instr;
     const FitchProgram *prog;
     unsigned long long *totals;  /* [n_prog] score mode: partial sums of the column blocks; left zero by the kernel */

@@ -23,6 +23,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -145,6 +146,7 @@ struct lvb_gpu_ctx
     size_t cap_tot = 0;
     unsigned *d_dep = nullptr;                         /* [cap_dep] + 1 ticket: dependency counters of one store launch; zero between */
     size_t cap_dep = 0;
+    bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
     bool last_dep = false;
     std::vector<int32_t> owner_stamp, owner_piece;     /* (tree, node) -> piece that stores it in the current batch */
@@ -171,7 +173,19 @@ struct lvb_gpu_ctx
 
     void *comm = nullptr;
     int nranks = 1, rank = 0;
+
+    /* LVB_GPU_PROFILE=1: host seconds per stage of commit/score calls, printed at shutdown */
+    bool profile = false;
+    double t_compile = 0, t_layout = 0, t_submit = 0, t_wait = 0;
+    int64_t n_calls = 0, n_cand_total = 0;
 };
+
+static inline double wall_now()
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
 
 static size_t grow(size_t have, size_t need, size_t start)
 {
@@ -295,6 +309,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     const int block = pick_block(c);
     p.n_colblocks = (int32_t)((c->stride_u4 + block - 1) / block);
     p.n_slots = c->last_slots;
+    p.score_v1 = c->score_v1 ? 1 : 0;
     p.instr = d_instr;
     p.totals = c->d_totals;
     p.done = c->d_done;
@@ -305,6 +320,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     p.chg = c->chg;
     p.sum_chg = c->sum_chg;
 
+    const double ts0 = c->profile ? wall_now() : 0;
     int slot = -1;
     if (c->timing)
     {
@@ -346,9 +362,14 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
     }
     CU(cudaEventRecord(st.done, c->stream));
     st.pending = true;
+    const double ts1 = c->profile ? wall_now() : 0;
+    if (c->profile)
+        c->t_submit += ts1 - ts0;
     if (lengths)
     {
         CU(cudaEventSynchronize(st.done));
+        if (c->profile)
+            c->t_wait += wall_now() - ts1;
         st.pending = false;
         for (int64_t k = 0; k < K; k++)
             lengths[k] = (int64_t)st.h_len[k];
@@ -366,6 +387,7 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         return 0;
     CU(cudaSetDevice(c->device));
     c->last_K = 0;
+    const double tp0 = c->profile ? wall_now() : 0;
     /* Large store programs are cut into independent subtrees so that enough warps are resident:
      * a program owns ceil(cols/32) warps per piece. */
     const int64_t warps_per_piece = (c->stride_u4 + 31) / 32;
@@ -435,6 +457,7 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         for (int64_t k = 0; k < K; k++)
             if (!c->c_err[k].empty())
                 return fail("candidate %lld: %s", (long long)k, c->c_err[k].c_str());
+    const double tp1 = c->profile ? wall_now() : 0;
 
     /* lay the batch out: [pieces sorted by level][one record per candidate][instructions] */
     size_t n_instr = 0, n_prog = 0;
@@ -571,6 +594,13 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     for (int64_t k = 0; k < K; k++)
         c->last_max_instr = std::max(c->last_max_instr, (int)c->c_instr[k].size());
     c->last_n_prog = n_prog;
+    if (c->profile)
+    {
+        c->t_compile += tp1 - tp0;
+        c->t_layout += wall_now() - tp1;
+        c->n_calls++;
+        c->n_cand_total += K;
+    }
     return launch_resident(c, lengths);
 }
 
@@ -702,6 +732,10 @@ extern "C"
         const char *tw = getenv("LVB_GPU_TARGET_WARPS");
         if (tw && atoll(tw) > 0)
             c->target_warps = atoll(tw);
+        const char *v1 = getenv("LVB_GPU_SCORE_V1");
+        c->score_v1 = v1 && atoi(v1) != 0;
+        const char *pf = getenv("LVB_GPU_PROFILE");
+        c->profile = pf && atoi(pf) != 0;
         const char *ll = getenv("LVB_GPU_LEVEL_LAUNCHES");
         c->level_launches = ll && atoi(ll) != 0;
         const char *b = getenv("LVB_GPU_BLOCK");
@@ -721,6 +755,10 @@ extern "C"
             return 0;
         cudaSetDevice(c->device);
         cudaStreamSynchronize(c->stream);
+        if (c->profile)
+            fprintf(stderr, "[lvb_gpu profile] %lld calls, %lld candidates: compile %.3f s, layout+H2D enqueue %.3f s, "
+                            "launch enqueue %.3f s, wait %.3f s\n", (long long)c->n_calls, (long long)c->n_cand_total,
+                    c->t_compile, c->t_layout, c->t_submit, c->t_wait);
         if (c->comm && g_nccl.CommDestroy)
             g_nccl.CommDestroy(c->comm);
         free_matrix(c);

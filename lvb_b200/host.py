@@ -140,17 +140,17 @@ class HostMSA:
                replicates: int = 1, speculation: int = 0, max_rearrangements: int = 0, host_threads: int = 1,
                tsv_path: Optional[str] = None, outtree_path: Optional[str] = None):
         """GetSoln for `replicates` chains; returns a list of dicts (one per chain)."""
-        out = np.zeros(6 * replicates, dtype=np.int64)
+        out = np.zeros(7 * replicates, dtype=np.int64)
         t0 = np.zeros(replicates, dtype=np.float64)
         secs = C.c_double(0)
         _check(self.L.lvbh_search(self.h, device, seed, algorithm, cooling, max_trees, replicates, speculation,
                                   max_rearrangements, host_threads, tsv_path.encode() if tsv_path else None,
                                   outtree_path.encode() if outtree_path else None, out.ctypes.data, t0.ctypes.data,
                                   C.byref(secs)))
-        keys = ("final_length", "rearrangements", "topologies", "initial_length", "trees_scored", "score_launches")
+        keys = ("final_length", "rearrangements", "topologies", "initial_length", "trees_scored", "score_launches", "groups")
         res = []
         for r in range(replicates):
-            d = {k: int(out[6 * r + i]) for i, k in enumerate(keys)}
+            d = {k: int(out[7 * r + i]) for i, k in enumerate(keys)}
             d["start_temperature"] = float(t0[r])
             d["seconds"] = float(secs.value)
             res.append(d)

@@ -258,7 +258,7 @@ long lvbh_getplen(void *hv, void *t, long root)
 }
 
 /* ---- the search: GetSoln for `replicates` chains on one device.
- * out (per chain, 6 longs): final length, rearrangements, topologies, initial length, trees scored, score launches
+ * out (per chain, 7 longs): final length, rearrangements, topologies, initial length, trees scored, score launches, groups
  * start_t (per chain): starting temperature.  tsv_path / outtree_path may be NULL (chain 0 only;
  * further chains write outtree_path.r<k>). ---- */
 int lvbh_search(void *hv, int device, int seed, int algorithm, int cooling, int max_trees_kept, int replicates,
@@ -287,12 +287,13 @@ int lvbh_search(void *hv, int device, int seed, int algorithm, int cooling, int 
             fclose(tsv);
         for (int r = 0; r < replicates; r++)
         {
-            out[6 * r + 0] = results[(size_t)r].final_length;
-            out[6 * r + 1] = results[(size_t)r].rearrangements;
-            out[6 * r + 2] = stacks[(size_t)r].next;
-            out[6 * r + 3] = results[(size_t)r].initial_length;
-            out[6 * r + 4] = results[(size_t)r].getplen_calls;
-            out[6 * r + 5] = results[(size_t)r].launches_scored;
+            out[7 * r + 0] = results[(size_t)r].final_length;
+            out[7 * r + 1] = results[(size_t)r].rearrangements;
+            out[7 * r + 2] = stacks[(size_t)r].next;
+            out[7 * r + 3] = results[(size_t)r].initial_length;
+            out[7 * r + 4] = results[(size_t)r].getplen_calls;
+            out[7 * r + 5] = results[(size_t)r].launches_scored;
+            out[7 * r + 6] = results[(size_t)r].groups;
             start_t[r] = results[(size_t)r].start_temperature;
             if (outtree_path)
             {

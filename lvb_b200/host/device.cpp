@@ -14,22 +14,31 @@ static void gpu_check(int rc)
         crash("GPU error: %s", lvb_gpu_last_error()); /* errors of the device layer surface as crash(), src/Error.c:49 */
 }
 
-int64_t Device::launches() const { return ctx ? lvb_gpu_launch_count(ctx) : 0; }
+int64_t Device::launches() const { return (ctx ? lvb_gpu_launch_count(ctx) : 0) + extra_launches; }
 
 /* Main.c:82 lvb_initialize() + Solve.c:516-519 (enc_mat, DNAToBinary): the packed leaf rows
  * are built once with the reference's layout and live on the device from here on */
 void device_open(Device &dev, int device_index, Dataptr MSA, int max_trees, int64_t word_begin, int64_t word_count)
 {
-    dev.MSA = MSA;
-    gpu_check(lvb_gpu_init(device_index, &dev.ctx));
     std::vector<Lvb_bit_length> flat((size_t)MSA->n * (size_t)MSA->nwords);
     std::vector<Lvb_bit_length *> rows((size_t)MSA->n);
     for (long i = 0; i < MSA->n; i++)
         rows[(size_t)i] = flat.data() + (size_t)i * (size_t)MSA->nwords;
     DNAToBinary(MSA, rows.data());
+    device_open_encoded(dev, device_index, MSA, rows.data(), max_trees, word_begin, word_count);
+}
+
+/* the same with the DNAToBinary rows already made (several contexts on one alignment) */
+void device_open_encoded(Device &dev, int device_index, Dataptr MSA, Lvb_bit_length *const *rows, int max_trees,
+                         int64_t word_begin, int64_t word_count)
+{
+    dev.MSA = MSA;
+    dev.index = device_index;
+    gpu_check(lvb_gpu_init(device_index, &dev.ctx));
     if (word_count < 0)
         word_count = MSA->nwords - word_begin;
-    gpu_check(lvb_gpu_matrix_upload(dev.ctx, MSA->n, MSA->nwords, (const uint64_t *const *)rows.data(), word_begin,
+    dev.word_count = word_count;
+    gpu_check(lvb_gpu_matrix_upload(dev.ctx, MSA->n, MSA->nwords, (const uint64_t *const *)rows, word_begin,
                                     word_count, max_trees));
 }
 

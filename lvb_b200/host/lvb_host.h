@@ -108,6 +108,7 @@ struct Parameters
     int device = 0;            /* CUDA device of a single-chain run */
     int speculation = 0;       /* max proposals scored per launch and chain; 0 = adaptive */
     int replicates = 1;        /* independent SA chains (seed, seed+1, ...) */
+    int groups = 0;            /* device contexts / host driver threads the chains are spread over; 0 = auto */
     long max_rearrangements = 0; /* > 0: stop every chain after this many proposals (benchmarks) */
 };
 
@@ -209,11 +210,16 @@ struct Device
 {
     lvb_gpu_ctx *ctx = nullptr;
     Dataptr MSA = nullptr;
+    int index = 0;              /* CUDA device */
+    int64_t word_count = -1;    /* words of every row this context holds (site-block mode: fewer than nwords) */
+    int64_t extra_launches = 0; /* launches of the additional contexts GetSolnBatched opened on this device */
     int64_t launches() const;
 };
 /* lvb_gpu_init + DNAToBinary + lvb_gpu_matrix_upload; crash() on any device error */
 void device_open(Device &dev, int device_index, Dataptr MSA, int max_trees, int64_t word_begin = 0,
                  int64_t word_count = -1);
+void device_open_encoded(Device &dev, int device_index, Dataptr MSA, Lvb_bit_length *const *rows, int max_trees,
+                         int64_t word_begin = 0, int64_t word_count = -1);
 void device_close(Device &dev);
 
 /* ---- getplen: src/TreeEvaluation.c:49-270, same signature (the scratch pointers are
@@ -248,6 +254,8 @@ struct SearchResult
     double seconds = 0;
     double prof[4] = {0, 0, 0, 0}; /* seconds in: proposal generation, commit calls, score calls, acceptance replay */
     long rounds = 0;
+    int groups = 1;                /* device contexts / driver threads used */
+    double setup_seconds = 0;      /* part of `seconds` spent opening the additional contexts */
 };
 struct Chain; /* one SA replicate: solve.cpp */
 

@@ -5,9 +5,11 @@
  *   -d <int>  CUDA device            -R <int>  independent SA replicates (seeds s, s+1, ...)
  *   -K <int>  proposals scored per launch and chain (0 = adaptive)
  *   -x <int>  stop after this many rearrangements (benchmarking)
+ *   -G <int>  device contexts / driver threads the replicates are spread over (0 = auto)
  */
 #include <ctime>
 #include <getopt.h>
+#include <omp.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -41,6 +43,7 @@ static void usage()
     printf("    CUDA device                       -d [VALUE]          default: 0\n");
     printf("    Independent SA replicates         -R [VALUE]          seeds s, s+1, ...; default: 1\n");
     printf("    Proposals per launch and chain    -K [VALUE]          default: adaptive\n");
+    printf("    Driver threads / device contexts  -G [VALUE]          default: about one per 4 replicates\n");
     printf("    Maximum trees kept                -t [VALUE]\n\n");
     exit(0);
 }
@@ -50,10 +53,10 @@ static void getparam(Parameters &p, int argc, char **argv)
 {
     const time_t tim = time(nullptr);
     p.seed = (int)((unsigned long)tim % 900000001UL);
-    p.n_processors_available = 1;
+    p.n_processors_available = omp_get_max_threads(); /* SearchParameters.c:86: all cores unless -p */
     int c;
     opterr = 0;
-    while ((c = getopt(argc, argv, "t:c:b:vs:i:o:f:a:p:N:SC:h?d:R:K:x:")) != -1)
+    while ((c = getopt(argc, argv, "t:c:b:vs:i:o:f:a:p:N:SC:h?d:R:K:x:G:")) != -1)
     {
         switch (c)
         {
@@ -94,7 +97,7 @@ static void getparam(Parameters &p, int argc, char **argv)
         case 'p':
             p.n_processors_available = atoi(optarg);
             if (p.n_processors_available < 1)
-                p.n_processors_available = 1;
+                p.n_processors_available = omp_get_max_threads(); /* SearchParameters.c:86: all cores unless -p */
             break;
         case 't':
             p.n_number_max_trees = atoi(optarg);
@@ -105,6 +108,7 @@ static void getparam(Parameters &p, int argc, char **argv)
         case 'R': p.replicates = atoi(optarg) < 1 ? 1 : atoi(optarg); break;
         case 'K': p.speculation = atoi(optarg) < 0 ? 0 : atoi(optarg); break;
         case 'x': p.max_rearrangements = atol(optarg); break;
+        case 'G': p.groups = atoi(optarg) < 0 ? 0 : atoi(optarg); break;
         default: usage();
         }
     }
@@ -134,7 +138,7 @@ static void writeinf(const Parameters &p, Dataptr MSA, int argc, char **argv)
     else
         printf("          2 (PBS)\n");
     printf("\nParallelisation Properties: \n");
-    printf("  PThreads:            %d\n", p.n_processors_available); /* accepted for compatibility; scoring runs on the GPU */
+    printf("  PThreads:            %d\n", p.n_processors_available); /* host threads: chains are advanced in parallel; scoring runs on the GPU */
     printf("  GPU:                 device %d, %d SA replicate(s)\n", p.device, p.replicates);
     printf("\n================================================================================\n");
     printf("\nInitialising search: \n");
@@ -213,10 +217,16 @@ int main(int argc, char **argv)
     for (int r = 1; r < rc.replicates; r++)
         printf("  Replicate %d (seed %d): score %ld, %ld topologies, %ld rearrangements\n", r, rc.seed + r,
                results[(size_t)r].final_length, (long)stacks[(size_t)r].next, results[(size_t)r].rearrangements);
+    long all_scored = 0;
+    for (int r = 0; r < rc.replicates; r++)
+        all_scored += results[(size_t)r].getplen_calls;
     printf("  Wall time of the search:  %.3lf s; trees scored: %ld in %ld launches; kernel launches: %ld\n",
            results[0].seconds, results[0].getplen_calls, results[0].launches_scored, (long)dev.launches());
-    printf("  Host time split (s):      propose %.3f, commit calls %.3f, score calls %.3f, replay %.3f; %ld rounds\n",
-           results[0].prof[0], results[0].prof[1], results[0].prof[2], results[0].prof[3], results[0].rounds);
+    printf("  All replicates:           %ld trees scored, %.0f per second\n", all_scored,
+           results[0].seconds > 0 ? all_scored / results[0].seconds : 0.0);
+    printf("  Host time split (s):      propose %.3f, commit calls %.3f, score calls %.3f, replay %.3f; %ld rounds; %d group(s), set up in %.3f s\n",
+           results[0].prof[0], results[0].prof[1], results[0].prof[2], results[0].prof[3], results[0].rounds,
+           results[0].groups, results[0].setup_seconds);
     printf("\nAll topologies written to '%s'\n", rc.file_name_out.c_str());
     device_close(dev);
     return fflush(stdout) == 0 ? EXIT_SUCCESS : EXIT_FAILURE;

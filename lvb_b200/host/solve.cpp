@@ -25,6 +25,7 @@
 #include <cerrno>
 #include <cfloat>
 #include <chrono>
+#include <thread>
 #include <cmath>
 #include <algorithm>
 #include <cstring>
@@ -597,45 +598,20 @@ static void gpu_check(int rc_)
 }
 
 /* src/Solve.c:481-609 for R chains at once */
-void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicates, std::vector<TREESTACK> &stacks,
-                    std::vector<SearchResult> &results, std::vector<TrajectoryRow> *trajectory, FILE *tsv)
+/* One group of chains [r0, r1) on one device context, driven by the calling thread (its inner
+ * loops over chains use `threads` OpenMP threads).  Rounds: advance every chain (speculative
+ * proposals), one commit launch for the chains whose device tree must catch up, one score launch
+ * for all proposals, replay. */
+static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int r0, int r1, int threads,
+                      long &score_launches, long &rounds, double prof[4])
 {
-    const auto t_start = std::chrono::steady_clock::now();
-    const int R = replicates;
-    stacks.assign((size_t)R, TREESTACK());
-    results.assign((size_t)R, SearchResult());
-    std::vector<Chain> chains((size_t)R);
-    FILE *sumfp = nullptr;
-    if (rc.verbose)
-    {
-        sumfp = fopen("sum", "w");
-        if (sumfp)
-            fprintf(sumfp, "StartNo\tCycleNo\tCycInit\tCycBest\tCycTrees\n");
-    }
-    for (int r = 0; r < R; r++)
-    {
-        int t = -1;
-        gpu_check(lvb_gpu_tree_create(dev.ctx, &t));
-        chains[(size_t)r].init(MSA, rc, r, t, rc.speculation);
-        chains[(size_t)r].stack = &stacks[(size_t)r];
-        if (r == 0)
-        {
-            chains[0].log_progress = true;
-            chains[0].trajectory = trajectory;
-            chains[0].tsv = tsv;
-            chains[0].sumfp = sumfp;
-        }
-    }
     std::vector<int> trees;
     std::vector<lvb_gpu_topology> topos;
-    std::vector<int64_t> lens, clen((size_t)R, 0);
+    std::vector<int64_t> lens, clen((size_t)(r1 - r0), 0);
     std::vector<int> owner;
     std::vector<size_t> offsets;
-    const int host_threads = std::max(1, std::min(R, rc.n_processors_available));
-    long score_launches = 0;
     const size_t stride = sizeof(TREESTACK_TREE_NODES);
-    double prof[4] = {0, 0, 0, 0};
-    long rounds = 0;
+    (void)MSA;
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto since = [](std::chrono::steady_clock::time_point a) {
         return std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
@@ -646,8 +622,8 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         auto tp0 = now();
         /* chains are independent between device calls: spread them over the host threads (-p) */
         std::string failure;
-#pragma omp parallel for schedule(dynamic, 1) num_threads(host_threads) if (host_threads > 1)
-        for (int r = 0; r < R; r++)
+#pragma omp parallel for schedule(dynamic, 1) num_threads(threads) if (threads > 1)
+        for (int r = r0; r < r1; r++)
         {
             try
             {
@@ -661,8 +637,8 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         }
         if (!failure.empty())
             crash("%s", failure.c_str());
-        for (auto &c : chains)
-            alive = alive || c.S.phase != PH_DONE;
+        for (int r = r0; r < r1; r++)
+            alive = alive || chains[(size_t)r].S.phase != PH_DONE;
         prof[0] += since(tp0);
         rounds++;
         tp0 = now();
@@ -671,7 +647,7 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         topos.clear();
         owner.clear();
         bool want = false;
-        for (int r = 0; r < R; r++)
+        for (int r = r0; r < r1; r++)
         {
             Chain &c = chains[(size_t)r];
             if (!c.commit.used)
@@ -697,7 +673,7 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             {
                 Chain &c = chains[(size_t)owner[i]];
                 if (c.commit.want_length)
-                    clen[(size_t)owner[i]] = lens[i];
+                    clen[(size_t)(owner[i] - r0)] = lens[i];
                 c.commit.used = c.commit.all = c.commit.want_length = false;
                 c.commit.dirty.clear();
             }
@@ -709,7 +685,7 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         /* proposals of all chains in one launch */
         trees.clear();
         topos.clear();
-        for (int r = 0; r < R; r++)
+        for (int r = r0; r < r1; r++)
         {
             Chain &c = chains[(size_t)r];
             for (int k = 0; k < c.n_spec; k++)
@@ -738,19 +714,19 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         }
         prof[2] += since(tp0);
         tp0 = now();
-        offsets.resize((size_t)R);
+        offsets.resize((size_t)(r1 - r0));
         size_t off = 0;
-        for (int r = 0; r < R; r++)
+        for (int r = r0; r < r1; r++)
         {
-            offsets[(size_t)r] = off;
+            offsets[(size_t)(r - r0)] = off;
             off += (size_t)chains[(size_t)r].n_spec;
         }
-#pragma omp parallel for schedule(dynamic, 1) num_threads(host_threads) if (host_threads > 1)
-        for (int r = 0; r < R; r++)
+#pragma omp parallel for schedule(dynamic, 1) num_threads(threads) if (threads > 1)
+        for (int r = r0; r < r1; r++)
         {
             try
             {
-                chains[(size_t)r].resolve(&clen[(size_t)r], lens.data() + offsets[(size_t)r]);
+                chains[(size_t)r].resolve(&clen[(size_t)(r - r0)], lens.data() + offsets[(size_t)(r - r0)]);
             }
             catch (const LvbError &e)
             {
@@ -762,16 +738,108 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             crash("%s", failure.c_str());
         prof[3] += since(tp0);
     }
-    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
-    for (int r = 0; r < R; r++)
+}
+
+/* GetSoln for R independent replicates.  The chains are split into G groups; every group has
+ * its own device context (own stream, own copy of the leaf rows) and its own host thread, so
+ * that one group's host work (proposing, replaying, compiling schedules) overlaps the other
+ * groups' kernels.  Chain r uses seed rc.seed + r whatever the grouping: results do not depend
+ * on G (tested). */
+void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicates, std::vector<TREESTACK> &stacks,
+                    std::vector<SearchResult> &results, std::vector<TrajectoryRow> *trajectory, FILE *tsv)
+{
+    const auto t_start = std::chrono::steady_clock::now();
+    const int R = replicates;
+    stacks.assign((size_t)R, TREESTACK());
+    results.assign((size_t)R, SearchResult());
+    std::vector<Chain> chains((size_t)R);
+    FILE *sumfp = nullptr;
+    if (rc.verbose)
     {
-        results[(size_t)r] = chains[(size_t)r].res;
-        results[(size_t)r].launches_scored = score_launches;
-        results[(size_t)r].seconds = secs;
-        results[(size_t)r].rounds = rounds;
-        for (int i = 0; i < 4; i++)
-            results[(size_t)r].prof[i] = prof[i];
-        gpu_check(lvb_gpu_tree_destroy(dev.ctx, chains[(size_t)r].dev_tree));
+        sumfp = fopen("sum", "w");
+        if (sumfp)
+            fprintf(sumfp, "StartNo\tCycleNo\tCycInit\tCycBest\tCycTrees\n");
+    }
+    const int host_threads = std::max(1, rc.n_processors_available);
+    /* auto: about 8 chains per group, at most 4 groups — measured on a 16-core host with one B200:
+     * 64 chains of 1000 x 200k run 1.0 / 1.4 / 1.7 / 1.3 / 1.1 times the single-group rate with
+     * 1 / 2 / 4 / 8 / 16 groups (more driver threads contend in the CUDA driver) */
+    int G = rc.groups > 0 ? rc.groups : std::min(std::min(host_threads, 4), (R + 7) / 8);
+    G = std::max(1, std::min(G, R));
+    if (dev.word_count >= 0 && dev.word_count != MSA->nwords)
+        G = 1; /* site-block mode: one context per rank, the all-reduce keeps the ranks in lock-step */
+    std::vector<Device> extra((size_t)G);
+    std::vector<int> first((size_t)G + 1);
+    for (int g = 0; g <= G; g++)
+        first[(size_t)g] = (int)((long)R * g / G);
+    if (G > 1)
+    { /* the extra contexts hold their own copy of the leaf rows: encode once, upload G-1 times */
+        std::vector<Lvb_bit_length> flat((size_t)MSA->n * (size_t)MSA->nwords);
+        std::vector<Lvb_bit_length *> rows((size_t)MSA->n);
+        for (long i = 0; i < MSA->n; i++)
+            rows[(size_t)i] = flat.data() + (size_t)i * (size_t)MSA->nwords;
+        DNAToBinary(MSA, rows.data());
+        for (int g = 1; g < G; g++)
+            device_open_encoded(extra[(size_t)g], dev.index, MSA, rows.data(), first[(size_t)g + 1] - first[(size_t)g]);
+    }
+    const double setup_secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
+    auto device_of = [&](int g) -> Device & { return g == 0 ? dev : extra[(size_t)g]; };
+    for (int g = 0; g < G; g++)
+        for (int r = first[(size_t)g]; r < first[(size_t)g + 1]; r++)
+        {
+            int t = -1;
+            gpu_check(lvb_gpu_tree_create(device_of(g).ctx, &t));
+            chains[(size_t)r].init(MSA, rc, r, t, rc.speculation);
+            chains[(size_t)r].stack = &stacks[(size_t)r];
+            if (r == 0)
+            {
+                chains[0].log_progress = true;
+                chains[0].trajectory = trajectory;
+                chains[0].tsv = tsv;
+                chains[0].sumfp = sumfp;
+            }
+        }
+    struct GroupStat
+    {
+        long score_launches = 0, rounds = 0;
+        double prof[4] = {0, 0, 0, 0};
+    };
+    std::vector<GroupStat> stat((size_t)G);
+    const int inner = std::max(1, host_threads / G);
+    if (G == 1)
+        run_group(MSA, dev, chains, 0, R, std::min(inner, R), stat[0].score_launches, stat[0].rounds, stat[0].prof);
+    else
+    {
+        std::vector<std::thread> workers;
+        for (int g = 0; g < G; g++)
+            workers.emplace_back([&, g] {
+                run_group(MSA, device_of(g), chains, first[(size_t)g], first[(size_t)g + 1],
+                          std::min(inner, first[(size_t)g + 1] - first[(size_t)g]), stat[(size_t)g].score_launches,
+                          stat[(size_t)g].rounds, stat[(size_t)g].prof);
+            });
+        for (auto &w : workers)
+            w.join();
+    }
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
+    for (int g = 0; g < G; g++)
+    {
+        for (int r = first[(size_t)g]; r < first[(size_t)g + 1]; r++)
+        {
+            results[(size_t)r] = chains[(size_t)r].res;
+            results[(size_t)r].launches_scored = stat[(size_t)g].score_launches;
+            results[(size_t)r].seconds = secs;
+            results[(size_t)r].rounds = stat[(size_t)g].rounds;
+            results[(size_t)r].groups = G;
+            results[(size_t)r].setup_seconds = setup_secs;
+            for (int i = 0; i < 4; i++)
+                results[(size_t)r].prof[i] = stat[(size_t)g].prof[i];
+            gpu_check(lvb_gpu_tree_destroy(device_of(g).ctx, chains[(size_t)r].dev_tree));
+        }
+        if (g > 0)
+        {
+            dev.extra_launches += extra[(size_t)g].launches();
+            device_close(extra[(size_t)g]);
+        }
     }
     if (sumfp)
     {

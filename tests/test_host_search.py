@@ -70,3 +70,22 @@ def test_replicates_are_independent_chains():
         assert multi["outtrees"][r] == single["outtrees"][0]
         if r == 0:
             assert multi["tsv_md5"] == single["tsv_md5"]
+
+
+def test_chain_groups_do_not_change_the_result():
+    """9 chains, 4 host threads -> 2 groups, each with its own device context and driver thread
+    (GetSolnBatched); chain r is still the single-chain run with seed s + r"""
+    p = subprocess.run([sys.executable, os.path.join(HERE, "run_host_search.py"), "--mock", "treelength.npz:tl5_thread_2_text",
+                        "7", "1", "0", "9", "0", "4"], capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, p.stderr[-2000:]
+    multi = json.loads(p.stdout.strip().splitlines()[-1])
+    assert multi["results"][0]["groups"] == 2
+    for r in (3, 4, 8):
+        q = subprocess.run([sys.executable, os.path.join(HERE, "run_host_search.py"), "--mock",
+                            "treelength.npz:tl5_thread_2_text", str(7 + r), "1"], capture_output=True, text=True, timeout=900)
+        assert q.returncode == 0, q.stderr[-2000:]
+        single = json.loads(q.stdout.strip().splitlines()[-1])
+        a, b = multi["results"][r], single["results"][0]
+        for k in ("final_length", "rearrangements", "topologies", "initial_length", "start_temperature"):
+            assert a[k] == b[k], (r, k)
+        assert multi["outtrees"][r] == single["outtrees"][0]
