@@ -287,8 +287,10 @@ def main():
     eng = Engine(local_rank)
     enc = synthetic.random_packed(n, nwords, seed=1)
     if siteblock:
-        w0, w1 = nwords * rank // world, nwords * (rank + 1) // world
-        eng.upload(enc, word_begin=w0, word_count=w1 - w0, max_trees=1)
+        from lvb_b200 import sharding
+
+        w0, wc = sharding.word_block(nwords, rank, world)
+        eng.upload(enc, word_begin=w0, word_count=wc, max_trees=1)
         uid = [Engine.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         eng.comm_init(world, rank, uid[0])

@@ -74,24 +74,44 @@ int lvb_gpu_shutdown(lvb_gpu_ctx *c)
 int lvb_gpu_matrix_upload(lvb_gpu_ctx *c, int64_t n, int64_t nwords, const uint64_t *const *enc_rows, int64_t word_begin,
                           int64_t word_count, int64_t max_trees)
 {
-    if (word_begin != 0 || word_count != nwords)
-        return fail("site blocks are not mocked");
+    if (word_begin < 0 || word_count < 1 || word_begin + word_count > nwords)
+        return fail("bad word block");
+    /* a site block is simply a narrower alignment: words [word_begin, word_begin + word_count) */
     c->n = n;
-    c->nwords = nwords;
+    c->nwords = word_count;
     c->B = 2 * n - 3;
     c->I = n - 3;
     c->max_trees = max_trees;
-    c->leaves = (uint64_t *)malloc((size_t)n * nwords * 8);
+    c->leaves = (uint64_t *)malloc((size_t)n * word_count * 8);
     for (long i = 0; i < n; i++)
-        memcpy(c->leaves + i * nwords, enc_rows[i], (size_t)nwords * 8);
+        memcpy(c->leaves + i * word_count, enc_rows[i] + word_begin, (size_t)word_count * 8);
     c->rows = (uint64_t **)calloc((size_t)max_trees, sizeof(uint64_t *));
     c->changes = (long **)calloc((size_t)max_trees, sizeof(long *));
     c->used = (char *)calloc((size_t)max_trees, 1);
     c->ready = (char *)calloc((size_t)max_trees, 1);
     c->left = (long *)malloc((size_t)c->B * sizeof(long));
     c->right = (long *)malloc((size_t)c->B * sizeof(long));
-    c->scratch = (uint64_t *)malloc((size_t)c->B * nwords * 8);
+    c->scratch = (uint64_t *)malloc((size_t)c->B * word_count * 8);
     c->scratch_chg = (long *)malloc((size_t)c->B * sizeof(long));
+    return 0;
+}
+
+int lvb_gpu_matrix_upload_flat(lvb_gpu_ctx *c, int64_t n, int64_t nwords, const uint64_t *enc, int64_t word_begin,
+                               int64_t word_count, int64_t max_trees)
+{
+    const uint64_t **rows = (const uint64_t **)malloc((size_t)n * sizeof(*rows));
+    for (long i = 0; i < n; i++)
+        rows[i] = enc + i * nwords;
+    const int rc = lvb_gpu_matrix_upload(c, n, nwords, rows, word_begin, word_count, max_trees);
+    free(rows);
+    return rc;
+}
+
+/* cached change counts of all 2n-3 nodes of this context's block */
+int lvb_gpu_tree_changes(lvb_gpu_ctx *c, int tree, int64_t *changes)
+{
+    for (long v = 0; v < c->B; v++)
+        changes[v] = v < c->n ? 0 : c->changes[tree][v];
     return 0;
 }
 
