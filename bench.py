@@ -359,6 +359,11 @@ def main():
         eng.synchronize()
         c_ms, c_launch = eng.kernel_time()
         dirty_mean = float(np.mean([len(c.dirty) for c in cands]))
+        # rows each candidate's program reads from HBM/L2 (operands >= 0), from the host compiler
+        from lvb_b200 import compile_schedule
+
+        rows_read = [int((compile_schedule(n, c, store=False)[0][:, :2] >= 0).sum()) for c in cands[:64]]
+        rows_read_mean = float(np.mean(rows_read))
 
     total_ranks = 1 if siteblock else world
     value = total_ranks * args.steps * updates_per_pass / wall_a
@@ -399,6 +404,16 @@ def main():
             "device": total_ranks * len(cands) / (c_ms / max(1, c_launch) * 1e-3),
             "batch": len(cands), "mean_dirty_nodes": dirty_mean,
             "api": "lvb_gpu_score_batch: NNI candidates of the current tree, one launch per batch",
+        },
+        "roofline_score": {
+            "bound": "hbm (L2-assisted)", "unit": "GB/s", "peak": peak,
+            "achieved": rows_read_mean * 8 * my_words * len(cands) / (c_ms / max(1, c_launch) * 1e-3) / 1e9,
+            "frac": rows_read_mean * 8 * my_words * len(cands) / (c_ms / max(1, c_launch) * 1e-3) / 1e9 / peak,
+            "rows_read_per_candidate": rows_read_mean,
+            "kernel": "fitch_score_kernel", "kernel_ms_per_batch": c_ms / max(1, c_launch),
+            "note": "SURVEY.md 8(d): 8 B x nwords x (clean rows read) per candidate, nothing written; candidates "
+                    "of one tree share sibling rows, so part of this is served by L2 and the figure may exceed the "
+                    "HBM peak",
         },
         "length_check": int(length0), "e2e_lengths_head": [int(x) for x in lens[:3]],
     }

@@ -109,6 +109,7 @@ struct Parameters
     int speculation = 0;       /* max proposals scored per launch and chain; 0 = adaptive */
     int replicates = 1;        /* independent SA chains (seed, seed+1, ...) */
     int groups = 0;            /* device contexts / host driver threads the chains are spread over; 0 = auto */
+    int devices = 1;           /* GPUs (device, device+1, ...) the replicates are spread over */
     long max_rearrangements = 0; /* > 0: stop every chain after this many proposals (benchmarks) */
 };
 

@@ -6,6 +6,7 @@
  *   -K <int>  proposals scored per launch and chain (0 = adaptive)
  *   -x <int>  stop after this many rearrangements (benchmarking)
  *   -G <int>  device contexts / driver threads the replicates are spread over (0 = auto)
+ *   -D <int>  number of GPUs (device, device+1, ...) the replicates are spread over
  */
 #include <ctime>
 #include <getopt.h>
@@ -43,7 +44,8 @@ static void usage()
     printf("    CUDA device                       -d [VALUE]          default: 0\n");
     printf("    Independent SA replicates         -R [VALUE]          seeds s, s+1, ...; default: 1\n");
     printf("    Proposals per launch and chain    -K [VALUE]          default: adaptive\n");
-    printf("    Driver threads / device contexts  -G [VALUE]          default: about one per 4 replicates\n");
+    printf("    Driver threads / device contexts  -G [VALUE]          default: about one per 8 replicates, at most 4 per GPU\n");
+    printf("    GPUs used for the replicates      -D [VALUE]          devices d, d+1, ...; default: 1\n");
     printf("    Maximum trees kept                -t [VALUE]\n\n");
     exit(0);
 }
@@ -56,7 +58,7 @@ static void getparam(Parameters &p, int argc, char **argv)
     p.n_processors_available = omp_get_max_threads(); /* SearchParameters.c:86: all cores unless -p */
     int c;
     opterr = 0;
-    while ((c = getopt(argc, argv, "t:c:b:vs:i:o:f:a:p:N:SC:h?d:R:K:x:G:")) != -1)
+    while ((c = getopt(argc, argv, "t:c:b:vs:i:o:f:a:p:N:SC:h?d:R:K:x:G:D:")) != -1)
     {
         switch (c)
         {
@@ -109,6 +111,7 @@ static void getparam(Parameters &p, int argc, char **argv)
         case 'K': p.speculation = atoi(optarg) < 0 ? 0 : atoi(optarg); break;
         case 'x': p.max_rearrangements = atol(optarg); break;
         case 'G': p.groups = atoi(optarg) < 0 ? 0 : atoi(optarg); break;
+        case 'D': p.devices = atoi(optarg) < 1 ? 1 : atoi(optarg); break;
         default: usage();
         }
     }
@@ -139,7 +142,7 @@ static void writeinf(const Parameters &p, Dataptr MSA, int argc, char **argv)
         printf("          2 (PBS)\n");
     printf("\nParallelisation Properties: \n");
     printf("  PThreads:            %d\n", p.n_processors_available); /* host threads: chains are advanced in parallel; scoring runs on the GPU */
-    printf("  GPU:                 device %d, %d SA replicate(s)\n", p.device, p.replicates);
+    printf("  GPU:                 device %d (+%d more), %d SA replicate(s)\n", p.device, p.devices - 1, p.replicates);
     printf("\n================================================================================\n");
     printf("\nInitialising search: \n");
 }

@@ -761,11 +761,16 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             fprintf(sumfp, "StartNo\tCycleNo\tCycInit\tCycBest\tCycTrees\n");
     }
     const int host_threads = std::max(1, rc.n_processors_available);
-    /* auto: about 8 chains per group, at most 4 groups — measured on a 16-core host with one B200:
-     * 64 chains of 1000 x 200k run 1.0 / 1.4 / 1.7 / 1.3 / 1.1 times the single-group rate with
-     * 1 / 2 / 4 / 8 / 16 groups (more driver threads contend in the CUDA driver) */
-    int G = rc.groups > 0 ? rc.groups : std::min(std::min(host_threads, 4), (R + 7) / 8);
-    G = std::max(1, std::min(G, R));
+    /* Replicates are spread over rc.devices GPUs (device, device+1, ...: no communication between
+     * them, BASELINE.json configs[4]) and, on each GPU, over driver groups.  auto: about 8 chains
+     * per group, at most 4 groups per GPU — measured on a 16-core host with one B200: 64 chains of
+     * 1000 x 200k run 1.0 / 1.4 / 1.7 / 1.3 / 1.1 times the single-group rate with 1 / 2 / 4 / 8 / 16
+     * groups (more driver threads contend in the CUDA driver) */
+    const int ND = std::max(1, std::min(rc.devices, R));
+    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND)
+                                : std::min(std::min(std::max(1, host_threads / ND), 4), (R / ND + 7) / 8);
+    per_dev = std::max(1, per_dev);
+    int G = std::max(1, std::min(ND * per_dev, R));
     if (dev.word_count >= 0 && dev.word_count != MSA->nwords)
         G = 1; /* site-block mode: one context per rank, the all-reduce keeps the ranks in lock-step */
     std::vector<Device> extra((size_t)G);
@@ -780,7 +785,8 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             rows[(size_t)i] = flat.data() + (size_t)i * (size_t)MSA->nwords;
         DNAToBinary(MSA, rows.data());
         for (int g = 1; g < G; g++)
-            device_open_encoded(extra[(size_t)g], dev.index, MSA, rows.data(), first[(size_t)g + 1] - first[(size_t)g]);
+            device_open_encoded(extra[(size_t)g], dev.index + g % ND, MSA, rows.data(),
+                                first[(size_t)g + 1] - first[(size_t)g]);
     }
     const double setup_secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
     auto device_of = [&](int g) -> Device & { return g == 0 ? dev : extra[(size_t)g]; };
