@@ -134,7 +134,8 @@ int lvb_gpu_last_kernel_ms(lvb_gpu_ctx *ctx, float *ms);
 int lvb_gpu_kernel_time(lvb_gpu_ctx *ctx, double *total_ms, int64_t *launches, int reset);
 /* launch again the batch left on the device by the last commit/score call (same programs, no
  * host compile, no host-to-device copy): device-resident timing, and re-scoring after the trees
- * changed.  lengths may be NULL (no wait). */
+ * changed.  lengths may be NULL (no wait: consecutive re-runs queue up on the stream).  With a
+ * communicator attached, every re-run ends with the all-reduce of the partial lengths. */
 int lvb_gpu_rerun_last_batch(lvb_gpu_ctx *ctx, int64_t *lengths);
 /* wait for all work enqueued on the context's stream */
 int lvb_gpu_synchronize(lvb_gpu_ctx *ctx);

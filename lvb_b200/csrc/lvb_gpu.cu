@@ -168,6 +168,10 @@ struct lvb_gpu_ctx
     static const int kEvRing = 32;
     cudaEvent_t ring0[kEvRing] = {}, ring1[kEvRing] = {};
     int ring_used = 0;
+    uint8_t ring_kind[kEvRing] = {};       /* 1: store launch, 0: score launch */
+    int64_t ring_cand[kEvRing] = {}, ring_instr[kEvRing] = {};
+    double kind_ms[2] = {0, 0};            /* profile: device time, launches, candidates, instructions per kind */
+    int64_t kind_launches[2] = {0, 0}, kind_cand[2] = {0, 0}, kind_instr[2] = {0, 0};
     double kernel_ms_total = 0;
     int64_t kernel_launches_timed = 0;
 
@@ -282,13 +286,18 @@ static int drain_kernel_events(lvb_gpu_ctx *c)
         CU(cudaEventElapsedTime(&ms, c->ring0[i], c->ring1[i]));
         c->kernel_ms_total += ms;
         c->kernel_launches_timed++;
+        const int kd = c->ring_kind[i];
+        c->kind_ms[kd] += ms;
+        c->kind_launches[kd]++;
+        c->kind_cand[kd] += c->ring_cand[i];
+        c->kind_instr[kd] += c->ring_instr[i];
     }
     c->ring_used = 0;
     return 0;
 }
 
 /* launch the batch that is resident in staging slot c->last_slot */
-static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
+static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always = false)
 {
     const int64_t K = c->last_K;
     const bool store = c->last_store;
@@ -327,6 +336,9 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
         if (c->ring_used == lvb_gpu_ctx::kEvRing && drain_kernel_events(c))
             return 1;
         slot = c->ring_used++;
+        c->ring_kind[slot] = store ? 1 : 0;
+        c->ring_cand[slot] = K;
+        c->ring_instr[slot] = (int64_t)c->last_n_instr;
         CU(cudaEventRecord(c->ring0[slot], c->stream));
     }
     /* one launch per dependency level: pieces of a level only read rows stored by earlier levels */
@@ -352,7 +364,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths)
                                   c->last_max_instr, c->stream));
         c->launches++;
     }
-    if (c->comm && (lengths || !store))
+    if (c->comm && (lengths || !store || reduce_always))
     {
         int r = g_nccl.AllReduce(c->d_lengths, c->d_lengths, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
         if (r != 0)
@@ -736,6 +748,8 @@ extern "C"
         c->score_v1 = v1 && atoi(v1) != 0;
         const char *pf = getenv("LVB_GPU_PROFILE");
         c->profile = pf && atoi(pf) != 0;
+        if (pf && atoi(pf) >= 2) /* also device time of the Fitch kernels (events around every launch) */
+            c->timing = true;
         const char *ll = getenv("LVB_GPU_LEVEL_LAUNCHES");
         c->level_launches = ll && atoi(ll) != 0;
         const char *b = getenv("LVB_GPU_BLOCK");
@@ -759,6 +773,11 @@ extern "C"
             fprintf(stderr, "[lvb_gpu profile] %lld calls, %lld candidates: compile %.3f s, layout+H2D enqueue %.3f s, "
                             "launch enqueue %.3f s, wait %.3f s\n", (long long)c->n_calls, (long long)c->n_cand_total,
                     c->t_compile, c->t_layout, c->t_submit, c->t_wait);
+        if (c->profile && c->timing && drain_kernel_events(c) == 0)
+            for (int kd = 0; kd < 2; kd++)
+                fprintf(stderr, "[lvb_gpu profile] %s kernel: %.3f s on the device, %lld launches, %lld programs, %lld instructions\n",
+                        kd ? "store" : "score", c->kind_ms[kd] * 1e-3, (long long)c->kind_launches[kd],
+                        (long long)c->kind_cand[kd], (long long)c->kind_instr[kd]);
         if (c->comm && g_nccl.CommDestroy)
             g_nccl.CommDestroy(c->comm);
         free_matrix(c);
@@ -1073,13 +1092,10 @@ extern "C"
         if (c->last_K <= 0)
             return fail("no batch is resident on the device");
         CU(cudaSetDevice(c->device));
-        Staging &st = c->ring[c->last_slot];
-        if (st.pending)
-        {
-            CU(cudaEventSynchronize(st.done));
-            st.pending = false;
-        }
-        return launch_resident(c, lengths);
+        /* nothing is re-staged, so the launches of consecutive re-runs queue up behind each other on
+         * the stream without a host wait.  With a communicator attached the partial lengths are
+         * all-reduced on every re-run (the site-block step of BASELINE.json configs[3]). */
+        return launch_resident(c, lengths, true);
     }
 
     int lvb_gpu_kernel_time(lvb_gpu_ctx *c, double *total_ms, int64_t *launches, int reset)
