@@ -107,6 +107,22 @@ int lvb_gpu_commit_batch(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, con
 int lvb_gpu_score_batch(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
                         int64_t *lengths);
 
+/* ---- the exhaustive NNI neighbourhood of one evaluated tree, in one call: what the loop of
+ * deterministic_hillclimb (Solve.c:100-111) computes with 2(n-3) x (mutate_deterministic,
+ * TreeOperations.c:105-158, + getplen).  lengths[2*(u-n) + j] is the length getplen would return
+ * for mutate_deterministic(p = u, left = j) of `topo`, for every internal node u in n..2n-4 and
+ * j = 0 (left == LVB_FALSE: u keeps its left child and takes its sister) then 1 — the order of
+ * the reference's two loops.
+ * `tree` must hold the evaluated current tree (`topo` as last committed; its dirty list is
+ * ignored); nothing in it is written.  `scratch_tree` is another device tree of this context whose
+ * rows are overwritten with the "up" state sets (the Fitch set of the rest of the tree seen from
+ * each internal branch); afterwards it counts as never evaluated.
+ * Method: tree lengths do not depend on the root, so each candidate is evaluated on the branch it
+ * rearranges from four state rows (two children, sister, up set): 2 launches of row-streaming
+ * kernels for all 2(n-3) candidates instead of 2(n-3) dirty paths. ---- */
+int lvb_gpu_nni_neighbourhood(lvb_gpu_ctx *ctx, int tree, int scratch_tree, const lvb_gpu_topology *topo,
+                              int64_t *lengths);
+
 /* ---- parity / debugging (treedump, TreeOperations.c:1082-1112) ---- */
 /* state row of `node` (leaf or internal) of `tree`: word_count words of this context's block */
 int lvb_gpu_download_row(lvb_gpu_ctx *ctx, int tree, int64_t node, uint64_t *out);
@@ -152,6 +168,13 @@ int lvb_gpu_compile_schedule(int64_t n, const lvb_gpu_topology *topo, int store,
 int lvb_gpu_compile_pieces(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,
                            int64_t *n_instr, int64_t *n_slots, int32_t *pieces, int64_t pieces_cap,
                            int64_t *n_pieces);
+
+/* Host-only: the up-pass program lvb_gpu_nni_neighbourhood runs — one store instruction per
+ * internal node v, in pre-order, whose result is the Fitch set of the tree WITHOUT the subtree
+ * below v.  Operand rows >= n are rows of the evaluated tree; results belong under the same node
+ * numbers in the scratch tree. */
+int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int32_t *instr, int64_t cap, int64_t *n_instr,
+                            int64_t *n_slots);
 
 #ifdef __cplusplus
 }

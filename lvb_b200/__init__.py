@@ -8,4 +8,4 @@ contains no arithmetic and has no CPU fallback: importing :mod:`lvb_b200.gpu` ra
 library has not been built.
 """
 
-from .gpu import Engine, GpuError, Topology, load_library, compile_schedule, compile_pieces  # noqa: F401
+from .gpu import Engine, GpuError, Topology, load_library, compile_schedule, compile_pieces, compile_up_pass  # noqa: F401

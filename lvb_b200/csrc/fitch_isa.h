@@ -51,7 +51,10 @@ typedef struct FitchProgram
     int32_t parent;      /* piece (index into the launch's program array) that reads the row this piece's
                           * top node stores, -1 if none */
     int32_t n_wait;      /* number of pieces of the same launch whose stored rows this piece reads */
-    int32_t pad0, pad1;
+    int32_t src_tree1;   /* store programs: 1 + device tree the internal-row OPERANDS are read from, when
+                          * that is not `tree` (up-pass: reads the evaluated tree, stores into a scratch
+                          * tree); 0 = same tree */
+    int32_t pad1;
 } FitchProgram;
 
 #endif

@@ -172,6 +172,8 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
     const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal; /* internal node v lives in row v + tree_off */
+    /* rows the operands are read from: the program's own tree unless it names another one */
+    const unsigned src_off = prog.src_tree1 > 0 ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
     const FitchInstr *gi = p.instr + prog.instr_begin;
     /* threads past the end of the row (last column block only) redo the last column; their
      * counts are masked and their stores suppressed */
@@ -217,14 +219,14 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
                     a = 0;
                 }
                 else if (a >= p.n)
-                    a += tree_off;
+                    a += src_off;
                 if (b < 0)
                 {
                     w |= D_BSLOT;
                     b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
                 }
                 else if (b >= p.n)
-                    b += tree_off;
+                    b += src_off;
                 d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
             }
             s_instr[i] = d;
@@ -618,6 +620,85 @@ cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *
      * (instruction -> count, cached count), so width, not work, sets the duration */
     const int threads = max_instr >= 1024 ? 1024 : max_instr <= 128 ? 128 : (max_instr + 31) / 32 * 32;
     fitch_commit_finalize_kernel<<<n_prog, threads, 0, stream>>>(instr, prog, cnts, chg, sum_chg, n, n_internal, lengths);
+    return cudaGetLastError();
+}
+
+/* ---- exhaustive NNI neighbourhood --------------------------------------------------------
+ * deterministic_hillclimb (src/Solve.c:64-142) scores the 2(n-3) trees mutate_deterministic
+ * (src/TreeOperations.c:105-158) makes from one current tree.  A Fitch length does not depend
+ * on where the tree is rooted, so a candidate can be evaluated on the branch that is being
+ * rearranged: with A, B the subtrees below u, C the sister of u and D everything above the
+ * parent of u (its "up" set, produced by the up-pass program), the current tree is
+ * ((A,B),(C,D)), the candidate for left == FALSE is ((A,C),(B,D)) and the one for left == TRUE
+ * is ((B,C),(A,D)); the lengths inside A, B, C and D are common to all three.  One thread
+ * reads its 16-byte column of the four rows and returns both length differences: 4 rows of
+ * traffic per PAIR of candidates, whatever the depth of u. */
+__device__ __forceinline__ unsigned fitch_lane_flags(unsigned x, unsigned y)
+{
+    const unsigned t = x & y;
+    const unsigned a = (t & 0x77777777u) + 0x77777777u;
+    return ~(a | t) & 0x88888888u;
+}
+/* number of sites of the column whose intersection is empty (no result row wanted) */
+__device__ __forceinline__ int fitch_count(const uint4 &x, const uint4 &y)
+{
+    const unsigned f = (fitch_lane_flags(x.x, y.x) >> 3) | (fitch_lane_flags(x.y, y.y) >> 2) |
+                       (fitch_lane_flags(x.z, y.z) >> 1) | fitch_lane_flags(x.w, y.w);
+    return __popc(f);
+}
+__device__ __forceinline__ int join_cost(const uint4 &p, const uint4 &q, const uint4 &r, const uint4 &s)
+{
+    /* ((p,q),(r,s)) evaluated on its middle branch */
+    uint4 pq, rs;
+    int c = __popc(fitch_step(p, q, pq));
+    c += __popc(fitch_step(r, s, rs));
+    return c + fitch_count(pq, rs);
+}
+
+__global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams p)
+{
+    __shared__ int s_d[2];
+    const int tid = threadIdx.x;
+    /* column-block-major: the CTAs of neighbouring branches over the same columns run together,
+     * and a row is an operand of up to three branches (its own, its sister's, its children's) */
+    const int edge = blockIdx.x % p.n_edges;
+    const int cb = blockIdx.x / p.n_edges;
+    const int col = cb * blockDim.x + tid;
+    if (tid < 2)
+        s_d[tid] = 0;
+    __syncthreads();
+    int d0 = 0, d1 = 0;
+    if (col < p.ncols)
+    {
+        const uint4 r = p.rows[edge]; /* pool rows of A, B, C, D */
+        const uint4 *base = p.pool + col;
+        const uint4 A = __ldg(base + (size_t)r.x * p.stride_u4);
+        const uint4 B = __ldg(base + (size_t)r.y * p.stride_u4);
+        const uint4 C = __ldg(base + (size_t)r.z * p.stride_u4);
+        const uint4 D = __ldg(base + (size_t)r.w * p.stride_u4);
+        const int cur = join_cost(A, B, C, D);
+        d0 = join_cost(A, C, B, D) - cur;
+        d1 = join_cost(B, C, A, D) - cur;
+    }
+    d0 = __reduce_add_sync(0xffffffffu, d0);
+    d1 = __reduce_add_sync(0xffffffffu, d1);
+    if ((tid & 31) == 0)
+    {
+        if (d0)
+            atomicAdd(&s_d[0], d0);
+        if (d1)
+            atomicAdd(&s_d[1], d1);
+    }
+    __syncthreads();
+    if (tid < 2 && s_d[tid])
+        atomicAdd(reinterpret_cast<unsigned long long *>(p.delta + 2 * (size_t)edge + tid),
+                  (unsigned long long)(long long)s_d[tid]);
+}
+
+cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t stream)
+{
+    const unsigned grid = (unsigned)p.n_edges * (unsigned)p.n_colblocks;
+    nni_neighbourhood_kernel<<<grid, block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

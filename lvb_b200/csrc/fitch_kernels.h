@@ -46,6 +46,22 @@ cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
                                    int max_instr, cudaStream_t stream);
 
+/* Exhaustive NNI neighbourhood (Solve.c:64-142, TreeOperations.c:105-158): branch e joins the
+ * pool rows rows[e] = {A, B, C, D}; delta[2e] += length(((A,C),(B,D))) - length(((A,B),(C,D))),
+ * delta[2e+1] += length(((B,C),(A,D))) - the same, over this context's columns.  delta must be
+ * zero before the launch. */
+struct NniParams
+{
+    const uint4 *pool;
+    int64_t stride_u4;
+    int32_t ncols;
+    int32_t n_edges;
+    int32_t n_colblocks;
+    const uint4 *rows; /* [n_edges] */
+    long long *delta;  /* [2 * n_edges] */
+};
+cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t stream);
+
 /* DNAToBinary on the device (reference: src/DataOperations.c:164-249).  text: n x m bytes
  * row-major; writes words [word_begin, word_begin + word_count) of each leaf row into the pool;
  * *bad is set to 1 + the offending byte if a symbol is not allowed. */

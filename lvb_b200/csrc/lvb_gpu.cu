@@ -146,6 +146,8 @@ struct lvb_gpu_ctx
     size_t cap_tot = 0;
     unsigned *d_dep = nullptr;                         /* [cap_dep] + 1 ticket: dependency counters of one store launch; zero between */
     size_t cap_dep = 0;
+    long long *d_nni = nullptr, *h_nni = nullptr;      /* [cap_nni] length differences of an NNI neighbourhood */
+    size_t cap_nni = 0;
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
     bool last_dep = false;
@@ -786,6 +788,9 @@ extern "C"
         cudaFree(c->d_totals);
         cudaFree(c->d_done);
         cudaFree(c->d_lengths);
+        cudaFree(c->d_nni);
+        if (c->h_nni)
+            cudaFreeHost(c->h_nni);
         for (auto &st : c->ring)
         {
             cudaFreeHost(st.h);
@@ -952,6 +957,149 @@ extern "C"
         if (!c || !trees || !topos || !lengths)
             return fail("lvb_gpu_score_batch: null argument");
         return run_batch(c, n_cand, trees, topos, false, lengths);
+    }
+
+    int lvb_gpu_nni_neighbourhood(lvb_gpu_ctx *c, int tree, int scratch_tree, const lvb_gpu_topology *topo,
+                                  int64_t *lengths)
+    {
+        if (!c || !topo || !lengths)
+            return fail("lvb_gpu_nni_neighbourhood: null argument");
+        if (!c->pool)
+            return fail("no alignment on the device: call lvb_gpu_matrix_upload first");
+        if (tree < 0 || tree >= c->max_trees || !c->tree_used[tree] || !c->tree_ready[tree])
+            return fail("lvb_gpu_nni_neighbourhood: tree %d has not been evaluated", tree);
+        if (scratch_tree < 0 || scratch_tree >= c->max_trees || !c->tree_used[scratch_tree] || scratch_tree == tree)
+            return fail("lvb_gpu_nni_neighbourhood: scratch tree %d does not exist or is the tree itself", scratch_tree);
+        if (c->I < 1)
+            return fail("lvb_gpu_nni_neighbourhood: the tree has no internal branch");
+        /* length of the current tree as getplen returns it: cached counts + root step */
+        lvb_gpu_topology clean = *topo;
+        clean.n_dirty = 0;
+        clean.dirty = nullptr;
+        int64_t base_len = 0;
+        if (run_batch(c, 1, &tree, &clean, false, &base_len))
+            return 1;
+        c->last_K = 0;
+
+        std::vector<FitchInstr> instr;
+        std::vector<int32_t> parent, left, right;
+        std::string err;
+        int n_slots = 0;
+        if (!c->sc[0]->compile_up_pass(*topo, instr, n_slots, parent, left, right, err))
+            return fail("%s", err.c_str());
+        const int64_t E = c->I;
+        const size_t n_instr = instr.size();
+        if (ensure_device_arrays(c, n_instr, 1))
+            return 1;
+        if ((size_t)(2 * E) > c->cap_nni)
+        {
+            CU(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_nni);
+            if (c->h_nni)
+                CU(cudaFreeHost(c->h_nni));
+            c->cap_nni = grow(c->cap_nni, (size_t)(2 * E), 1024);
+            CU(cudaMalloc(&c->d_nni, c->cap_nni * sizeof(long long)));
+            CU(cudaMallocHost(&c->h_nni, c->cap_nni * sizeof(long long)));
+        }
+        const size_t bytes = 2 * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr) + (size_t)E * sizeof(uint4);
+        int slot;
+        if (acquire_slot(c, bytes, 1, &slot))
+            return 1;
+        Staging &st = c->ring[slot];
+        FitchProgram *h_prog = reinterpret_cast<FitchProgram *>(st.h);
+        FitchInstr *h_instr = reinterpret_cast<FitchInstr *>(h_prog + 2);
+        uint4 *h_rows = reinterpret_cast<uint4 *>(h_instr + n_instr);
+        /* up-pass: operands from `tree`, stores (and the per-node counts nobody reads) into scratch_tree */
+        h_prog[0] = FitchProgram{0, (int32_t)n_instr, scratch_tree, 0, -1, 0, tree + 1, 0};
+        h_prog[1] = FitchProgram{0, (int32_t)n_instr, scratch_tree, 1, -1, 0, tree + 1, 0};
+        if (n_instr)
+            memcpy(h_instr, instr.data(), n_instr * sizeof(FitchInstr));
+        const int64_t root = topo->root;
+        auto low_row = [&](int32_t v) { return (uint32_t)(v < c->n ? v : v + (int64_t)tree * c->I); };
+        for (int64_t e = 0; e < E; e++)
+        {
+            const int32_t u = (int32_t)(c->n + e), v = parent[u];
+            const int32_t sis = left[v] == u ? right[v] : left[v];
+            const uint32_t up = v == root ? (uint32_t)root : (uint32_t)(v + (int64_t)scratch_tree * c->I);
+            h_rows[e] = make_uint4(low_row(left[u]), low_row(right[u]), low_row(sis), up);
+        }
+        CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
+        c->tree_ready[scratch_tree] = 0; /* its rows now hold up sets, not an evaluated tree */
+        const FitchProgram *d_prog = reinterpret_cast<const FitchProgram *>(st.d);
+        const FitchInstr *d_instr = reinterpret_cast<const FitchInstr *>(d_prog + 2);
+        const uint4 *d_rows = reinterpret_cast<const uint4 *>(d_instr + n_instr);
+        const int block = pick_block(c);
+        const int n_cb = (int)((c->stride_u4 + block - 1) / block);
+        if (n_instr)
+        {
+            ExecParams p;
+            p.pool = c->pool;
+            p.stride_u4 = c->stride_u4;
+            p.ncols = (int32_t)c->stride_u4;
+            p.n = (int32_t)c->n;
+            p.n_internal = (int32_t)c->I;
+            p.n_prog = 1;
+            p.n_colblocks = n_cb;
+            p.n_slots = n_slots;
+            p.score_v1 = 0;
+            p.instr = d_instr;
+            p.prog = d_prog;
+            p.totals = c->d_totals;
+            p.done = c->d_done;
+            p.out = c->d_lengths;
+            p.cnts = c->d_cnts;
+            p.ticket = nullptr;
+            p.dep = nullptr;
+            p.chg = c->chg;
+            p.sum_chg = c->sum_chg;
+            CU(launch_fitch_exec(p, true, block, c->stream));
+            CU(launch_commit_finalize(d_instr, d_prog + 1, 1, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
+                                      c->d_lengths, (int)n_instr, c->stream));
+            c->launches += 2;
+        }
+        CU(cudaMemsetAsync(c->d_nni, 0, (size_t)(2 * E) * sizeof(long long), c->stream));
+        NniParams q;
+        q.pool = c->pool;
+        q.stride_u4 = c->stride_u4;
+        q.ncols = (int32_t)c->stride_u4;
+        q.n_edges = (int32_t)E;
+        q.n_colblocks = n_cb;
+        q.rows = d_rows;
+        q.delta = c->d_nni;
+        if ((int64_t)E * n_cb > (int64_t)INT32_MAX)
+            return fail("lvb_gpu_nni_neighbourhood: %lld CTAs", (long long)E * n_cb);
+        int ev = -1;
+        if (c->timing)
+        {
+            if (c->ring_used == lvb_gpu_ctx::kEvRing && drain_kernel_events(c))
+                return 1;
+            ev = c->ring_used++;
+            c->ring_kind[ev] = 0;
+            c->ring_cand[ev] = 2 * E;
+            c->ring_instr[ev] = 0;
+            CU(cudaEventRecord(c->ring0[ev], c->stream));
+        }
+        CU(launch_nni_neighbourhood(q, block, c->stream));
+        c->launches++;
+        if (c->timing)
+        {
+            CU(cudaEventRecord(c->ring1[ev], c->stream));
+            c->ev0 = c->ring0[ev];
+            c->ev1 = c->ring1[ev];
+            c->timed = true;
+        }
+        if (c->comm)
+        {
+            int r = g_nccl.AllReduce(c->d_nni, c->d_nni, (size_t)(2 * E), kNcclInt64, kNcclSum, c->comm, c->stream);
+            if (r != 0)
+                return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+        }
+        CU(cudaMemcpyAsync(c->h_nni, c->d_nni, (size_t)(2 * E) * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaEventRecord(st.done, c->stream));
+        CU(cudaEventSynchronize(st.done));
+        for (int64_t k = 0; k < 2 * E; k++)
+            lengths[k] = base_len + (int64_t)c->h_nni[k];
+        return 0;
     }
 
     int lvb_gpu_download_row(lvb_gpu_ctx *c, int tree, int64_t node, uint64_t *out)
@@ -1136,6 +1284,31 @@ extern "C"
         int slots = 0;
         std::string err;
         if (!sc.compile(*topo, store != 0, out, slots, err))
+            return fail("%s", err.c_str());
+        *n_instr = (int64_t)out.size();
+        *n_slots = slots;
+        if (instr)
+        {
+            if ((int64_t)out.size() > cap)
+                return fail("instruction buffer too small: need %zu", out.size());
+            memcpy(instr, out.data(), out.size() * sizeof(FitchInstr));
+        }
+        return 0;
+    }
+
+    int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int32_t *instr, int64_t cap, int64_t *n_instr,
+                                int64_t *n_slots)
+    {
+        if (!topo || !n_instr || !n_slots)
+            return fail("lvb_gpu_compile_up_pass: null argument");
+        if (n < 4)
+            return fail("lvb_gpu_compile_up_pass: n too small");
+        ScheduleCompiler sc(n);
+        std::vector<FitchInstr> out;
+        std::vector<int32_t> parent, left, right;
+        int slots = 0;
+        std::string err;
+        if (!sc.compile_up_pass(*topo, out, slots, parent, left, right, err))
             return fail("%s", err.c_str());
         *n_instr = (int64_t)out.size();
         *n_slots = slots;

@@ -293,4 +293,142 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
     return true;
 }
 
+bool ScheduleCompiler::compile_up_pass(const lvb_gpu_topology &topo, std::vector<FitchInstr> &out, int &n_slots,
+                                       std::vector<int32_t> &parent, std::vector<int32_t> &left,
+                                       std::vector<int32_t> &right, std::string &err)
+{
+    const int64_t root = topo.root;
+    if (n_ < 4 || root < 0 || root >= n_)
+    {
+        err = "up-pass: bad root or fewer than 4 leaves";
+        return false;
+    }
+    /* materialise the child links (overlay applied) and the parents */
+    left.assign((size_t)B_, -1);
+    right.assign((size_t)B_, -1);
+    parent.assign((size_t)B_, -1);
+    for (int64_t v = 0; v < B_; v++)
+    {
+        if (v < n_ && v != root)
+            continue;
+        left[v] = (int32_t)strided(topo.left, topo.stride_bytes, v);
+        right[v] = (int32_t)strided(topo.right, topo.stride_bytes, v);
+    }
+    for (int64_t i = 0; i < topo.n_mod; i++)
+    {
+        const int64_t v = topo.mod_node[i];
+        if (v < 0 || v >= B_ || (v < n_ && v != root))
+        {
+            err = "up-pass: overlay names node " + std::to_string(v);
+            return false;
+        }
+        left[v] = (int32_t)topo.mod_left[i];
+        right[v] = (int32_t)topo.mod_right[i];
+    }
+    for (int64_t v = 0; v < B_; v++)
+    {
+        if (v < n_ && v != root)
+            continue;
+        const int64_t c[2] = {left[v], right[v]};
+        for (int k = 0; k < 2; k++)
+        {
+            if (c[k] < 0 || c[k] >= B_ || c[k] == root || c[k] == v || parent[c[k]] != -1)
+            {
+                err = "up-pass: node " + std::to_string(v) + " has bad children";
+                return false;
+            }
+            parent[c[k]] = (int32_t)v;
+        }
+    }
+    /* pre-order of the internal nodes from the root (also proves that the links form one tree) */
+    order_.clear();
+    for (int k = 0; k < 2; k++)
+    {
+        const int32_t c = k ? right[root] : left[root];
+        if (c >= n_)
+            order_.push_back(c);
+    }
+    for (size_t head = 0; head < order_.size(); head++)
+    {
+        const int32_t v = order_[head];
+        if (left[v] >= n_)
+            order_.push_back(left[v]);
+        if (right[v] >= n_)
+            order_.push_back(right[v]);
+    }
+    if ((int64_t)order_.size() != B_ - n_)
+    {
+        err = "up-pass: the links do not form one tree";
+        return false;
+    }
+    /* stack slots the pre-order walk below v needs: a node with two internal children parks
+     * up(v) while the first child's subtree is walked; the child that needs fewer goes first */
+    for (size_t k = order_.size(); k-- > 0;)
+    {
+        const int32_t v = order_[k];
+        const int32_t a = left[v], b = right[v];
+        const int na = a >= n_ ? need_[a] : -1, nb = b >= n_ ? need_[b] : -1;
+        if (na >= 0 && nb >= 0)
+            need_[v] = std::max(std::max(na, nb), std::min(na, nb) + 1);
+        else
+            need_[v] = std::max(0, std::max(na, nb));
+    }
+    int depth = 0, peak = 0;
+    auto walk = [&](int32_t top) { /* the instruction that produced up(top) was emitted last */
+        frames_.clear();
+        frames_.push_back(Frame{top, -1, -1, 0});
+        while (!frames_.empty())
+        {
+            Frame &f = frames_.back();
+            const int32_t v = f.v, a = left[v], b = right[v];
+            if (f.stage == 0)
+            {
+                const bool ia = a >= n_, ib = b >= n_;
+                if (ia && ib)
+                {
+                    const bool a_first = need_[a] <= need_[b];
+                    f.first = a_first ? a : b;
+                    f.second = a_first ? b : a;
+                    f.stage = 1;
+                    out.back().ctl |= (uint32_t)(depth + 1) << LVB_CTL_PUSH_SHIFT;
+                    depth++;
+                    peak = std::max(peak, depth);
+                    const int32_t c = f.first, o = f.second;
+                    out.push_back(FitchInstr{LVB_OPER_PREV, o, c, LVB_CTL_STORE});
+                    frames_.push_back(Frame{c, -1, -1, 0});
+                }
+                else if (ia || ib)
+                {
+                    const int32_t c = ia ? a : b, o = ia ? b : a;
+                    out.push_back(FitchInstr{LVB_OPER_PREV, o, c, LVB_CTL_STORE});
+                    f = Frame{c, -1, -1, 0}; /* tail call */
+                }
+                else
+                    frames_.pop_back();
+            }
+            else
+            { /* back from the first child's subtree: up(v) is in the top slot */
+                depth--;
+                const int32_t c = f.second, o = f.first;
+                out.push_back(FitchInstr{LVB_OPER_SLOT(depth), o, c, LVB_CTL_STORE});
+                f = Frame{c, -1, -1, 0};
+            }
+        }
+    };
+    const int32_t rc[2] = {left[root], right[root]};
+    for (int k = 0; k < 2; k++)
+        if (rc[k] >= n_)
+        {
+            out.push_back(FitchInstr{(int32_t)root, rc[1 - k], rc[k], LVB_CTL_STORE});
+            walk(rc[k]);
+        }
+    if (peak > LVB_MAX_SLOTS)
+    {
+        err = "up-pass: program needs " + std::to_string(peak) + " stack slots";
+        return false;
+    }
+    n_slots = peak;
+    return true;
+}
+
 } // namespace lvbgpu

@@ -45,6 +45,19 @@ class ScheduleCompiler
 
     int64_t n() const { return n_; }
 
+    /* The up-pass of a whole tree: one store instruction per internal node v computing
+     * up(v) = the Fitch set of everything that is NOT below v (the tree seen from v's parent
+     * branch): up(v) = fitch(up(parent), low(sister)), and fitch(row(root), low(sister)) for
+     * the two children of the root.  Operand rows >= n are rows of the evaluated tree (low
+     * sets), results are stored under the same node numbers in another device tree.  The
+     * traversal is pre-order with up(parent) in the previous-result register or in a stack
+     * slot, so no instruction reads a row the program itself stores.
+     * parent receives the parent of every node (root: -1).  Used by the exhaustive NNI
+     * neighbourhood (src/Solve.c:64-142). */
+    bool compile_up_pass(const lvb_gpu_topology &topo, std::vector<FitchInstr> &out, int &n_slots,
+                         std::vector<int32_t> &parent, std::vector<int32_t> &left, std::vector<int32_t> &right,
+                         std::string &err);
+
   private:
     struct Frame
     {

@@ -64,6 +64,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_tree_commit.argtypes = [vp, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_commit_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_score_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
+    lib.lvb_gpu_nni_neighbourhood.argtypes = [vp, C.c_int, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_download_row.argtypes = [vp, C.c_int, i64, vp]
     lib.lvb_gpu_tree_changes.argtypes = [vp, C.c_int, vp]
     lib.lvb_gpu_comm_unique_id.argtypes = [vp]
@@ -77,6 +78,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_synchronize.argtypes = [vp]
     lib.lvb_gpu_compile_schedule.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64)]
     lib.lvb_gpu_compile_pieces.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64), vp, i64, C.POINTER(i64)]
+    lib.lvb_gpu_compile_up_pass.argtypes = [i64, C.POINTER(_Topo), vp, i64, C.POINTER(i64), C.POINTER(i64)]
     _lib = lib
     return lib
 
@@ -133,6 +135,17 @@ def compile_schedule(n: int, topo: Topology, store: bool = False):
     _check(lib.lvb_gpu_compile_schedule(n, C.byref(ts), int(store), None, 0, C.byref(k), C.byref(slots)))
     out = np.zeros((k.value, 4), dtype=np.int32)
     _check(lib.lvb_gpu_compile_schedule(n, C.byref(ts), int(store), out.ctypes.data, k.value, C.byref(k), C.byref(slots)))
+    return out, int(slots.value)
+
+
+def compile_up_pass(n: int, topo: Topology):
+    """Host-only: the up-pass program of the NNI neighbourhood as an (n-3, 4) int32 array and its slot count."""
+    lib = load_library()
+    ts = topo.as_struct()
+    k, slots = C.c_int64(0), C.c_int64(0)
+    _check(lib.lvb_gpu_compile_up_pass(n, C.byref(ts), None, 0, C.byref(k), C.byref(slots)))
+    out = np.zeros((k.value, 4), dtype=np.int32)
+    _check(lib.lvb_gpu_compile_up_pass(n, C.byref(ts), out.ctypes.data, k.value, C.byref(k), C.byref(slots)))
     return out, int(slots.value)
 
 
@@ -232,6 +245,15 @@ class Engine:
 
     def score_batch(self, trees: Sequence[int], topos: Sequence[Topology]) -> np.ndarray:
         return self._batch(self.lib.lvb_gpu_score_batch, trees, topos)
+
+    def nni_neighbourhood(self, tree: int, scratch_tree: int, topo: Topology) -> np.ndarray:
+        """lengths of all 2(n-3) mutate_deterministic candidates of the evaluated `tree`
+        (index 2*(u-n)+left); `scratch_tree` receives the up sets"""
+        ts = topo.as_struct()
+        out = np.zeros(2 * (self.n - 3), dtype=np.int64)
+        _check(self.lib.lvb_gpu_nni_neighbourhood(self.ctx, tree, scratch_tree, C.byref(ts),
+                                                  out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return out
 
     # ---- parity helpers ----
     def download_row(self, tree: int, node: int) -> np.ndarray:

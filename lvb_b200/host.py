@@ -63,6 +63,7 @@ def load_host_library() -> C.CDLL:
     L.lvbh_device_open.argtypes = [_vp, C.c_int, C.c_int]
     L.lvbh_getplen.restype = _l
     L.lvbh_getplen.argtypes = [_vp, _vp, _l]
+    L.lvbh_hillclimb.argtypes = [_vp, C.c_int, _vp, _l, C.c_char_p, _lp]
     L.lvbh_search.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _l, C.c_int, C.c_char_p,
                               C.c_char_p, _vp, _vp, C.POINTER(C.c_double)]
     _lib = L
@@ -224,6 +225,12 @@ class HostTree:
 
     def newick(self, path: str) -> None:
         _check(self.L.lvbh_treeprint(self.msa.h, self.t, self.root, path.encode()))
+
+    def hillclimb(self, device: int = 0, outtree_path: Optional[str] = None) -> dict:
+        """deterministic_hillclimb (Solve.c:64-142) from this tree, on the device"""
+        out = (C.c_long * 4)()
+        _check(self.L.lvbh_hillclimb(self.msa.h, device, self.t, self.root, outtree_path.encode() if outtree_path else None, out))
+        return dict(length=int(out[0]), iterations=int(out[1]), trees=int(out[2]), neighbourhood_calls=int(out[3]))
 
     def getplen(self) -> int:
         """the compatible one-tree getplen (needs lvbh_device_open first)"""

@@ -311,4 +311,33 @@ int lvbh_search(void *hv, int device, int seed, int algorithm, int cooling, int 
     });
 }
 
+/* ---- deterministic_hillclimb (Solve.c:64-142) from `tree`/`root`.  out: final length, iterations
+ * (current_iter), trees on the stack, neighbourhood calls; outtree_path (may be NULL) receives
+ * the stack as PrintTreestack writes it. ---- */
+int lvbh_hillclimb(void *hv, int device, const void *tree, long root, const char *outtree_path, long *out)
+{
+    Handle *h = (Handle *)hv;
+    return guarded([&] {
+        Device dev;
+        device_open(dev, device, &h->msa, 2);
+        TREESTACK stack = CreateNewTreestack();
+        long iter = 0, calls = 0;
+        const long len = deterministic_hillclimb(&h->msa, dev, &stack, (const TREESTACK_TREE_NODES *)tree, h->rc, root,
+                                                 nullptr, &iter, false, &calls);
+        out[0] = len;
+        out[1] = iter;
+        out[2] = stack.next;
+        out[3] = calls;
+        if (outtree_path)
+        {
+            FILE *fp = fopen(outtree_path, "w");
+            if (!fp)
+                crash("cannot open %s", outtree_path);
+            PrintTreestack(&h->msa, &stack, fp);
+            fclose(fp);
+        }
+        device_close(dev);
+    });
+}
+
 } /* extern "C" */

@@ -266,5 +266,14 @@ struct Chain; /* one SA replicate: solve.cpp */
 void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicates, std::vector<TREESTACK> &stacks,
                     std::vector<SearchResult> &results, std::vector<TrajectoryRow> *trajectory, FILE *tsv);
 
+/* src/Solve.c:64-142 (switched off in the reference, Solve.c:571-572): NNI on every internal
+ * branch, both sides, in index order, accepting every move that does not lengthen the tree and
+ * is a new topology, until a whole sweep accepts nothing; returns the final length, the trees
+ * of that length are on the stack.  One lvb_gpu_nni_neighbourhood call per accepted move
+ * instead of one getplen per candidate; needs two free device trees. */
+long deterministic_hillclimb(Dataptr MSA, Device &dev, TREESTACK *treestack_ptr, const TREESTACK_TREE_NODES *inittree,
+                             const Parameters &rcstruct, long root, FILE *lenfp, long *current_iter, bool log_progress,
+                             long *neighbourhood_calls = nullptr);
+
 } // namespace lvbhost
 #endif

@@ -740,6 +740,95 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
     }
 }
 
+/* src/Solve.c:64-142, same loops and the same accept rule; the 2(n-3) getplen calls of one
+ * sweep position onwards are answered by ONE lvb_gpu_nni_neighbourhood call, made again only
+ * after a rearrangement was accepted (the lengths of the others are then stale). */
+long deterministic_hillclimb(Dataptr MSA, Device &dev, TREESTACK *treestack_ptr, const TREESTACK_TREE_NODES *inittree,
+                             const Parameters &rcstruct, long root, FILE *lenfp, long *current_iter, bool log_progress,
+                             long *neighbourhood_calls)
+{
+    (void)rcstruct;
+    const long n = MSA->n, number_of_internal_branches = MSA->numberofpossiblebranches - MSA->n;
+    TREESTACK_TREE_NODES *p_current_tree = treealloc(MSA, true);
+    TREESTACK_TREE_NODES *p_proposed_tree = treealloc(MSA, true);
+    treecopy(MSA, p_current_tree, inittree, true);
+    int dev_tree = -1, up_tree = -1;
+    gpu_check(lvb_gpu_tree_create(dev.ctx, &dev_tree));
+    gpu_check(lvb_gpu_tree_create(dev.ctx, &up_tree));
+    const int64_t stride = (int64_t)sizeof(TREESTACK_TREE_NODES);
+    auto topology_of = [&](const TREESTACK_TREE_NODES *t, const std::vector<int64_t> *dirty) {
+        lvb_gpu_topology tp = lvb_gpu_topology();
+        tp.left = &t[0].left;
+        tp.right = &t[0].right;
+        tp.stride_bytes = stride;
+        tp.root = root;
+        tp.dirty = dirty ? dirty->data() : nullptr;
+        tp.n_dirty = dirty ? (int64_t)dirty->size() : -1;
+        return tp;
+    };
+    int64_t len64 = 0;
+    {
+        const lvb_gpu_topology tp = topology_of(p_current_tree, nullptr); /* first evaluation: every node */
+        gpu_check(lvb_gpu_tree_commit(dev.ctx, dev_tree, &tp, &len64));
+    }
+    mark_all_clean(MSA, p_current_tree);
+    long current_tree_length = (long)len64;
+    std::vector<int64_t> lens((size_t)(2 * number_of_internal_branches)), dirty;
+    bool stale = true, newtree;
+    long calls = 0;
+    do
+    {
+        newtree = false;
+        for (long i = 0; i < number_of_internal_branches; i++)
+        {
+            for (int j = 0; j < 2; j++)
+            {
+                if (stale)
+                {
+                    const lvb_gpu_topology tp = topology_of(p_current_tree, nullptr);
+                    gpu_check(lvb_gpu_nni_neighbourhood(dev.ctx, dev_tree, up_tree, &tp, lens.data()));
+                    stale = false;
+                    calls++;
+                }
+                const long proposed_tree_length = (long)lens[(size_t)(2 * i + j)];
+                lvb_assert(proposed_tree_length >= 1L);
+                const long tree_length_change = proposed_tree_length - current_tree_length;
+                if (tree_length_change <= 0)
+                {
+                    mutate_deterministic(MSA, p_proposed_tree, p_current_tree, root, n + i, j == 1);
+                    if (tree_length_change < 0) /* very best so far */
+                    {
+                        ClearTreestack(treestack_ptr);
+                        current_tree_length = proposed_tree_length;
+                    }
+                    if (CompareHashTreeToHashstack(MSA, treestack_ptr, p_proposed_tree, root) == 1)
+                    {
+                        newtree = true;
+                        /* SwapTrees: the proposal becomes the current tree; on the device only the
+                         * rows mutate_deterministic dirtied are rewritten */
+                        collect_dirty(MSA, p_proposed_tree, dirty);
+                        std::swap(p_current_tree, p_proposed_tree);
+                        const lvb_gpu_topology tp = topology_of(p_current_tree, &dirty);
+                        gpu_check(lvb_gpu_tree_commit(dev.ctx, dev_tree, &tp, nullptr));
+                        mark_all_clean(MSA, p_current_tree);
+                        stale = true;
+                    }
+                }
+                if (log_progress && (*current_iter % STAT_LOG_INTERVAL) == 0 && lenfp)
+                    fprintf(lenfp, "  %-15.8f%-15ld%-16ld%-15ld\n", 0.0, *current_iter, treestack_ptr->next, current_tree_length);
+                *current_iter += 1;
+            }
+        }
+    } while (newtree);
+    gpu_check(lvb_gpu_tree_destroy(dev.ctx, dev_tree));
+    gpu_check(lvb_gpu_tree_destroy(dev.ctx, up_tree));
+    free(p_current_tree);
+    free(p_proposed_tree);
+    if (neighbourhood_calls)
+        *neighbourhood_calls = calls;
+    return current_tree_length;
+}
+
 /* GetSoln for R independent replicates.  The chains are split into G groups; every group has
  * its own device context (own stream, own copy of the leaf rows) and its own host thread, so
  * that one group's host work (proposing, replaying, compiling schedules) overlaps the other
@@ -784,9 +873,16 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         for (long i = 0; i < MSA->n; i++)
             rows[(size_t)i] = flat.data() + (size_t)i * (size_t)MSA->nwords;
         DNAToBinary(MSA, rows.data());
+        /* one thread per context: opening a device (CUDA context, pool allocation, 0.3 s each on the
+         * 8-GPU box) and uploading its copy of the leaf rows are independent of each other */
+        std::vector<std::thread> openers;
         for (int g = 1; g < G; g++)
-            device_open_encoded(extra[(size_t)g], dev.index + g % ND, MSA, rows.data(),
-                                first[(size_t)g + 1] - first[(size_t)g]);
+            openers.emplace_back([&, g] {
+                device_open_encoded(extra[(size_t)g], dev.index + g % ND, MSA, rows.data(),
+                                    first[(size_t)g + 1] - first[(size_t)g]);
+            });
+        for (auto &t : openers)
+            t.join();
     }
     const double setup_secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
     auto device_of = [&](int g) -> Device & { return g == 0 ? dev : extra[(size_t)g]; };

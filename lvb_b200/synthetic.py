@@ -96,6 +96,38 @@ def random_topology(n: int, seed: int = 1):
     return left, right, 0
 
 
+def shaped_topology(n: int, shape: str):
+    """extreme tree shapes, root = leaf 0: "caterpillar" (a chain of n-3 internal nodes) or
+    "balanced" (leaves paired level by level)"""
+    B = 2 * n - 3
+    left, right = np.full(B, -1, dtype=np.int64), np.full(B, -1, dtype=np.int64)
+    if shape == "caterpillar":
+        left[0], right[0] = n, 1
+        leaf = 2
+        for v in range(n, B):
+            if v + 1 < B:
+                left[v], right[v] = v + 1, leaf
+                leaf += 1
+            else:
+                left[v], right[v] = leaf, leaf + 1
+        return left, right, 0
+    if shape != "balanced":
+        raise ValueError(shape)
+    level, nxt = list(range(1, n)), n
+    while len(level) > 2:
+        new = []
+        for k in range(0, len(level) - 1, 2):
+            left[nxt], right[nxt] = level[k], level[k + 1]
+            new.append(nxt)
+            nxt += 1
+        if len(level) % 2:
+            new.append(level[-1])
+        level = new
+    left[0], right[0] = level
+    assert nxt == B
+    return left, right, 0
+
+
 def survey_alignment(n: int, m: int, seed: int = 1, p: float = 0.05) -> np.ndarray:
     """The exact generator of SURVEY.md appendix A (float64 draws), n x m uint8 states 0..3 in
     file order.  `survey_alignment(100, 10000, 1, 0.05)` written by `write_phylip` is the file

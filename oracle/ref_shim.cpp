@@ -254,6 +254,28 @@ extern "C"
 		return StartingTemperature(h->msa, (const TREESTACK_TREE_NODES *)tv, h->rc, root, LVB_FALSE);
 	}
 
+	/* deterministic_hillclimb (Solve.c:64-142; switched off in the reference's own GetSoln) on a
+	 * fresh tree stack.  out: final length, *current_iter, trees on the stack. */
+	void ref_deterministic_hillclimb(void *hv, const void *tv, long root, const char *outtree_path, long *out)
+	{
+		RefHandle *h = (RefHandle *)hv;
+		TREESTACK stack = CreateNewTreestack();
+		long iter = 0;
+		out[0] = deterministic_hillclimb(h->msa, &stack, (const TREESTACK_TREE_NODES *)tv, h->rc, root, stdout, &iter, LVB_FALSE);
+		out[1] = iter;
+		out[2] = stack.next;
+		if (outtree_path)
+		{
+			FILE *fp = fopen(outtree_path, "w");
+			if (fp)
+			{
+				PrintTreestack(h->msa, &stack, fp, LVB_FALSE);
+				fclose(fp);
+			}
+		}
+		FreeTreestackMemory(h->msa, &stack);
+	}
+
 	/* ---- timing legs for bench.py (cpu_baseline / --impl reference) ----
 	 * Full passes: dirty every internal node, call getplen; returns seconds for `reps` calls
 	 * and writes the last length to *len_out. */

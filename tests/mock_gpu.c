@@ -212,6 +212,55 @@ int lvb_gpu_score_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const 
     return 0;
 }
 
+/* every mutate_deterministic candidate (TreeOperations.c:105-158), each by a FULL oracle pass:
+ * the slowest, most literal reading of deterministic_hillclimb's loop (Solve.c:100-111) */
+int lvb_gpu_nni_neighbourhood(lvb_gpu_ctx *c, int tree, int scratch_tree, const lvb_gpu_topology *tp, int64_t *lengths)
+{
+    if (!c->ready[tree] || scratch_tree == tree || !c->used[scratch_tree])
+        return fail("neighbourhood: bad trees");
+    long *l0 = (long *)malloc((size_t)c->B * sizeof(long)), *r0 = (long *)malloc((size_t)c->B * sizeof(long));
+    long *par = (long *)malloc((size_t)c->B * sizeof(long));
+    for (long v = 0; v < c->B; v++)
+    {
+        l0[v] = strided(tp->left, tp->stride_bytes, v);
+        r0[v] = strided(tp->right, tp->stride_bytes, v);
+    }
+    for (long k = 0; k < tp->n_mod; k++)
+    {
+        l0[tp->mod_node[k]] = (long)tp->mod_left[k];
+        r0[tp->mod_node[k]] = (long)tp->mod_right[k];
+    }
+    for (long v = 0; v < c->B; v++)
+        if (v >= c->n || v == tp->root)
+            par[l0[v]] = par[r0[v]] = v;
+    for (long u = c->n; u < c->B; u++)
+        for (int left = 0; left < 2; left++)
+        {
+            memcpy(c->left, l0, (size_t)c->B * sizeof(long));
+            memcpy(c->right, r0, (size_t)c->B * sizeof(long));
+            const long v = par[u], a = l0[u], b = r0[u];
+            const long sis = l0[v] == u ? r0[v] : l0[v];
+            const long moved = left ? a : b;
+            if (l0[v] == u)
+                c->right[v] = moved;
+            else
+                c->left[v] = moved;
+            c->left[u] = left ? b : a;
+            c->right[u] = sis;
+            memcpy(c->scratch, c->rows[tree], (size_t)c->B * c->nwords * 8);
+            memcpy(c->scratch_chg, c->changes[tree], (size_t)c->B * sizeof(long));
+            oracle_dirty_all(c->n, c->nwords, c->scratch);
+            lengths[2 * (u - c->n) + left] =
+                oracle_getplen(c->n, c->nwords, c->left, c->right, (long)tp->root, c->scratch, c->scratch_chg);
+        }
+    c->ready[scratch_tree] = 0;
+    c->launches += 3;
+    free(l0);
+    free(r0);
+    free(par);
+    return 0;
+}
+
 int64_t lvb_gpu_launch_count(lvb_gpu_ctx *c) { return c ? c->launches : 0; }
 int lvb_gpu_synchronize(lvb_gpu_ctx *c)
 {

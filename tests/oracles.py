@@ -97,6 +97,7 @@ def ref() -> C.CDLL:
         L.ref_tree_rows.argtypes = [_vp, _vp, _vp]
         L.ref_starting_temperature.restype = C.c_double
         L.ref_starting_temperature.argtypes = [_vp, _vp, _l]
+        L.ref_deterministic_hillclimb.argtypes = [_vp, _vp, _l, C.c_char_p, _lp]
         L.ref_time_full_passes.restype = C.c_double
         L.ref_time_full_passes.argtypes = [_vp, _vp, _l, C.c_int, _lp]
         L.ref_time_proposals.restype = C.c_double

@@ -230,6 +230,67 @@ def test_nni_neighbourhood_batch(engine, n, m):
     engine.tree_destroy(t)
 
 
+@pytest.mark.parametrize("n,m,seed", [(5, 40, 1), (6, 33, 2), (30, 500, 3), (150, 20000, 4), (400, 3000, 5)])
+def test_nni_neighbourhood_call(engine, n, m, seed):
+    """lvb_gpu_nni_neighbourhood (up-pass + four-row kernel) == one incremental getplen per
+    mutate_deterministic candidate (Solve.c:100-111), and == full oracle passes on a sample"""
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=seed, p=0.08))
+    left, right, root = synthetic.random_topology(n, seed=seed + 10)
+    engine.upload(enc, max_trees=2)
+    t, s = engine.tree_create(), engine.tree_create()
+    topo = Topology(left, right, root)
+    base = engine.commit(t, topo)
+    cands = nni_neighbourhood(left, right, root, n)
+    want = engine.score_batch([t] * len(cands), cands)
+    got = engine.nni_neighbourhood(t, s, topo)
+    assert np.array_equal(got, want)
+    for k in range(0, len(cands), max(1, len(cands) // 12)):
+        assert got[k] == oracles.oracle_getplen(enc, cands[k].left, cands[k].right, root)[0], k
+    # the evaluated tree is untouched, the scratch tree is no longer an evaluated tree
+    assert engine.score_batch([t], [Topology(left, right, root, [])])[0] == base
+    with pytest.raises(GpuError, match="never been evaluated"):
+        engine.score_batch([s], [Topology(left, right, root, [])])
+    # after a rearrangement is committed the neighbourhood follows
+    pick = cands[len(cands) // 2]
+    engine.commit(t, pick)
+    cands2 = nni_neighbourhood(pick.left, pick.right, root, n)
+    got2 = engine.nni_neighbourhood(t, s, Topology(pick.left, pick.right, root))
+    assert np.array_equal(got2, engine.score_batch([t] * len(cands2), cands2))
+    engine.tree_destroy(t)
+    engine.tree_destroy(s)
+
+
+def test_nni_neighbourhood_ambiguity_and_shapes(engine, golden_dir):
+    """example alignment (padding: 984 sites) and caterpillar / balanced shapes with ambiguity codes"""
+    g = np.load(os.path.join(golden_dir, "example.npz"))
+    enc = g["enc"]
+    n = enc.shape[0]
+    engine.upload(enc, max_trees=2)
+    t, s = engine.tree_create(), engine.tree_create()
+    left, right, root = g["random_left"], g["random_right"], int(g["random_root"])
+    assert engine.commit(t, Topology(left, right, root)) == 11808
+    got = engine.nni_neighbourhood(t, s, Topology(left, right, root))
+    cands = nni_neighbourhood(left, right, root, n)
+    assert np.array_equal(got, engine.score_batch([t] * len(cands), cands))
+    engine.tree_destroy(t)
+    engine.tree_destroy(s)
+    rng = np.random.default_rng(5)
+    n, m = 40, 700
+    st = rng.integers(1, 16, size=(n, m), dtype=np.uint8)  # every non-empty state set, ambiguity included
+    enc = synthetic.pack_states(st)
+    for shape in ("caterpillar", "balanced"):
+        left, right, root = synthetic.shaped_topology(n, shape)
+        engine.upload(enc, max_trees=2)
+        t, s = engine.tree_create(), engine.tree_create()
+        engine.commit(t, Topology(left, right, root))
+        cands = nni_neighbourhood(left, right, root, n)
+        got = engine.nni_neighbourhood(t, s, Topology(left, right, root))
+        for k in range(len(cands)):
+            assert got[k] == oracles.oracle_getplen(enc, cands[k].left, cands[k].right, root)[0], (shape, k)
+        engine.tree_destroy(t)
+        engine.tree_destroy(s)
+
+
 @pytest.mark.parametrize("n,m,seed", [(5, 1, 1), (5, 16, 2), (6, 17, 3), (17, 4097, 4), (64, 8 * 16 * 256 + 5, 5), (500, 100000, 6)])
 def test_full_pass_shapes(engine, n, m, seed):
     """ragged row widths (1 word, not a multiple of the 16-byte column, of the 128-byte pad,
@@ -318,3 +379,21 @@ def test_full_size_2000x1M(engine):
     assert engine.commit(t, pick[1]) == full
     assert engine.commit(t, Topology(pick[1].left, pick[1].right, root)) == full
     engine.tree_destroy(t)
+
+
+def test_nni_neighbourhood_2000x1M(engine):
+    """all 3994 mutate_deterministic candidates of a 2000 x 1M tree in one call == the incremental
+    path on a sample of them (which test_full_size_2000x1M ties to the oracle)"""
+    n, nwords = 2000, 62500
+    enc = synthetic.random_packed(n, nwords, seed=2)
+    left, right, root = synthetic.random_topology(n, seed=8)
+    engine.upload(enc, max_trees=2)
+    t, s = engine.tree_create(), engine.tree_create()
+    engine.commit(t, Topology(left, right, root))
+    got = engine.nni_neighbourhood(t, s, Topology(left, right, root))
+    cands = nni_neighbourhood(left, right, root, n)
+    idx = list(range(0, len(cands), 97)) + [len(cands) - 1]
+    want = engine.score_batch([t] * len(idx), [cands[k] for k in idx])
+    assert np.array_equal(got[idx], want)
+    engine.tree_destroy(t)
+    engine.tree_destroy(s)

@@ -239,3 +239,77 @@ def test_pieces_cover_the_program_and_respect_levels(golden_dir, piece_size):
             stored_level[v] = lvl
     assert total == int(g["tbr_length"])
     assert np.array_equal(rows, g["tbr_rows_after"])
+
+
+def _nni_candidates(left, right, root, n):
+    """mutate_deterministic (TreeOperations.c:105-158) for every internal node and both sides,
+    in the order of deterministic_hillclimb's loops (Solve.c:100-103); plain test-input code"""
+    B = 2 * n - 3
+    parent = np.full(B, -1, dtype=np.int64)
+    for v in list(range(n, B)) + [root]:
+        parent[left[v]] = v
+        parent[right[v]] = v
+    for u in range(n, B):
+        v = int(parent[u])
+        a, b = int(left[u]), int(right[u])
+        c = int(right[v]) if left[v] == u else int(left[v])
+        for take_left in (False, True):
+            l2, r2 = left.copy(), right.copy()
+            moved = a if take_left else b
+            if l2[v] == u:
+                r2[v] = moved
+            else:
+                l2[v] = moved
+            l2[u], r2[u] = (b, c) if take_left else (a, c)
+            yield u, v, a, b, c, l2, r2
+
+
+@pytest.mark.parametrize("n,m,shape", [(5, 40, "random"), (6, 50, "random"), (37, 300, "random"), (120, 200, "random"),
+                                       (40, 100, "caterpillar"), (33, 100, "balanced"), (40, 100, "balanced")])
+def test_up_pass_program_and_four_row_nni_lengths(n, m, shape):
+    """The up-pass program (pre-order, previous result / stack slots) run by the numpy VM gives,
+    with the four-row evaluation on the rearranged branch, exactly the length a full oracle pass
+    returns for every mutate_deterministic candidate — the identity lvb_gpu_nni_neighbourhood
+    rests on (Fitch lengths do not depend on the root)."""
+    import oracles
+    from lvb_b200 import compile_up_pass, synthetic
+
+    rng = np.random.default_rng(n * 1000 + m)
+    st = rng.integers(1, 16, size=(n, m), dtype=np.uint8) if shape != "random" else synthetic.states(n, m, seed=n, p=0.15)
+    enc = synthetic.pack_states(st)
+    left, right, root = synthetic.random_topology(n, seed=n + 1) if shape == "random" else synthetic.shaped_topology(n, shape)
+    base, rows, _ = oracles.oracle_getplen(enc, left, right, root)
+    instr, slots = compile_up_pass(n, Topology(left, right, root))
+    B = 2 * n - 3
+    assert instr.shape == (n - 3, 4)
+    assert sorted(instr[:, 2].tolist()) == list(range(n, B))      # every internal node once
+    assert np.all(instr[:, 3] & fitch_vm.CTL_STORE)
+    assert slots <= max(1, int(np.ceil(np.log2(n))))
+    # no instruction reads a row the program stores: internal operands are rows of the evaluated tree
+    up = rows.copy()
+    fitch_vm.run_program(instr, _ReadLowWriteUp(rows, up), n, store=True)
+    for u, v, a, b, c, l2, r2 in _nni_candidates(left, right, root, n):
+        A, Bq, Cq = rows[a], rows[b], rows[c]
+        D = rows[root] if v == root else up[v]
+
+        def join(p, q, r, s):
+            pq, c1 = fitch_vm.fitch_rows(p, q)
+            rs, c2 = fitch_vm.fitch_rows(r, s)
+            return c1 + c2 + fitch_vm.fitch_rows(pq, rs)[1]
+
+        cur = join(A, Bq, Cq, D)
+        got = base - cur + (join(Bq, Cq, A, D) if l2[u] == b else join(A, Cq, Bq, D))
+        assert got == oracles.oracle_getplen(enc, l2, r2, root)[0], (u, l2[u] == b)
+
+
+class _ReadLowWriteUp:
+    """rows[] as the up-pass sees them: operands come from the evaluated tree, stores go to the scratch tree"""
+
+    def __init__(self, low, up):
+        self.low, self.up = low, up
+
+    def __getitem__(self, v):
+        return self.low[v]
+
+    def __setitem__(self, v, val):
+        self.up[v] = val
