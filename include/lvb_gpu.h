@@ -107,6 +107,16 @@ int lvb_gpu_commit_batch(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, con
 int lvb_gpu_score_batch(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
                         int64_t *lengths);
 
+/* The same in two halves, so that a host thread that drives several SA chains can prepare the
+ * proposals of one set of chains while the device scores another set's: submit enqueues the
+ * batch and returns a ticket, wait blocks until that batch is done and delivers its n_cand
+ * lengths.  Batches run in submission order on the context's stream; commits enqueued after a
+ * submit do not disturb it (a chain's commit always follows the wait of its own proposals).
+ * At most 7 other commit/score calls may lie between a submit and its wait. */
+int lvb_gpu_score_batch_submit(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                               int *ticket);
+int lvb_gpu_batch_wait(lvb_gpu_ctx *ctx, int ticket, int64_t *lengths);
+
 /* ---- the exhaustive NNI neighbourhood of one evaluated tree, in one call: what the loop of
  * deterministic_hillclimb (Solve.c:100-111) computes with 2(n-3) x (mutate_deterministic,
  * TreeOperations.c:105-158, + getplen).  lengths[2*(u-n) + j] is the length getplen would return

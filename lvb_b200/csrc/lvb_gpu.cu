@@ -111,6 +111,7 @@ struct Staging
     size_t cap_len = 0;
     cudaEvent_t done = nullptr; /* recorded after the last kernel that reads this slot */
     bool pending = false;
+    int64_t unclaimed = 0;      /* > 0: a submitted batch whose lengths lvb_gpu_batch_wait has not fetched yet */
 };
 
 struct lvb_gpu_ctx
@@ -130,7 +131,7 @@ struct lvb_gpu_ctx
     std::vector<ScheduleCompiler *> sc; /* one per host thread that compiles */
 
     /* batch staging */
-    static const int kRing = 4;
+    static const int kRing = 8;
     Staging ring[kRing];
     int ring_next = 0;
     std::vector<std::vector<FitchInstr>> c_instr;              /* per candidate */
@@ -148,6 +149,8 @@ struct lvb_gpu_ctx
     size_t cap_dep = 0;
     long long *d_nni = nullptr, *h_nni = nullptr;      /* [cap_nni] length differences of an NNI neighbourhood */
     size_t cap_nni = 0;
+    int compile_par_min = 8;  /* host compile: batches of >= min candidates are spread over
+                                                        * OpenMP threads, >= grain candidates each */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
     bool last_dep = false;
@@ -236,6 +239,9 @@ static int acquire_slot(lvb_gpu_ctx *c, size_t bytes, size_t n_cand, int *slot_o
     const int slot = c->ring_next;
     c->ring_next = (c->ring_next + 1) % lvb_gpu_ctx::kRing;
     Staging &st = c->ring[slot];
+    if (st.unclaimed)
+        return fail("too many submitted batches are waiting for lvb_gpu_batch_wait (at most %d calls may lie between "
+                    "a submit and its wait)", lvb_gpu_ctx::kRing - 1);
     if (st.pending)
     {
         CU(cudaEventSynchronize(st.done));
@@ -299,7 +305,7 @@ static int drain_kernel_events(lvb_gpu_ctx *c)
 }
 
 /* launch the batch that is resident in staging slot c->last_slot */
-static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always = false)
+static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always = false, bool defer = false)
 {
     const int64_t K = c->last_K;
     const bool store = c->last_store;
@@ -366,12 +372,12 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
                                   c->last_max_instr, c->stream));
         c->launches++;
     }
-    if (c->comm && (lengths || !store || reduce_always))
+    if (c->comm && (lengths || !store || reduce_always || defer))
     {
         int r = g_nccl.AllReduce(c->d_lengths, c->d_lengths, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
         if (r != 0)
             return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
-        if (lengths)
+        if (lengths || defer)
             CU(cudaMemcpyAsync(st.h_len, c->d_lengths, K * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
     }
     CU(cudaEventRecord(st.done, c->stream));
@@ -379,6 +385,8 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     const double ts1 = c->profile ? wall_now() : 0;
     if (c->profile)
         c->t_submit += ts1 - ts0;
+    if (defer)
+        st.unclaimed = K;
     if (lengths)
     {
         CU(cudaEventSynchronize(st.done));
@@ -393,7 +401,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
 
 /* compile + launch one batch; store: commit semantics, else score semantics */
 static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_topology *topos, bool store,
-                     int64_t *lengths)
+                     int64_t *lengths, int *ticket = nullptr)
 {
     if (!c->pool)
         return fail("no alignment on the device: call lvb_gpu_matrix_upload first");
@@ -436,8 +444,10 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     /* host compile, one candidate at a time; spread over host threads when the batch is large */
     int nthreads = 1;
 #ifdef _OPENMP
-    if (K >= 64)
-        nthreads = std::min<int>({(int)c->sc.size(), omp_get_max_threads(), (int)(K / 16)});
+    /* always the caller's whole team: libgomp re-creates threads when consecutive parallel regions
+     * of one thread differ in size (measured: 3x slower rounds with teams alternating 8 / 16) */
+    if (K >= c->compile_par_min)
+        nthreads = std::min<int>((int)c->sc.size(), omp_get_max_threads());
 #endif
     bool bad = false;
     auto compile_one = [&](int64_t k, ScheduleCompiler *sc) {
@@ -459,7 +469,7 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     if (nthreads > 1)
     {
 #ifdef _OPENMP
-#pragma omp parallel for schedule(static) num_threads(nthreads)
+#pragma omp parallel for schedule(dynamic, 2) num_threads(nthreads)
         for (int64_t k = 0; k < K; k++)
             compile_one(k, c->sc[omp_get_thread_num()]);
 #endif
@@ -615,6 +625,11 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         c->n_calls++;
         c->n_cand_total += K;
     }
+    if (ticket)
+    { /* asynchronous: the lengths are fetched later through the staging slot */
+        *ticket = slot;
+        return launch_resident(c, nullptr, false, true);
+    }
     return launch_resident(c, lengths);
 }
 
@@ -746,6 +761,9 @@ extern "C"
         const char *tw = getenv("LVB_GPU_TARGET_WARPS");
         if (tw && atoll(tw) > 0)
             c->target_warps = atoll(tw);
+        const char *cp = getenv("LVB_GPU_COMPILE_PAR");
+        if (cp && atoi(cp) > 0)
+            c->compile_par_min = atoi(cp);
         const char *v1 = getenv("LVB_GPU_SCORE_V1");
         c->score_v1 = v1 && atoi(v1) != 0;
         const char *pf = getenv("LVB_GPU_PROFILE");
@@ -957,6 +975,35 @@ extern "C"
         if (!c || !trees || !topos || !lengths)
             return fail("lvb_gpu_score_batch: null argument");
         return run_batch(c, n_cand, trees, topos, false, lengths);
+    }
+
+    int lvb_gpu_score_batch_submit(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                   int *ticket)
+    {
+        if (!c || !trees || !topos || !ticket)
+            return fail("lvb_gpu_score_batch_submit: null argument");
+        if (n_cand <= 0)
+            return fail("lvb_gpu_score_batch_submit: empty batch");
+        return run_batch(c, n_cand, trees, topos, false, nullptr, ticket);
+    }
+
+    int lvb_gpu_batch_wait(lvb_gpu_ctx *c, int ticket, int64_t *lengths)
+    {
+        if (!c || !lengths || ticket < 0 || ticket >= lvb_gpu_ctx::kRing)
+            return fail("lvb_gpu_batch_wait: bad argument");
+        Staging &st = c->ring[ticket];
+        if (!st.unclaimed)
+            return fail("lvb_gpu_batch_wait: ticket %d names no submitted batch", ticket);
+        CU(cudaSetDevice(c->device));
+        const double t0 = c->profile ? wall_now() : 0;
+        CU(cudaEventSynchronize(st.done));
+        if (c->profile)
+            c->t_wait += wall_now() - t0;
+        st.pending = false;
+        for (int64_t k = 0; k < st.unclaimed; k++)
+            lengths[k] = (int64_t)st.h_len[k];
+        st.unclaimed = 0;
+        return 0;
     }
 
     int lvb_gpu_nni_neighbourhood(lvb_gpu_ctx *c, int tree, int scratch_tree, const lvb_gpu_topology *topo,

@@ -64,6 +64,8 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_tree_commit.argtypes = [vp, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_commit_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_score_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
+    lib.lvb_gpu_score_batch_submit.argtypes = [vp, i64, i32p, C.POINTER(_Topo), i32p]
+    lib.lvb_gpu_batch_wait.argtypes = [vp, C.c_int, C.POINTER(i64)]
     lib.lvb_gpu_nni_neighbourhood.argtypes = [vp, C.c_int, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_download_row.argtypes = [vp, C.c_int, i64, vp]
     lib.lvb_gpu_tree_changes.argtypes = [vp, C.c_int, vp]
@@ -245,6 +247,22 @@ class Engine:
 
     def score_batch(self, trees: Sequence[int], topos: Sequence[Topology]) -> np.ndarray:
         return self._batch(self.lib.lvb_gpu_score_batch, trees, topos)
+
+    def score_batch_submit(self, trees: Sequence[int], topos: Sequence[Topology]):
+        """enqueue a score batch; returns (ticket, n) for batch_wait"""
+        k = len(topos)
+        tarr = (C.c_int * k)(*[int(t) for t in trees])
+        sarr = (_Topo * k)()
+        for i, tp in enumerate(topos):
+            tp.fill(sarr[i])
+        ticket = C.c_int(-1)
+        _check(self.lib.lvb_gpu_score_batch_submit(self.ctx, k, tarr, sarr, C.byref(ticket)))
+        return ticket.value, k
+
+    def batch_wait(self, ticket) -> np.ndarray:
+        out = np.zeros(ticket[1], dtype=np.int64)
+        _check(self.lib.lvb_gpu_batch_wait(self.ctx, ticket[0], out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return out
 
     def nni_neighbourhood(self, tree: int, scratch_tree: int, topo: Topology) -> np.ndarray:
         """lengths of all 2(n-3) mutate_deterministic candidates of the evaluated `tree`

@@ -64,7 +64,7 @@ def load_host_library() -> C.CDLL:
     L.lvbh_getplen.restype = _l
     L.lvbh_getplen.argtypes = [_vp, _vp, _l]
     L.lvbh_hillclimb.argtypes = [_vp, C.c_int, _vp, _l, C.c_char_p, _lp]
-    L.lvbh_search.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _l, C.c_int, C.c_char_p,
+    L.lvbh_search.argtypes = [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _l, C.c_int, C.c_int, C.c_char_p,
                               C.c_char_p, _vp, _vp, C.POINTER(C.c_double)]
     _lib = L
     return L
@@ -139,13 +139,13 @@ class HostMSA:
 
     def search(self, seed: int, algorithm: int = 1, cooling: int = 0, device: int = 0, max_trees: int = 0,
                replicates: int = 1, speculation: int = 0, max_rearrangements: int = 0, host_threads: int = 1,
-               tsv_path: Optional[str] = None, outtree_path: Optional[str] = None):
+               groups: int = 0, tsv_path: Optional[str] = None, outtree_path: Optional[str] = None):
         """GetSoln for `replicates` chains; returns a list of dicts (one per chain)."""
         out = np.zeros(7 * replicates, dtype=np.int64)
         t0 = np.zeros(replicates, dtype=np.float64)
         secs = C.c_double(0)
         _check(self.L.lvbh_search(self.h, device, seed, algorithm, cooling, max_trees, replicates, speculation,
-                                  max_rearrangements, host_threads, tsv_path.encode() if tsv_path else None,
+                                  max_rearrangements, host_threads, groups, tsv_path.encode() if tsv_path else None,
                                   outtree_path.encode() if outtree_path else None, out.ctypes.data, t0.ctypes.data,
                                   C.byref(secs)))
         keys = ("final_length", "rearrangements", "topologies", "initial_length", "trees_scored", "score_launches", "groups")

@@ -262,7 +262,7 @@ long lvbh_getplen(void *hv, void *t, long root)
  * start_t (per chain): starting temperature.  tsv_path / outtree_path may be NULL (chain 0 only;
  * further chains write outtree_path.r<k>). ---- */
 int lvbh_search(void *hv, int device, int seed, int algorithm, int cooling, int max_trees_kept, int replicates,
-                int speculation, long max_rearrangements, int host_threads, const char *tsv_path, const char *outtree_path, long *out,
+                int speculation, long max_rearrangements, int host_threads, int groups, const char *tsv_path, const char *outtree_path, long *out,
                 double *start_t, double *seconds)
 {
     Handle *h = (Handle *)hv;
@@ -276,6 +276,7 @@ int lvbh_search(void *hv, int device, int seed, int algorithm, int cooling, int 
         rc.speculation = speculation;
         rc.max_rearrangements = max_rearrangements;
         rc.n_processors_available = host_threads < 1 ? 1 : host_threads;
+        rc.groups = groups < 0 ? 0 : groups;
         rc.device = device;
         Device dev;
         device_open(dev, device, &h->msa, replicates);

@@ -29,6 +29,9 @@
 #include <cmath>
 #include <algorithm>
 #include <cstring>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include "lvb_host.h"
 
@@ -128,6 +131,8 @@ struct Chain
     SAState S;
 
     int kmax = 32, k_now = 1;
+    double ema_used = 0, ema_taken = 0; /* recent proposals consumed / accepted (speculation depth) */
+    bool shared_device = false;         /* many chains per device: wasted proposals cost device time */
     struct Spec
     {
         SAState mid; /* state after the proposal was generated, before the acceptance draw */
@@ -581,13 +586,24 @@ struct Chain
             S = spec_end;
         if (S.phase == PH_AN_BEGIN && log_progress)
             printf("  SA Starting Temperature: %-.8f\n", S.t0);
-        /* speculation depth for the next round */
+        /* speculation depth for the next round.  With acceptance probability p per proposal a batch
+         * of K uses (1 - (1-p)^K) / p of its proposals; the rest is scored for nothing.  p is
+         * estimated from the recent rounds (exponentially forgotten counts) and K is a multiple of
+         * the expected run of rejections 1/p: about two runs when this chain has the device to
+         * itself (a round costs a launch and a read-back whatever K is, wasted proposals are
+         * nearly free), under one run when many chains share the device (the device is the
+         * bottleneck, a wasted proposal costs as much as a useful one).  Results do not depend
+         * on K (tested). */
+        ema_used = 0.9 * ema_used + (taken < 0 ? n_spec : taken + 1);
+        ema_taken = 0.9 * ema_taken + (taken < 0 ? 0 : 1);
         if (rc.speculation > 0)
             k_now = kmax;
-        else if (taken < 0)
-            k_now = std::min(kmax, k_now * 2);
         else
-            k_now = std::max(1, std::min(kmax, (k_now + 2 * (taken + 1)) / 2));
+        {
+            const double p_acc = (ema_taken + 0.25) / (ema_used + 0.5);
+            const double want = (shared_device ? 0.75 : 2.0) / p_acc;
+            k_now = want >= kmax ? kmax : std::max(1, (int)(want + 0.5));
+        }
     }
 };
 
@@ -599,134 +615,173 @@ static void gpu_check(int rc_)
 
 /* src/Solve.c:481-609 for R chains at once */
 /* One group of chains [r0, r1) on one device context, driven by the calling thread (its inner
- * loops over chains use `threads` OpenMP threads).  Rounds: advance every chain (speculative
- * proposals), one commit launch for the chains whose device tree must catch up, one score launch
- * for all proposals, replay. */
+ * loops over chains use `threads` OpenMP threads).  The group is worked as two alternating
+ * halves: while the device scores the proposals of one half, the host replays the acceptances
+ * of the other half, generates its next proposals and compiles their programs.  A round of a
+ * half: advance every chain (speculative proposals), one commit launch for the chains whose
+ * device tree must catch up, one score launch for all proposals (submitted, not waited for);
+ * then, a half-round later, wait and replay.  Chains never interact, so the result of a chain
+ * does not depend on which half or group it is in (tested). */
 static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int r0, int r1, int threads,
                       long &score_launches, long &rounds, double prof[4])
 {
-    std::vector<int> trees;
-    std::vector<lvb_gpu_topology> topos;
-    std::vector<int64_t> lens, clen((size_t)(r1 - r0), 0);
-    std::vector<int> owner;
-    std::vector<size_t> offsets;
+    struct Half
+    {
+        int a = 0, b = 0;
+        bool alive = true, inflight = false;
+        int ticket = -1;
+        std::vector<int> trees, owner;
+        std::vector<lvb_gpu_topology> topos;
+        std::vector<int64_t> lens, clen;
+        std::vector<size_t> offsets;
+    };
     const size_t stride = sizeof(TREESTACK_TREE_NODES);
     (void)MSA;
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto since = [](std::chrono::steady_clock::time_point a) {
         return std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
     };
-    for (;;)
+    /* site-block mode keeps the ranks in lock-step through the all-reduce: one half */
+    const bool whole = dev.word_count >= 0 && dev.word_count != MSA->nwords;
+#ifdef _OPENMP
+    /* this driver thread's team size, also seen by the library when it spreads the schedule
+     * compile of a batch over threads (omp_get_max_threads there) */
+    omp_set_num_threads(std::max(1, threads));
+#endif
+    const int nh = (r1 - r0 >= 2 && !whole) ? 2 : 1;
+    Half H[2];
+    for (int x = 0; x < nh; x++)
     {
-        bool alive = false;
-        auto tp0 = now();
-        /* chains are independent between device calls: spread them over the host threads (-p) */
-        std::string failure;
+        H[x].a = r0 + (int)((long)(r1 - r0) * x / nh);
+        H[x].b = r0 + (int)((long)(r1 - r0) * (x + 1) / nh);
+        H[x].clen.assign((size_t)(H[x].b - H[x].a), 0);
+    }
+    std::string failure;
+
+    /* first part of a round: up to the submitted score launch */
+    auto prep = [&](Half &h) {
+        for (;;)
+        {
+            auto tp0 = now();
+            /* chains are independent between device calls: spread them over the host threads (-p) */
 #pragma omp parallel for schedule(dynamic, 1) num_threads(threads) if (threads > 1)
-        for (int r = r0; r < r1; r++)
-        {
-            try
+            for (int r = h.a; r < h.b; r++)
             {
-                chains[(size_t)r].advance();
-            }
-            catch (const LvbError &e)
-            {
+                try
+                {
+                    chains[(size_t)r].advance();
+                }
+                catch (const LvbError &e)
+                {
 #pragma omp critical
-                failure = e.message;
+                    failure = e.message;
+                }
             }
-        }
-        if (!failure.empty())
-            crash("%s", failure.c_str());
-        for (int r = r0; r < r1; r++)
-            alive = alive || chains[(size_t)r].S.phase != PH_DONE;
-        prof[0] += since(tp0);
-        rounds++;
-        tp0 = now();
-        /* what the device trees must catch up with (at most one request per chain), one launch */
-        trees.clear();
-        topos.clear();
-        owner.clear();
-        bool want = false;
-        for (int r = r0; r < r1; r++)
-        {
-            Chain &c = chains[(size_t)r];
-            if (!c.commit.used)
-                continue;
-            lvb_gpu_topology tp = lvb_gpu_topology();
-            tp.left = &c.cur[0].left;
-            tp.right = &c.cur[0].right;
-            tp.stride_bytes = (int64_t)stride;
-            tp.root = c.root;
-            tp.dirty = c.commit.dirty.data();
-            tp.n_dirty = c.commit.all ? -1 : (int64_t)c.commit.dirty.size();
-            trees.push_back(c.dev_tree);
-            topos.push_back(tp);
-            owner.push_back(r);
-            want = want || c.commit.want_length;
-        }
-        if (!trees.empty())
-        {
-            lens.resize(trees.size());
-            gpu_check(lvb_gpu_commit_batch(dev.ctx, (int64_t)trees.size(), trees.data(), topos.data(),
-                                           want ? lens.data() : nullptr));
-            for (size_t i = 0; i < owner.size(); i++)
+            if (!failure.empty())
+                crash("%s", failure.c_str());
+            h.alive = false;
+            for (int r = h.a; r < h.b; r++)
+                h.alive = h.alive || chains[(size_t)r].S.phase != PH_DONE;
+            prof[0] += since(tp0);
+            rounds++;
+            tp0 = now();
+            /* what the device trees must catch up with (at most one request per chain), one launch */
+            h.trees.clear();
+            h.topos.clear();
+            h.owner.clear();
+            bool want = false;
+            for (int r = h.a; r < h.b; r++)
             {
-                Chain &c = chains[(size_t)owner[i]];
-                if (c.commit.want_length)
-                    clen[(size_t)(owner[i] - r0)] = lens[i];
-                c.commit.used = c.commit.all = c.commit.want_length = false;
-                c.commit.dirty.clear();
-            }
-        }
-        prof[1] += since(tp0);
-        if (!alive)
-            break;
-        tp0 = now();
-        /* proposals of all chains in one launch */
-        trees.clear();
-        topos.clear();
-        for (int r = r0; r < r1; r++)
-        {
-            Chain &c = chains[(size_t)r];
-            for (int k = 0; k < c.n_spec; k++)
-            {
-                const Proposal &pr = c.cand[(size_t)k];
+                Chain &c = chains[(size_t)r];
+                if (!c.commit.used)
+                    continue;
                 lvb_gpu_topology tp = lvb_gpu_topology();
-                tp.left = &c.cur[0].left; /* the current tree ... */
+                tp.left = &c.cur[0].left;
                 tp.right = &c.cur[0].right;
                 tp.stride_bytes = (int64_t)stride;
                 tp.root = c.root;
-                tp.dirty = pr.dirty.data();
-                tp.n_dirty = (int64_t)pr.dirty.size();
-                tp.mod_node = pr.mod_node.data(); /* ... with the links this proposal rewired */
-                tp.mod_left = pr.mod_left.data();
-                tp.mod_right = pr.mod_right.data();
-                tp.n_mod = (int64_t)pr.mod_node.size();
-                trees.push_back(c.dev_tree);
-                topos.push_back(tp);
+                tp.dirty = c.commit.dirty.data();
+                tp.n_dirty = c.commit.all ? -1 : (int64_t)c.commit.dirty.size();
+                h.trees.push_back(c.dev_tree);
+                h.topos.push_back(tp);
+                h.owner.push_back(r);
+                want = want || c.commit.want_length;
             }
+            if (!h.trees.empty())
+            {
+                h.lens.resize(h.trees.size());
+                gpu_check(lvb_gpu_commit_batch(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
+                                               want ? h.lens.data() : nullptr));
+                for (size_t i = 0; i < h.owner.size(); i++)
+                {
+                    Chain &c = chains[(size_t)h.owner[i]];
+                    if (c.commit.want_length)
+                        h.clen[(size_t)(h.owner[i] - h.a)] = h.lens[i];
+                    c.commit.used = c.commit.all = c.commit.want_length = false;
+                    c.commit.dirty.clear();
+                }
+            }
+            prof[1] += since(tp0);
+            if (!h.alive)
+                return;
+            tp0 = now();
+            /* proposals of all chains of the half in one launch */
+            h.trees.clear();
+            h.topos.clear();
+            h.offsets.resize((size_t)(h.b - h.a));
+            for (int r = h.a; r < h.b; r++)
+            {
+                Chain &c = chains[(size_t)r];
+                h.offsets[(size_t)(r - h.a)] = h.trees.size();
+                for (int k = 0; k < c.n_spec; k++)
+                {
+                    const Proposal &pr = c.cand[(size_t)k];
+                    lvb_gpu_topology tp = lvb_gpu_topology();
+                    tp.left = &c.cur[0].left; /* the current tree ... */
+                    tp.right = &c.cur[0].right;
+                    tp.stride_bytes = (int64_t)stride;
+                    tp.root = c.root;
+                    tp.dirty = pr.dirty.data();
+                    tp.n_dirty = (int64_t)pr.dirty.size();
+                    tp.mod_node = pr.mod_node.data(); /* ... with the links this proposal rewired */
+                    tp.mod_left = pr.mod_left.data();
+                    tp.mod_right = pr.mod_right.data();
+                    tp.n_mod = (int64_t)pr.mod_node.size();
+                    h.trees.push_back(c.dev_tree);
+                    h.topos.push_back(tp);
+                }
+            }
+            h.lens.resize(h.trees.size());
+            if (!h.trees.empty())
+            {
+                gpu_check(lvb_gpu_score_batch_submit(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
+                                                     &h.ticket));
+                score_launches++;
+                h.inflight = true;
+            }
+            prof[2] += since(tp0);
+            if (h.inflight)
+                return;
+            /* nothing to score (every live chain only changed phase): replay and go round again */
+            auto tp1 = now();
+            for (int r = h.a; r < h.b; r++)
+                chains[(size_t)r].resolve(&h.clen[(size_t)(r - h.a)], nullptr);
+            prof[3] += since(tp1);
         }
-        lens.resize(trees.size());
-        if (!trees.empty())
-        {
-            gpu_check(lvb_gpu_score_batch(dev.ctx, (int64_t)trees.size(), trees.data(), topos.data(), lens.data()));
-            score_launches++;
-        }
+    };
+    /* second part: the lengths are known */
+    auto finish = [&](Half &h) {
+        auto tp0 = now();
+        gpu_check(lvb_gpu_batch_wait(dev.ctx, h.ticket, h.lens.data()));
+        h.inflight = false;
         prof[2] += since(tp0);
         tp0 = now();
-        offsets.resize((size_t)(r1 - r0));
-        size_t off = 0;
-        for (int r = r0; r < r1; r++)
-        {
-            offsets[(size_t)(r - r0)] = off;
-            off += (size_t)chains[(size_t)r].n_spec;
-        }
 #pragma omp parallel for schedule(dynamic, 1) num_threads(threads) if (threads > 1)
-        for (int r = r0; r < r1; r++)
+        for (int r = h.a; r < h.b; r++)
         {
             try
             {
-                chains[(size_t)r].resolve(&clen[(size_t)(r - r0)], lens.data() + offsets[(size_t)(r - r0)]);
+                chains[(size_t)r].resolve(&h.clen[(size_t)(r - h.a)], h.lens.data() + h.offsets[(size_t)(r - h.a)]);
             }
             catch (const LvbError &e)
             {
@@ -737,6 +792,15 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
         if (!failure.empty())
             crash("%s", failure.c_str());
         prof[3] += since(tp0);
+    };
+    for (int x = 0; x < nh; x++)
+        prep(H[x]);
+    for (int x = 0; H[0].inflight || H[nh - 1].inflight; x = (x + 1) % nh)
+    {
+        if (!H[x].inflight)
+            continue;
+        finish(H[x]);
+        prep(H[x]);
     }
 }
 
@@ -851,13 +915,13 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
     }
     const int host_threads = std::max(1, rc.n_processors_available);
     /* Replicates are spread over rc.devices GPUs (device, device+1, ...: no communication between
-     * them, BASELINE.json configs[4]) and, on each GPU, over driver groups.  auto: about 8 chains
-     * per group, at most 4 groups per GPU — measured on a 16-core host with one B200: 64 chains of
-     * 1000 x 200k run 1.0 / 1.4 / 1.7 / 1.3 / 1.1 times the single-group rate with 1 / 2 / 4 / 8 / 16
-     * groups (more driver threads contend in the CUDA driver) */
+     * them, BASELINE.json configs[4]); auto: ONE driver group per GPU, working its chains as two
+     * alternating halves with all of this GPU's share of the host threads (-p) on the per-chain
+     * work and on the schedule compile.  Measured on a 16-core host with one B200, 64 chains of
+     * 1000 x 200k (profiles/r01f_sa_host_profile.log): 1 group 1.60 s, 2 groups 1.95 s, 4 groups
+     * 2.1 s — more driver threads contend in the CUDA driver and for the cores.  -G overrides. */
     const int ND = std::max(1, std::min(rc.devices, R));
-    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND)
-                                : std::min(std::min(std::max(1, host_threads / ND), 4), (R / ND + 7) / 8);
+    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : 1;
     per_dev = std::max(1, per_dev);
     int G = std::max(1, std::min(ND * per_dev, R));
     if (dev.word_count >= 0 && dev.word_count != MSA->nwords)
@@ -892,6 +956,7 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
             int t = -1;
             gpu_check(lvb_gpu_tree_create(device_of(g).ctx, &t));
             chains[(size_t)r].init(MSA, rc, r, t, rc.speculation);
+            chains[(size_t)r].shared_device = R / ND >= 4;
             chains[(size_t)r].stack = &stacks[(size_t)r];
             if (r == 0)
             {

@@ -28,7 +28,11 @@ struct lvb_gpu_ctx
     uint64_t *scratch;
     long *scratch_chg;
     int64_t launches;
+    int64_t *ticket_len[8]; /* submitted batches waiting for lvb_gpu_batch_wait */
+    int64_t ticket_n[8];
+    int ticket_next;
 };
+#define MOCK_TICKETS 8
 
 static char g_err[512];
 static int fail(const char *msg)
@@ -209,6 +213,29 @@ int lvb_gpu_score_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const 
         memcpy(c->scratch_chg, c->changes[t], (size_t)c->B * sizeof(long));
         lengths[k] = evaluate(c, &topos[k], c->scratch, c->scratch_chg);
     }
+    return 0;
+}
+
+/* asynchronous halves: the mock computes at submit time and hands the lengths over at wait time */
+int lvb_gpu_score_batch_submit(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos, int *ticket)
+{
+    const int t = c->ticket_next;
+    c->ticket_next = (c->ticket_next + 1) % MOCK_TICKETS;
+    if (c->ticket_n[t])
+        return fail("too many submitted batches");
+    c->ticket_len[t] = (int64_t *)realloc(c->ticket_len[t], (size_t)n_cand * sizeof(int64_t));
+    if (lvb_gpu_score_batch(c, n_cand, trees, topos, c->ticket_len[t]))
+        return 1;
+    c->ticket_n[t] = n_cand;
+    *ticket = t;
+    return 0;
+}
+int lvb_gpu_batch_wait(lvb_gpu_ctx *c, int ticket, int64_t *lengths)
+{
+    if (ticket < 0 || ticket >= MOCK_TICKETS || !c->ticket_n[ticket])
+        return fail("no such ticket");
+    memcpy(lengths, c->ticket_len[ticket], (size_t)c->ticket_n[ticket] * sizeof(int64_t));
+    c->ticket_n[ticket] = 0;
     return 0;
 }
 

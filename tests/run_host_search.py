@@ -3,7 +3,7 @@ its own and print one JSON line.  With --mock the lvb_gpu_* entry points are ans
 tests/mock_gpu.c (CPU oracle) — for the `-m "not gpu"` suite; without it the real
 liblvbgpu.so and a GPU are used.
 
-usage: run_host_search.py [--mock] <alignment.npz key | path.phy> seed algorithm [speculation] [replicates] [max_rearr] [host_threads]
+usage: run_host_search.py [--mock] <alignment.npz key | path.phy> seed algorithm [speculation] [replicates] [max_rearr] [host_threads] [groups]
 """
 import ctypes as C
 import hashlib
@@ -50,6 +50,7 @@ def main():
     reps = int(args[4]) if len(args) > 4 else 1
     max_rearr = int(args[5]) if len(args) > 5 else 0
     threads = int(args[6]) if len(args) > 6 else 1
+    groups = int(args[7]) if len(args) > 7 else 0
     if src.endswith(".phy"):
         msa = host.HostMSA.load(src)
     else:
@@ -59,7 +60,7 @@ def main():
     with tempfile.TemporaryDirectory() as d:
         tsv, out = os.path.join(d, "t.tsv"), os.path.join(d, "outtree")
         res = msa.search(seed, algorithm=algo, speculation=spec, replicates=reps, max_rearrangements=max_rearr, host_threads=threads,
-                         tsv_path=tsv, outtree_path=out)
+                         groups=groups, tsv_path=tsv, outtree_path=out)
         line = {"mock": mock, "results": res, "tsv_md5": md5(tsv), "outtree_md5": md5(out),
                 "tsv_head": open(tsv).read().split("\n")[:41],
                 "outtrees": [md5(out + (f".r{r}" if r else "")) for r in range(reps)]}

@@ -260,6 +260,38 @@ def test_nni_neighbourhood_call(engine, n, m, seed):
     engine.tree_destroy(s)
 
 
+def test_submit_and_wait_halves(engine):
+    """lvb_gpu_score_batch_submit / lvb_gpu_batch_wait: several batches in flight, a commit of
+    another tree in between, lengths identical to the synchronous call; misuse is loud"""
+    n, m = 60, 4000
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=21, p=0.06))
+    engine.upload(enc, max_trees=2)
+    t0, t1 = engine.tree_create(), engine.tree_create()
+    la, ra, roota = synthetic.random_topology(n, seed=1)
+    lb, rb, rootb = synthetic.random_topology(n, seed=2)
+    engine.commit(t0, Topology(la, ra, roota))
+    engine.commit(t1, Topology(lb, rb, rootb))
+    ca, cb = nni_neighbourhood(la, ra, roota, n), nni_neighbourhood(lb, rb, rootb, n)
+    want_a = engine.score_batch([t0] * len(ca), ca)
+    want_b = engine.score_batch([t1] * 7, cb[:7])
+    ta = engine.score_batch_submit([t0] * len(ca), ca)
+    tb = engine.score_batch_submit([t1] * 7, cb[:7])
+    engine.commit(t1, cb[3], wait=False)  # enqueued behind both batches
+    tc = engine.score_batch_submit([t0] * 5, ca[:5])
+    assert np.array_equal(engine.batch_wait(tb), want_b)
+    assert np.array_equal(engine.batch_wait(ta), want_a)
+    assert np.array_equal(engine.batch_wait(tc), want_a[:5])
+    with pytest.raises(GpuError, match="names no submitted batch"):
+        engine.batch_wait(ta)
+    tickets = [engine.score_batch_submit([t0], ca[:1]) for _ in range(8)]
+    with pytest.raises(GpuError, match="waiting for lvb_gpu_batch_wait"):
+        engine.score_batch_submit([t0], ca[:1])
+    for tk in tickets:
+        assert engine.batch_wait(tk)[0] == want_a[0]
+    engine.tree_destroy(t0)
+    engine.tree_destroy(t1)
+
+
 def test_nni_neighbourhood_ambiguity_and_shapes(engine, golden_dir):
     """example alignment (padding: 984 sites) and caterpillar / balanced shapes with ambiguity codes"""
     g = np.load(os.path.join(golden_dir, "example.npz"))

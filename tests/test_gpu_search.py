@@ -76,7 +76,8 @@ def test_replicates_on_gpu():
         for k in ("final_length", "rearrangements", "topologies", "initial_length", "start_temperature"):
             assert multi["results"][r][k] == single["results"][0][k], (r, k)
         assert multi["outtrees"][r] == single["outtrees"][0]
-    assert multi["results"][0]["score_launches"] < multi["results"][0]["trees_scored"]
+    # proposals of several chains (and several proposals per chain) share a launch
+    assert multi["results"][0]["score_launches"] < sum(r["trees_scored"] for r in multi["results"])
 
 
 def test_compatible_getplen_on_gpu(golden_dir):

@@ -73,10 +73,11 @@ def test_replicates_are_independent_chains():
 
 
 def test_chain_groups_do_not_change_the_result():
-    """9 chains, 4 host threads -> 2 groups, each with its own device context and driver thread
-    (GetSolnBatched); chain r is still the single-chain run with seed s + r"""
+    """9 chains, 4 host threads, 2 groups, each with its own device context and driver thread and
+    each worked as two alternating halves (GetSolnBatched); chain r is still the single-chain run
+    with seed s + r"""
     p = subprocess.run([sys.executable, os.path.join(HERE, "run_host_search.py"), "--mock", "treelength.npz:tl5_thread_2_text",
-                        "7", "1", "0", "9", "0", "4"], capture_output=True, text=True, timeout=900)
+                        "7", "1", "0", "9", "0", "4", "2"], capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, p.stderr[-2000:]
     multi = json.loads(p.stdout.strip().splitlines()[-1])
     assert multi["results"][0]["groups"] == 2

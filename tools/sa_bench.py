@@ -71,6 +71,8 @@ def complete_search(name: str, raw: bytes, flags, nproc: int, with_ref: bool = T
     g = res["lvb_gpu"]
     if g.get("rc") == 0 and g.get("search_seconds"):
         res["gpu_trees_scored_per_s"] = g["trees_scored"] / g["search_seconds"]
+        # proposals of the reference's trajectory (what both programs have to get through), per second
+        res["gpu_rearrangements_per_s"] = g["rearrangements"] / g["search_seconds"]
     return res
 
 
@@ -85,6 +87,8 @@ def budget_search(name: str, n: int, m: int, p: float, chains: int, budget: int,
         if g.get("rc") == 0 and g.get("search_seconds"):
             # trees_scored is chain 0's count; every chain does the same number of evaluations +-
             res["gpu_trees_scored_per_s_all_chains"] = chains * g["trees_scored"] / g["search_seconds"]
+            # speculative proposals that were scored but not used are in trees_scored, not here
+            res["gpu_rearrangements_per_s_all_chains"] = chains * budget / g["search_seconds"]
     if oracles.have_ref():
         rows = synthetic.text_rows(st)
         L = oracles.ref()
