@@ -77,6 +77,18 @@ int lvb_gpu_matrix_upload_flat(lvb_gpu_ctx *ctx, int64_t n, int64_t nwords, cons
 int lvb_gpu_matrix_pack(lvb_gpu_ctx *ctx, int64_t n, int64_t m, const char *const *rows,
                         int64_t word_begin, int64_t word_count, int64_t max_trees);
 
+/* ---- column scans of the text alignment, before it is packed: constchar
+ * (DataOperations.c:272-307; matchange, :309-349, cuts the columns where keep[k] == 0) and
+ * MinimumTreeLength (:53-105, literal-character semantics: ambiguity letters count as states of
+ * their own, '-' '?' 'N' 'X' do not count, more than MAXSTATES = 5 states add 5, a column with
+ * no countable character adds -1).  rows = n pointers to m characters as read_file() left them.
+ * keep (m bytes, may be NULL) <- 1 where the column is NOT constant; *n_variable = their number;
+ * *min_len_all = MinimumTreeLength of the alignment as given, *min_len_variable = of the
+ * alignment after cutcols (what matchange stores in min_len_tree, :404).  Needs no uploaded
+ * matrix. ---- */
+int lvb_gpu_column_stats(lvb_gpu_ctx *ctx, int64_t n, int64_t m, const char *const *rows, unsigned char *keep,
+                         int64_t *n_variable, int64_t *min_len_all, int64_t *min_len_variable);
+
 /* ---- trees: device-resident state rows + cached per-node change counts of one
  * search chain's current tree (what treealloc gives Anneal, TreeOperations.c:914-955;
  * Solve.c:194-197).  A new tree has every internal node dirty. ---- */

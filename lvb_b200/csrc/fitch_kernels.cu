@@ -765,4 +765,76 @@ cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int
     return cudaGetLastError();
 }
 
+/* ---- column statistics of the text alignment --------------------------------------------
+ * constchar (src/DataOperations.c:272-307): a column is kept when some row differs from row 0
+ * in the literal character.  MinimumTreeLength / getstatev (:53-105): per column the number of
+ * distinct literal characters other than '-', '?', 'N', 'X', minus one — or MAXSTATES = 5 when
+ * more than five are met (the order of the rows does not matter: only the set of characters
+ * does), and -1 for a column with no countable character (strlen("") - 1, kept).
+ * One thread = one column; a warp reads 32 consecutive characters of each row. */
+__global__ void __launch_bounds__(256) column_stats_kernel(const unsigned char *text, int64_t n, int64_t m,
+                                                           unsigned char *keep, long long *sums)
+{
+    __shared__ long long s_sum[3];
+    if (threadIdx.x < 3)
+        s_sum[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    long long kept = 0, all = 0, of_kept = 0;
+    if (k < m)
+    {
+        unsigned mask[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}; /* one bit per byte value */
+        const unsigned char *p = text + k;
+        for (int64_t i = 0; i < n; i++, p += m)
+        {
+            const unsigned c = *p;
+#pragma unroll
+            for (int w = 0; w < 8; w++)
+                mask[w] |= (c >> 5) == (unsigned)w ? 1u << (c & 31u) : 0u;
+        }
+        int present = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++)
+            present += __popc(mask[w]);
+        mask['-' >> 5] &= ~(1u << ('-' & 31));
+        mask['?' >> 5] &= ~(1u << ('?' & 31));
+        mask['N' >> 5] &= ~(1u << ('N' & 31));
+        mask['X' >> 5] &= ~(1u << ('X' & 31));
+        int states = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++)
+            states += __popc(mask[w]);
+        const int contrib = states > 5 ? 5 : states - 1;
+        const int variable = present > 1 ? 1 : 0;
+        if (keep)
+            keep[k] = (unsigned char)variable;
+        kept = variable;
+        all = contrib;
+        of_kept = variable ? contrib : 0;
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        kept += __shfl_xor_sync(0xffffffffu, kept, o);
+        all += __shfl_xor_sync(0xffffffffu, all, o);
+        of_kept += __shfl_xor_sync(0xffffffffu, of_kept, o);
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicAdd((unsigned long long *)&s_sum[0], (unsigned long long)kept);
+        atomicAdd((unsigned long long *)&s_sum[1], (unsigned long long)all);
+        atomicAdd((unsigned long long *)&s_sum[2], (unsigned long long)of_kept);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 && s_sum[threadIdx.x])
+        atomicAdd((unsigned long long *)&sums[threadIdx.x], (unsigned long long)s_sum[threadIdx.x]);
+}
+
+cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *sums,
+                                cudaStream_t stream)
+{
+    const unsigned grid = (unsigned)((m + 255) / 256);
+    column_stats_kernel<<<grid, 256, 0, stream>>>(text, n, m, keep, sums);
+    return cudaGetLastError();
+}
+
 } // namespace lvbgpu

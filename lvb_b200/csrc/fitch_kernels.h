@@ -68,5 +68,11 @@ cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t
 cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int64_t word_begin, int64_t word_count,
                             uint4 *pool, int64_t stride_u4, int *bad, cudaStream_t stream);
 
+/* constchar + MinimumTreeLength on the device (src/DataOperations.c:272-307, 53-105).  text: n x m
+ * bytes row-major.  keep[k] (may be NULL) <- 1 where column k is not constant; sums[0] += kept
+ * columns, sums[1] += MinimumTreeLength over all columns, sums[2] += over the kept columns. */
+cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *sums,
+                                cudaStream_t stream);
+
 } // namespace lvbgpu
 #endif

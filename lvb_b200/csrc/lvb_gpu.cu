@@ -904,6 +904,64 @@ extern "C"
         return rc;
     }
 
+    int lvb_gpu_column_stats(lvb_gpu_ctx *c, int64_t n, int64_t m, const char *const *rows, unsigned char *keep,
+                             int64_t *n_variable, int64_t *min_len_all, int64_t *min_len_variable)
+    {
+        if (!c || !rows)
+            return fail("lvb_gpu_column_stats: null argument");
+        if (n < 1 || m < 1)
+            return fail("lvb_gpu_column_stats: empty alignment");
+        CU(cudaSetDevice(c->device));
+        unsigned char *d_text = nullptr, *h_text = nullptr, *d_keep = nullptr;
+        long long *d_sums = nullptr;
+        long long sums[3] = {0, 0, 0};
+        int rc = 0;
+        auto check = [&](cudaError_t e, const char *what) {
+            if (e != cudaSuccess && !rc)
+                rc = fail("%s: %s", what, cudaGetErrorString(e));
+            return e == cudaSuccess;
+        };
+        const size_t chunk_rows = std::max<size_t>(1, std::min<size_t>((size_t)n, (64u << 20) / (size_t)m));
+        if (check(cudaMalloc(&d_text, (size_t)n * m), "text allocation") &&
+            check(cudaMalloc(&d_keep, (size_t)m), "keep allocation") &&
+            check(cudaMalloc(&d_sums, sizeof sums), "sums allocation") &&
+            check(cudaMallocHost(&h_text, chunk_rows * (size_t)m), "staging allocation") &&
+            check(cudaMemsetAsync(d_sums, 0, sizeof sums, c->stream), "memset"))
+        {
+            for (int64_t r0 = 0; r0 < n && !rc; r0 += (int64_t)chunk_rows)
+            {
+                const int64_t nr = std::min<int64_t>((int64_t)chunk_rows, n - r0);
+                for (int64_t r = 0; r < nr; r++)
+                    memcpy(h_text + r * m, rows[r0 + r], (size_t)m);
+                if (check(cudaMemcpyAsync(d_text + r0 * m, h_text, (size_t)nr * m, cudaMemcpyHostToDevice, c->stream),
+                          "text upload"))
+                    check(cudaStreamSynchronize(c->stream), "text upload");
+            }
+            if (!rc && check(launch_column_stats(d_text, n, m, d_keep, d_sums, c->stream), "column_stats kernel"))
+            {
+                c->launches++;
+                if (keep)
+                    check(cudaMemcpyAsync(keep, d_keep, (size_t)m, cudaMemcpyDeviceToHost, c->stream), "keep download");
+                check(cudaMemcpyAsync(sums, d_sums, sizeof sums, cudaMemcpyDeviceToHost, c->stream), "sums download");
+                check(cudaStreamSynchronize(c->stream), "column_stats kernel");
+            }
+        }
+        cudaFree(d_text);
+        cudaFree(d_keep);
+        cudaFree(d_sums);
+        if (h_text)
+            cudaFreeHost(h_text);
+        if (rc)
+            return rc;
+        if (n_variable)
+            *n_variable = (int64_t)sums[0];
+        if (min_len_all)
+            *min_len_all = (int64_t)sums[1];
+        if (min_len_variable)
+            *min_len_variable = (int64_t)sums[2];
+        return 0;
+    }
+
     int lvb_gpu_tree_create(lvb_gpu_ctx *c, int *tree)
     {
         if (!c || !tree)

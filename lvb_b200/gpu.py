@@ -58,6 +58,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_matrix_upload.argtypes = [vp, i64, i64, C.POINTER(vp), i64, i64, i64]
     lib.lvb_gpu_matrix_upload_flat.argtypes = [vp, i64, i64, vp, i64, i64, i64]
     lib.lvb_gpu_matrix_pack.argtypes = [vp, i64, i64, C.POINTER(C.c_char_p), i64, i64, i64]
+    lib.lvb_gpu_column_stats.argtypes = [vp, i64, i64, C.POINTER(C.c_char_p), vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
     lib.lvb_gpu_tree_create.argtypes = [vp, i32p]
     lib.lvb_gpu_tree_destroy.argtypes = [vp, C.c_int]
     lib.lvb_gpu_tree_copy.argtypes = [vp, C.c_int, C.c_int]
@@ -210,6 +211,15 @@ class Engine:
         wc = nwords - word_begin if word_count is None else word_count
         _check(self.lib.lvb_gpu_matrix_pack(self.ctx, n, m, arr, word_begin, wc, max_trees))
         self.n, self.nwords, self.word_count = n, nwords, wc
+
+    def column_stats(self, rows: Sequence[bytes]):
+        """(keep[m] uint8, variable columns, MinimumTreeLength of all columns, of the variable columns)"""
+        n, m = len(rows), len(rows[0])
+        arr = (C.c_char_p * n)(*rows)
+        keep = np.zeros(m, dtype=np.uint8)
+        a, b, c_ = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+        _check(self.lib.lvb_gpu_column_stats(self.ctx, n, m, arr, keep.ctypes.data, C.byref(a), C.byref(b), C.byref(c_)))
+        return keep, int(a.value), int(b.value), int(c_.value)
 
     # ---- trees ----
     def tree_create(self) -> int:

@@ -260,6 +260,51 @@ def test_nni_neighbourhood_call(engine, n, m, seed):
     engine.tree_destroy(s)
 
 
+def _oracle_column_stats(rows):
+    import ctypes as C
+
+    L = oracles.oracle()
+    n, m = len(rows), len(rows[0])
+    arr = (C.c_char_p * n)(*rows)
+    keep = np.zeros(m, dtype=np.uint8)
+    kept = L.oracle_variable_columns(n, m, arr, keep.ctypes.data)
+    cut = [bytes(np.frombuffer(r, dtype=np.uint8)[keep.astype(bool)]) for r in rows]
+    arr2 = (C.c_char_p * n)(*cut)
+    return keep, int(kept), int(L.oracle_min_tree_length(n, m, arr)), (int(L.oracle_min_tree_length(n, kept, arr2)) if kept else 0)
+
+
+def test_column_stats_constchar_and_min_tree_length(engine, golden_dir):
+    """lvb_gpu_column_stats == constchar + MinimumTreeLength (DataOperations.c:272-307, 53-105):
+    the reference's test inputs (golden min_len values from the reference itself), every accepted
+    symbol incl. ambiguity letters, > 5 states in a column, columns of only '-' (the -1 quirk)"""
+    g = load(golden_dir, "treelength.npz")
+    for key in [k[:-5] for k in g.files if k.endswith("_text")]:
+        rows = [bytes(r) for r in g[key + "_text"]]
+        keep, kept, all_len, kept_len = engine.column_stats(rows)
+        okeep, okept, oall, okept_len = _oracle_column_stats(rows)
+        assert np.array_equal(keep, okeep) and (kept, all_len, kept_len) == (okept, oall, okept_len), key
+        if f"{key}_min_len" in g.files:
+            # the reference's own MinimumTreeLength, taken after or before matchange depending on the fixture
+            assert int(g[f"{key}_min_len"]) in (all_len, kept_len), key
+    ex = load(golden_dir, "example.npz")
+    rows = [bytes(r) for r in ex["text"]]  # already cut to 984 columns by the reference's matchange
+    keep, kept, all_len, kept_len = engine.column_stats(rows)
+    assert kept == 984 and keep.all() and all_len == kept_len == 1816  # SURVEY.md 8(c): min_len=1816
+    rng = np.random.default_rng(3)
+    sym = np.frombuffer(b"ACGTUYRWSKMBDHVNX?O-", dtype=np.uint8)
+    n, m = 37, 1003
+    t = sym[rng.integers(0, len(sym), size=(n, m))].copy()
+    t[:, 5] = ord("-")           # no countable character: adds -1
+    t[:, 6] = ord("A")           # constant
+    t[:, 7] = ord("N"); t[3, 7] = ord("X")   # variable, but nothing countable
+    t[:, 8] = sym[:1]; t[:6, 8] = sym[:6]    # exactly 6 distinct countable -> 5
+    rows = [bytes(r) for r in t]
+    got = engine.column_stats(rows)
+    want = _oracle_column_stats(rows)
+    assert np.array_equal(got[0], want[0]) and got[1:] == want[1:]
+    assert got[0][5] == 0 and got[0][6] == 0 and got[0][7] == 1
+
+
 def test_submit_and_wait_halves(engine):
     """lvb_gpu_score_batch_submit / lvb_gpu_batch_wait: several batches in flight, a commit of
     another tree in between, lengths identical to the synchronous call; misuse is loud"""
