@@ -44,18 +44,18 @@ long MinimumTreeLength(const Dataptr MSA)
     return minlen;
 }
 
-static void set_shape(Dataptr MSA)
+static void set_shape(Dataptr MSA, long min_len_known)
 {
     MSA->bytes = bytes_per_row(MSA->m);
     MSA->nwords = words_per_row(MSA->m);
-    MSA->min_len_tree = MinimumTreeLength(MSA);
+    MSA->min_len_tree = min_len_known != UNSET ? min_len_known : MinimumTreeLength(MSA);
 }
 
 /* src/DataOperations.c:272-405: drop every column in which all rows hold the same character
  * (literal comparison with row 0), then set m, bytes, nwords and min_len_tree */
 void matchange(Dataptr MSA, const Parameters &rc)
 {
-    std::vector<char> keep((size_t)MSA->m, 0);
+    std::vector<unsigned char> keep((size_t)MSA->m, 0);
     long kept = 0;
     for (long k = 0; k < MSA->m; ++k)
         for (long i = 1; i < MSA->n; ++i)
@@ -65,6 +65,14 @@ void matchange(Dataptr MSA, const Parameters &rc)
                 ++kept;
                 break;
             }
+    matchange_apply(MSA, rc, keep.data(), kept, UNSET);
+}
+
+/* the rest of matchange once the column scan is known (from the loop above or from
+ * lvb_gpu_column_stats): logcut, cutcols, shape.  min_len_after: MinimumTreeLength of the
+ * alignment after the cut if already known, else UNSET */
+void matchange_apply(Dataptr MSA, const Parameters &rc, const unsigned char *keep, long kept, long min_len_after)
+{
     if (rc.verbose)
     {
         printf("Constant columns excluded from analysis: ");
@@ -110,7 +118,7 @@ void matchange(Dataptr MSA, const Parameters &rc)
         MSA->m = kept;
     }
     if (MSA->m >= MIN_M)
-        set_shape(MSA);
+        set_shape(MSA, min_len_after);
     if (MSA->m < MIN_M)
         crash("after constant columns are ignored, data MSA has\n"
               "%ld columns, which is less than LVB's lower limit of\n"

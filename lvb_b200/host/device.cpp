@@ -42,6 +42,29 @@ void device_open_encoded(Device &dev, int device_index, Dataptr MSA, Lvb_bit_len
                                     word_count, max_trees));
 }
 
+/* matchange (src/DataOperations.c:309-349) with the two O(n*m) text scans — constchar (:272-307)
+ * and the MinimumTreeLength of the cut alignment (:53-105, :404) — done by the device in one pass
+ * over the characters (lvb_gpu_column_stats); cutting the columns stays on the host. */
+void matchange_device(Dataptr MSA, const Parameters &rc, int device_index)
+{
+    lvb_gpu_ctx *ctx = nullptr;
+    gpu_check(lvb_gpu_init(device_index, &ctx));
+    std::vector<const char *> rows((size_t)MSA->n);
+    for (long i = 0; i < MSA->n; i++)
+        rows[(size_t)i] = MSA->row[(size_t)i].data();
+    std::vector<unsigned char> keep((size_t)MSA->m, 0);
+    int64_t kept = 0, min_all = 0, min_kept = 0;
+    const int rc_ = lvb_gpu_column_stats(ctx, MSA->n, MSA->m, rows.data(), keep.data(), &kept, &min_all, &min_kept);
+    if (rc_ != 0)
+    {
+        const std::string msg = lvb_gpu_last_error();
+        lvb_gpu_shutdown(ctx);
+        crash("GPU error: %s", msg.c_str());
+    }
+    gpu_check(lvb_gpu_shutdown(ctx));
+    matchange_apply(MSA, rc, keep.data(), (long)kept, (long)min_kept);
+}
+
 void device_close(Device &dev)
 {
     if (dev.ctx)

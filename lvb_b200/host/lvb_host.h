@@ -133,6 +133,11 @@ long bytes_per_row(long m);                                     /* :460-467 */
 long MinimumTreeLength(const Dataptr MSA);                      /* :53-105 */
 void matchange(Dataptr MSA, const Parameters &rc);              /* :309-349 (+ constchar, cutcols) */
 void DNAToBinary(const Dataptr MSA, Lvb_bit_length **enc_mat);  /* :164-249 */
+/* matchange after the column scan: keep[k] != 0 where column k stays, kept = their number,
+ * min_len_after = MinimumTreeLength of the cut alignment if known, else UNSET */
+void matchange_apply(Dataptr MSA, const Parameters &rc, const unsigned char *keep, long kept, long min_len_after);
+/* matchange with both text scans on the device (lvb_gpu_column_stats); same result */
+void matchange_device(Dataptr MSA, const Parameters &rc, int device_index);
 /* src/Wrapper.c:49-68 + src/CommandLineParser.cpp:49-105 (PHYLIP and FASTA only) */
 void phylip_dna_matrin(const char *file_name, int n_file_format, Dataptr MSA);
 /* build the DataStructure from rows already in memory (what read_file() fills) */

@@ -161,7 +161,16 @@ int main(int argc, char **argv)
     }
     DataStructure MSA;
     phylip_dna_matrin(rc.file_name_in.c_str(), rc.n_file_format, &MSA);
-    matchange(&MSA, rc);
+    {
+        /* the two text scans of matchange are O(n*m): on the device once the alignment is large
+         * (LVB_GPU_MATCHANGE=1 / 0 forces the choice) */
+        const char *mc = getenv("LVB_GPU_MATCHANGE");
+        const bool on_device = mc ? atoi(mc) != 0 : (double)MSA.n * (double)MSA.m >= 64.0 * 1024 * 1024;
+        if (on_device)
+            matchange_device(&MSA, rc, rc.device);
+        else
+            matchange(&MSA, rc);
+    }
     writeinf(rc, &MSA, argc, argv);
     if (rc.verbose)
         printf("MinimumTreeLength: %ld\n\n", MinimumTreeLength(&MSA));

@@ -216,6 +216,35 @@ int lvb_gpu_score_batch(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const 
     return 0;
 }
 
+int lvb_gpu_column_stats(lvb_gpu_ctx *c, int64_t n, int64_t m, const char *const *rows, unsigned char *keep,
+                         int64_t *n_variable, int64_t *min_len_all, int64_t *min_len_variable)
+{
+    (void)c;
+    unsigned char *k = keep ? keep : (unsigned char *)malloc((size_t)m);
+    const long kept = oracle_variable_columns((long)n, (long)m, rows, k);
+    char **cut = (char **)malloc((size_t)n * sizeof(char *));
+    for (long i = 0; i < n; i++)
+    {
+        cut[i] = (char *)malloc((size_t)kept + 1);
+        long w = 0;
+        for (long col = 0; col < m; col++)
+            if (k[col])
+                cut[i][w++] = rows[i][col];
+    }
+    if (n_variable)
+        *n_variable = kept;
+    if (min_len_all)
+        *min_len_all = oracle_min_tree_length((long)n, (long)m, rows);
+    if (min_len_variable)
+        *min_len_variable = kept ? oracle_min_tree_length((long)n, kept, (const char *const *)cut) : 0;
+    for (long i = 0; i < n; i++)
+        free(cut[i]);
+    free(cut);
+    if (!keep)
+        free(k);
+    return 0;
+}
+
 /* asynchronous halves: the mock computes at submit time and hands the lengths over at wait time */
 int lvb_gpu_score_batch_submit(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos, int *ticket)
 {

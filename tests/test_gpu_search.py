@@ -113,3 +113,14 @@ def test_compatible_getplen_on_gpu(golden_dir):
                 cur, prop = prop, cur
     finally:
         L.lvbh_device_close()
+
+
+def test_matchange_on_the_device(monkeypatch):
+    """the example alignment loses 16 constant columns (1000 -> 984): with
+    LVB_GPU_MATCHANGE=1 the scan and MinimumTreeLength come from lvb_gpu_column_stats and the
+    whole run (starting temperature uses min_len_tree) is unchanged"""
+    monkeypatch.setenv("LVB_GPU_MATCHANGE", "1")
+    want = SA_RUNS["a1"]
+    got = H.run_cli(H.example_input(), ["-s", "12345", "-a", "1"], mock=False)
+    H.check_against(got, want, "example a=1, matchange on the device")
+    assert "In total, 16 columns are excluded" in got["stdout"]

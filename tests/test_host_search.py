@@ -90,3 +90,13 @@ def test_chain_groups_do_not_change_the_result():
         for k in ("final_length", "rearrangements", "topologies", "initial_length", "start_temperature"):
             assert a[k] == b[k], (r, k)
         assert multi["outtrees"][r] == single["outtrees"][0]
+
+
+def test_matchange_on_the_device_route(monkeypatch):
+    """LVB_GPU_MATCHANGE=1: constchar + MinimumTreeLength come from lvb_gpu_column_stats
+    (matchange_device); same run as with the host scans"""
+    monkeypatch.setenv("LVB_GPU_MATCHANGE", "1")
+    for case in ("test_treelength_5_thread_2", "test_treelength_4@2"):
+        want = CLI_RUNS[case]
+        got = H.run_cli(H.cli_input(case.split("@")[0]), want["flags"], mock=True)
+        H.check_against(got, want, case)
