@@ -120,8 +120,56 @@ __device__ __forceinline__ unsigned fitch_step(const uint4 &x, const uint4 &y, u
     return s0 + 2u * s1 + 4u * s2 + 8u * s3;
 }
 
+/* store mode, after the counts of a program are complete: one CTA folds them into chg / sum_chg
+ * and publishes the length (its own launch, or the last column block of a single-level batch) */
+__device__ __forceinline__ void fitch_commit_finalize_body(const FitchInstr *instr, const FitchProgram *progs,
+                                                           int32_t *cnts, int32_t *chg, long long *sum_chg, int n,
+                                                           int n_internal, long long *lengths, int pi)
+{
+    __shared__ long long s_delta, s_root;
+    const FitchProgram prog = progs[pi];
+    int32_t *tchg = chg + (int64_t)prog.tree * n_internal;
+    if (threadIdx.x == 0)
+    {
+        s_delta = 0;
+        s_root = 0;
+    }
+    __syncthreads();
+    long long delta = 0, rootc = 0;
+    for (int i = threadIdx.x; i < prog.n_instr; i += blockDim.x)
+    {
+        const int node = instr[prog.instr_begin + i].node;
+        const int c = __ldcg(&cnts[prog.instr_begin + i]);
+        cnts[prog.instr_begin + i] = 0; /* ready for the next store batch */
+        if (node >= 0)
+        {
+            delta += (long long)c - tchg[node - n];
+            tchg[node - n] = c;
+        }
+        else
+            rootc += c; /* root step: never cached (TreeEvaluation.c:238-264) */
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        delta += __shfl_xor_sync(0xffffffffu, delta, o);
+        rootc += __shfl_xor_sync(0xffffffffu, rootc, o);
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicAdd((unsigned long long *)&s_delta, (unsigned long long)delta);
+        atomicAdd((unsigned long long *)&s_root, (unsigned long long)rootc);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        const long long s = sum_chg[prog.tree] + s_delta;
+        sum_chg[prog.tree] = s;
+        lengths[pi] = s + s_root;
+    }
+}
+
 template <bool PER_NODE>
-__global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
+__device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const FitchProgram *progs, const FitchInstr *instrs)
 {
     extern __shared__ uint4 smem_u4[];
     uint4 *s_instr = smem_u4;                                          /* LVB_CHUNK + 2 decoded instructions */
@@ -155,7 +203,7 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
     const bool piece_major = PER_NODE && p.dep;
     const int prog_id = piece_major ? vb / p.n_colblocks : vb % p.n_prog;
     const int cb = piece_major ? vb % p.n_colblocks : vb / p.n_prog;
-    const FitchProgram prog = p.prog[prog_id];
+    const FitchProgram prog = progs[prog_id];
     if (PER_NODE && p.dep && prog.n_wait > 0)
     {
         if (tid == 0)
@@ -174,7 +222,7 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
     const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal; /* internal node v lives in row v + tree_off */
     /* rows the operands are read from: the program's own tree unless it names another one */
     const unsigned src_off = prog.src_tree1 > 0 ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
-    const FitchInstr *gi = p.instr + prog.instr_begin;
+    const FitchInstr *gi = instrs + prog.instr_begin;
     /* threads past the end of the row (last column block only) redo the last column; their
      * counts are masked and their stores suppressed */
     const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
@@ -299,6 +347,26 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
                 atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
             }
         }
+        if (p.fused_finalize)
+        { /* single-level batch (program == candidate): the column block that finishes last folds the
+           * counts and publishes the length — no second launch on the latency path of a round */
+            __shared__ unsigned s_last;
+            __syncthreads(); /* this CTA's count atomics are issued */
+            if (tid == 0)
+            {
+                __threadfence();
+                const unsigned last = atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u ? 1u : 0u;
+                if (last)
+                    p.done[prog_id] = 0u;
+                s_last = last;
+            }
+            __syncthreads();
+            if (s_last)
+            {
+                __threadfence();
+                fitch_commit_finalize_body(instrs, progs, p.cnts, p.chg_rw, p.sum_chg_rw, p.n, p.n_internal, p.out, prog_id);
+            }
+        }
         return;
     }
     /* per-program length: block reduce, one 64-bit atomic per CTA */
@@ -327,6 +395,12 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
         if (tid == 0)
             s_total += (unsigned long long)p.sum_chg[prog.tree];
     }
+    if (p.n_colblocks == 1)
+    { /* one CTA holds the whole program (narrow alignments): nothing to combine across blocks */
+        if (tid == 0)
+            p.out[prog_id] = (long long)s_total;
+        return;
+    }
     if (tid == 0)
     {
         /* the column block that finishes last publishes the length and leaves totals/done zero
@@ -341,6 +415,33 @@ __global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
             p.done[prog_id] = 0u;
         }
     }
+}
+
+/* Programs and instructions either in device memory (staged by the host with one copy per
+ * batch) or, for the small batches of a single SA chain, INSIDE the kernel parameters: the
+ * launch carries them, no host-to-device copy sits on the latency path of a round. */
+template <int NP, int NI>
+struct InlineBatch
+{
+    FitchProgram prog[NP]; /* pieces / programs of the launch */
+    FitchProgram cand[NP]; /* one record per candidate (finalize) */
+    FitchInstr instr[NI];
+};
+#define LVB_INL_SMALL_P 4
+#define LVB_INL_SMALL_I 112
+#define LVB_INL_LARGE_P 16
+#define LVB_INL_LARGE_I 480
+
+template <bool PER_NODE>
+__global__ void __launch_bounds__(256, 6) fitch_exec_kernel(const ExecParams p)
+{
+    fitch_exec_body<PER_NODE>(p, p.prog, p.instr);
+}
+template <bool PER_NODE, int NP, int NI>
+__global__ void __launch_bounds__(256, 6)
+    fitch_exec_kernel_inl(const __grid_constant__ ExecParams p, const __grid_constant__ InlineBatch<NP, NI> b)
+{
+    fitch_exec_body<PER_NODE>(p, b.prog, b.instr);
 }
 
 /* ---- score mode, deep pipeline -------------------------------------------------------------
@@ -370,7 +471,7 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-__global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
+__device__ __forceinline__ void fitch_score_body(const ExecParams &p, const FitchProgram *progs, const FitchInstr *instrs)
 {
     extern __shared__ uint4 smem_u4[];
     uint4 *s_instr = smem_u4; /* LVB_CHUNK + 2 * LVB_RING decoded instructions */
@@ -384,11 +485,11 @@ __global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
      * rows shared between candidates of one tree are served from L2 */
     const int prog_id = blockIdx.x % p.n_prog;
     const int cb = blockIdx.x / p.n_prog;
-    const FitchProgram prog = p.prog[prog_id];
+    const FitchProgram prog = progs[prog_id];
     const int col = cb * nthr + tid;
     const unsigned amask = col < p.ncols ? ~0u : 0u;
     const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
-    const FitchInstr *gi = p.instr + prog.instr_begin;
+    const FitchInstr *gi = instrs + prog.instr_begin;
     const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
     const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
     const unsigned slot_bytes = (unsigned)nthr * 16u;
@@ -509,6 +610,12 @@ __global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
         if (tid == 0)
             s_total += (unsigned long long)p.sum_chg[prog.tree];
     }
+    if (p.n_colblocks == 1)
+    { /* one CTA holds the whole program (narrow alignments): nothing to combine across blocks */
+        if (tid == 0)
+            p.out[prog_id] = (long long)s_total;
+        return;
+    }
     if (tid == 0)
     {
         /* the column block that finishes last publishes the length and leaves totals/done zero
@@ -523,6 +630,17 @@ __global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
             p.done[prog_id] = 0u;
         }
     }
+}
+
+__global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
+{
+    fitch_score_body(p, p.prog, p.instr);
+}
+template <int NP, int NI>
+__global__ void __launch_bounds__(256)
+    fitch_score_kernel_inl(const __grid_constant__ ExecParams p, const __grid_constant__ InlineBatch<NP, NI> b)
+{
+    fitch_score_body(p, b.prog, b.instr);
 }
 
 static size_t exec_smem_bytes(bool per_node, int n_slots, int block)
@@ -564,52 +682,82 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
     return cudaGetLastError();
 }
 
-/* one CTA per program of a store-mode batch */
 __global__ void __launch_bounds__(1024) fitch_commit_finalize_kernel(const FitchInstr *instr, const FitchProgram *progs,
                                                                     int32_t *cnts, int32_t *chg,
                                                                     long long *sum_chg, int n, int n_internal,
                                                                     long long *lengths)
 {
-    __shared__ long long s_delta, s_root;
-    const FitchProgram prog = progs[blockIdx.x];
-    int32_t *tchg = chg + (int64_t)prog.tree * n_internal;
-    if (threadIdx.x == 0)
+    fitch_commit_finalize_body(instr, progs, cnts, chg, sum_chg, n, n_internal, lengths, blockIdx.x);
+}
+template <int NP, int NI>
+__global__ void __launch_bounds__(1024)
+    fitch_commit_finalize_kernel_inl(const __grid_constant__ InlineBatch<NP, NI> b, int32_t *cnts, int32_t *chg,
+                                     long long *sum_chg, int n, int n_internal, long long *lengths)
+{
+    fitch_commit_finalize_body(b.instr, b.cand, cnts, chg, sum_chg, n, n_internal, lengths, blockIdx.x);
+}
+
+/* ---- launches with the batch inside the kernel parameters ---- */
+bool inline_batch_fits(int n_prog, int n_cand, size_t n_instr)
+{
+    return n_prog <= LVB_INL_LARGE_P && n_cand <= LVB_INL_LARGE_P && n_instr <= (size_t)LVB_INL_LARGE_I;
+}
+
+template <int NP, int NI>
+static cudaError_t launch_inline_t(const ExecParams &p, bool per_node, int block, cudaStream_t stream,
+                                   const FitchProgram *prog, int n_prog, const FitchProgram *cand, int n_cand,
+                                   const FitchInstr *instr, size_t n_instr, bool finalize, int32_t *chg,
+                                   long long *sum_chg, long long *lengths, int max_instr)
+{
+    static thread_local InlineBatch<NP, NI> tb; /* host copy; the launch copies it into the command stream */
+    memcpy(tb.prog, prog, (size_t)n_prog * sizeof(FitchProgram));
+    memcpy(tb.cand, cand, (size_t)n_cand * sizeof(FitchProgram));
+    memcpy(tb.instr, instr, n_instr * sizeof(FitchInstr));
+    const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
+    cudaError_t e;
+    if (per_node)
     {
-        s_delta = 0;
-        s_root = 0;
-    }
-    __syncthreads();
-    long long delta = 0, rootc = 0;
-    for (int i = threadIdx.x; i < prog.n_instr; i += blockDim.x)
-    {
-        const int node = instr[prog.instr_begin + i].node;
-        const int c = cnts[prog.instr_begin + i];
-        cnts[prog.instr_begin + i] = 0; /* ready for the next store batch */
-        if (node >= 0)
+        const size_t smem = exec_smem_bytes(true, p.n_slots, block);
+        if (smem > 48 * 1024 &&
+            (e = cudaFuncSetAttribute(fitch_exec_kernel_inl<true, NP, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem)) != cudaSuccess)
+            return e;
+        fitch_exec_kernel_inl<true, NP, NI><<<grid, block, smem, stream>>>(p, tb);
+        if ((e = cudaGetLastError()) != cudaSuccess)
+            return e;
+        if (finalize && !p.fused_finalize)
         {
-            delta += (long long)c - tchg[node - n];
-            tchg[node - n] = c;
+            int threads = 32;
+            while (threads < max_instr && threads < 1024)
+                threads *= 2;
+            fitch_commit_finalize_kernel_inl<NP, NI><<<n_cand, threads, 0, stream>>>(tb, p.cnts, chg, sum_chg, p.n,
+                                                                                    p.n_internal, lengths);
         }
-        else
-            rootc += c; /* root step: never cached (TreeEvaluation.c:238-264) */
     }
-    for (int o = 16; o > 0; o >>= 1)
+    else
     {
-        delta += __shfl_xor_sync(0xffffffffu, delta, o);
-        rootc += __shfl_xor_sync(0xffffffffu, rootc, o);
+        const size_t smem2 =
+            (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(2 * LVB_RING + p.n_slots) * block) * sizeof(uint4);
+        if (smem2 > 48 * 1024 &&
+            (e = cudaFuncSetAttribute(fitch_score_kernel_inl<NP, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem2)) != cudaSuccess)
+            return e;
+        fitch_score_kernel_inl<NP, NI><<<grid, block, smem2, stream>>>(p, tb);
     }
-    if ((threadIdx.x & 31) == 0)
-    {
-        atomicAdd((unsigned long long *)&s_delta, (unsigned long long)delta);
-        atomicAdd((unsigned long long *)&s_root, (unsigned long long)rootc);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0)
-    {
-        const long long s = sum_chg[prog.tree] + s_delta;
-        sum_chg[prog.tree] = s;
-        lengths[blockIdx.x] = s + s_root;
-    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fitch_inline(const ExecParams &p, bool per_node, int block, cudaStream_t stream,
+                                const FitchProgram *prog, int n_prog, const FitchProgram *cand, int n_cand,
+                                const FitchInstr *instr, size_t n_instr, int32_t *chg, long long *sum_chg,
+                                long long *lengths, int max_instr)
+{
+    if (n_prog <= LVB_INL_SMALL_P && n_cand <= LVB_INL_SMALL_P && n_instr <= (size_t)LVB_INL_SMALL_I)
+        return launch_inline_t<LVB_INL_SMALL_P, LVB_INL_SMALL_I>(p, per_node, block, stream, prog, n_prog, cand, n_cand,
+                                                                 instr, n_instr, per_node, chg, sum_chg, lengths,
+                                                                 max_instr);
+    return launch_inline_t<LVB_INL_LARGE_P, LVB_INL_LARGE_I>(p, per_node, block, stream, prog, n_prog, cand, n_cand, instr,
+                                                             n_instr, per_node, chg, sum_chg, lengths, max_instr);
 }
 
 cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,

@@ -32,6 +32,10 @@ struct ExecParams
     unsigned *ticket;            /* store mode, dependent pieces: CTA start-order counter (left zero by the kernel) */
     unsigned *dep;               /* store mode: [n_prog][n_colblocks] finished child pieces per column block
                                   * (left zero by the kernel); NULL: pieces of the launch are independent */
+    int32_t fused_finalize;      /* store mode, single-level batch: the last column block of a program runs the
+                                  * finalize step (chg_rw / sum_chg_rw / out) instead of a second launch */
+    int32_t *chg_rw;             /* = chg, writable (fused finalize) */
+    long long *sum_chg_rw;       /* = sum_chg, writable */
     const int32_t *chg;          /* [trees][I] cached per-node change counts */
     const long long *sum_chg;    /* [trees] sum of chg over internal nodes */
 };
@@ -39,6 +43,17 @@ struct ExecParams
 /* block: threads per CTA (multiple of 32).  per_node: store-mode batch (per-instruction
  * counts are produced, base length is not added). */
 cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cudaStream_t stream);
+
+/* The same launch(es) with the batch INSIDE the kernel parameters (no staged copy on the device):
+ * for the small batches of a single SA chain, where a host-to-device copy per call is a large
+ * part of a round.  prog/cand/instr are HOST pointers.  per_node: store batch, followed by the
+ * finalize launch (lengths as for launch_commit_finalize); else score batch.
+ * inline_batch_fits tells whether a batch is small enough. */
+bool inline_batch_fits(int n_prog, int n_cand, size_t n_instr);
+cudaError_t launch_fitch_inline(const ExecParams &p, bool per_node, int block, cudaStream_t stream,
+                                const FitchProgram *prog, int n_prog, const FitchProgram *cand, int n_cand,
+                                const FitchInstr *instr, size_t n_instr, int32_t *chg, long long *sum_chg,
+                                long long *lengths, int max_instr);
 
 /* After a store-mode batch: chg[tree][node] <- new count, sum_chg[tree] += delta,
  * lengths[p] <- sum_chg[tree] + root step counts.  Trees of the batch must be distinct. */

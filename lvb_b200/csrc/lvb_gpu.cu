@@ -22,6 +22,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <climits>
 #include <cstring>
 #include <ctime>
 #include <string>
@@ -151,6 +152,9 @@ struct lvb_gpu_ctx
     size_t cap_nni = 0;
     int compile_par_min = 8;  /* host compile: batches of >= min candidates are spread over
                                                         * OpenMP threads, >= grain candidates each */
+    bool inline_ok = true;   /* small batches travel inside the kernel parameters (LVB_GPU_INLINE=0: always staged) */
+    bool last_inline = false;
+    bool fuse_ok = true;     /* single-level store batches finalize inside the Fitch kernel (LVB_GPU_FUSE=0: own launch) */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
     bool last_dep = false;
@@ -336,6 +340,11 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     p.dep = c->last_dep ? c->d_dep : nullptr;
     p.chg = c->chg;
     p.sum_chg = c->sum_chg;
+    p.chg_rw = c->chg;
+    p.sum_chg_rw = c->sum_chg;
+    /* a store batch without pieces: program == candidate, the kernel finalizes by itself */
+    const bool fused = store && !c->last_dep && c->levels.size() == 1 && c->last_n_prog == (size_t)K && c->fuse_ok;
+    p.fused_finalize = fused ? 1 : 0;
 
     const double ts0 = c->profile ? wall_now() : 0;
     int slot = -1;
@@ -349,9 +358,23 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
         c->ring_instr[slot] = (int64_t)c->last_n_instr;
         CU(cudaEventRecord(c->ring0[slot], c->stream));
     }
+    if (c->last_inline)
+    {
+        const FitchProgram *h_prog = reinterpret_cast<const FitchProgram *>(st.h);
+        const FitchProgram *h_cand = h_prog + c->last_n_prog;
+        const FitchInstr *h_instr = reinterpret_cast<const FitchInstr *>(h_cand + K);
+        p.prog = nullptr;
+        p.instr = nullptr;
+        p.n_prog = (int32_t)c->last_n_prog;
+        CU(launch_fitch_inline(p, store, block, c->stream, h_prog, (int)c->last_n_prog, h_cand, (int)K, h_instr,
+                               c->last_n_instr, c->chg, c->sum_chg, out, c->last_max_instr));
+        c->launches += store && !fused ? 2 : 1;
+    }
     /* one launch per dependency level: pieces of a level only read rows stored by earlier levels */
     for (const auto &lv : c->levels)
     {
+        if (c->last_inline)
+            break;
         p.prog = d_prog + lv.first;
         p.n_prog = lv.second;
         if ((int64_t)p.n_prog * p.n_colblocks > (int64_t)INT32_MAX)
@@ -366,7 +389,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
         c->ev1 = c->ring1[slot];
         c->timed = true;
     }
-    if (store)
+    if (store && !c->last_inline && !fused)
     {
         CU(launch_commit_finalize(d_instr, d_cand, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I, out,
                                   c->last_max_instr, c->stream));
@@ -605,7 +628,11 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     else
         c->levels.push_back({0, (int32_t)c->prog.size()});
     memcpy(h_prog, c->prog.data(), c->prog.size() * sizeof(FitchProgram));
-    CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
+    /* small single-level batches (one SA chain's proposals, an accepted move) ride in the kernel
+     * parameters; everything else is staged on the device with one copy */
+    c->last_inline = c->inline_ok && !multilevel && c->levels.size() == 1 && inline_batch_fits((int)n_prog, (int)K, n_instr);
+    if (!c->last_inline)
+        CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
     if (store)
         for (int64_t k = 0; k < K; k++)
             c->tree_ready[trees[k]] = 1;
@@ -764,6 +791,10 @@ extern "C"
         const char *cp = getenv("LVB_GPU_COMPILE_PAR");
         if (cp && atoi(cp) > 0)
             c->compile_par_min = atoi(cp);
+        const char *il = getenv("LVB_GPU_INLINE");
+        c->inline_ok = !(il && atoi(il) == 0);
+        const char *fz = getenv("LVB_GPU_FUSE");
+        c->fuse_ok = !(fz && atoi(fz) == 0);
         const char *v1 = getenv("LVB_GPU_SCORE_V1");
         c->score_v1 = v1 && atoi(v1) != 0;
         const char *pf = getenv("LVB_GPU_PROFILE");
@@ -1157,6 +1188,9 @@ extern "C"
             p.dep = nullptr;
             p.chg = c->chg;
             p.sum_chg = c->sum_chg;
+            p.chg_rw = c->chg;
+            p.sum_chg_rw = c->sum_chg;
+            p.fused_finalize = 0;
             CU(launch_fitch_exec(p, true, block, c->stream));
             CU(launch_commit_finalize(d_instr, d_prog + 1, 1, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
                                       c->d_lengths, (int)n_instr, c->stream));
@@ -1348,6 +1382,13 @@ extern "C"
         /* nothing is re-staged, so the launches of consecutive re-runs queue up behind each other on
          * the stream without a host wait.  With a communicator attached the partial lengths are
          * all-reduced on every re-run (the site-block step of BASELINE.json configs[3]). */
+        if (c->last_inline)
+        { /* the batch went out inside kernel parameters: stage it now, re-runs read device memory */
+            Staging &st = c->ring[c->last_slot];
+            const size_t bytes = (c->last_n_prog + (size_t)c->last_K) * sizeof(FitchProgram) + c->last_n_instr * sizeof(FitchInstr);
+            CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
+            c->last_inline = false;
+        }
         return launch_resident(c, lengths, true);
     }
 
