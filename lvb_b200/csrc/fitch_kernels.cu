@@ -18,6 +18,9 @@
  */
 #include "fitch_kernels.h"
 
+#include <cstdlib>
+#include <cstring>
+
 namespace lvbgpu
 {
 
@@ -452,8 +455,9 @@ __global__ void __launch_bounds__(256, 6)
  * of.  Here every thread streams its own 16-byte column of the operand rows through a private
  * ring in shared memory with cp.async (LDGSTS), LVB_PF instructions ahead of the arithmetic;
  * no cross-thread synchronisation is needed because a thread only ever reads what it fetched. */
-#define LVB_PF 3          /* instructions in flight ahead of the one being computed */
+#define LVB_PF 3          /* instructions in flight ahead of the one being computed: large batches */
 #define LVB_RING 4        /* ring slots (LVB_PF + 1: a slot is refilled one step after it was read) */
+#define LVB_PF_DEEP 7     /* the same for small batches (latency-bound) */
 #define D_NOP 0x10000000u /* padding up to a multiple of LVB_RING (bit outside the slot-offset range) */
 
 __device__ __forceinline__ void cp_async16_if(unsigned dst, unsigned long long src, unsigned pred)
@@ -471,14 +475,23 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+/* STORE: the same pipeline for single-level store batches (an accepted move, a re-root path):
+ * results marked LVB_CTL_STORE are written to their rows, per-instruction counts are collected
+ * as in fitch_exec_kernel<true>, and the last column block of a program finalizes it.
+ * PF: instructions in flight ahead of the arithmetic; 3 keeps 7 CTAs per SM for the large,
+ * bandwidth-bound batches, 7 is for small batches, whose duration is (instructions of the longest
+ * program) x (memory latency / PF). */
+template <bool STORE, int PF>
 __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const FitchProgram *progs, const FitchInstr *instrs)
 {
+    constexpr int RING = PF + 1; /* a slot is refilled one step after it was read */
     extern __shared__ uint4 smem_u4[];
-    uint4 *s_instr = smem_u4; /* LVB_CHUNK + 2 * LVB_RING decoded instructions */
+    uint4 *s_instr = smem_u4; /* LVB_CHUNK + 2 * RING decoded instructions */
     const int tid = threadIdx.x;
     const int nthr = blockDim.x;
-    uint4 *s_ring = smem_u4 + LVB_CHUNK + 2 * LVB_RING; /* [LVB_RING][2][nthr] */
-    uint4 *s_stack = s_ring + LVB_RING * 2 * nthr;     /* [n_slots][nthr] */
+    int *s_cnt = reinterpret_cast<int *>(smem_u4 + LVB_CHUNK + 2 * RING); /* STORE: [LVB_CHUNK][warps] */
+    uint4 *s_ring = smem_u4 + LVB_CHUNK + 2 * RING + (STORE ? LVB_CHUNK * 8 / 4 : 0); /* [RING][2][nthr] */
+    uint4 *s_stack = s_ring + RING * 2 * nthr;                                       /* [n_slots][nthr] */
     __shared__ unsigned long long s_total;
 
     /* column-block-major: CTAs of different programs over the same columns run together, so
@@ -487,7 +500,8 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     const int cb = blockIdx.x / p.n_prog;
     const FitchProgram prog = progs[prog_id];
     const int col = cb * nthr + tid;
-    const unsigned amask = col < p.ncols ? ~0u : 0u;
+    const unsigned active = col < p.ncols ? 1u : 0u;
+    const unsigned amask = active ? ~0u : 0u;
     const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
     const FitchInstr *gi = instrs + prog.instr_begin;
     const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
@@ -496,6 +510,10 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     const unsigned sa_instr = (unsigned)__cvta_generic_to_shared(s_instr);
     const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
     const unsigned sa_stack = (unsigned)__cvta_generic_to_shared(s_stack + tid);
+    const int nwarps = nthr >> 5;
+    const unsigned sa_cnt = (unsigned)__cvta_generic_to_shared(s_cnt + (tid >> 5));
+    const unsigned cnt_step = (unsigned)nwarps * 4u;
+    const unsigned lane0 = (tid & 31) == 0 ? 1u : 0u;
 
     if (tid == 0)
         s_total = 0ull;
@@ -505,9 +523,9 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     for (int base = 0; base < prog.n_instr; base += LVB_CHUNK)
     {
         const int m = min(LVB_CHUNK, prog.n_instr - base);
-        const int m_pad = (m + LVB_RING - 1) / LVB_RING * LVB_RING;
+        const int m_pad = (m + RING - 1) / RING * RING;
         __syncthreads();
-        for (int i = tid; i < m_pad + LVB_RING; i += nthr)
+        for (int i = tid; i < m_pad + RING; i += nthr)
         {
             uint4 d = make_uint4(0u, 0u, 0u, D_APREV | D_NOP); /* padding: no loads, no arithmetic */
             if (i < m)
@@ -520,7 +538,7 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
                     a = b;
                     b = t;
                 }
-                unsigned w = 0u;
+                unsigned w = (STORE && (in.ctl & LVB_CTL_STORE)) ? D_STORE : 0u;
                 const unsigned push = (in.ctl & LVB_CTL_PUSH_MASK) >> LVB_CTL_PUSH_SHIFT;
                 if (push)
                     w |= D_PUSH | ((push - 1u) * slot_bytes);
@@ -538,7 +556,7 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
                 }
                 else if (b >= p.n)
                     b += tree_off;
-                d = make_uint4((unsigned)a, (unsigned)b, 0u, w);
+                d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
             }
             s_instr[i] = d;
         }
@@ -554,36 +572,73 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     }
 #define LVB_SCORE_STEP(J, S)                                                                                          \
     {                                                                                                                 \
-        cp_async_wait<LVB_PF - 1>(); /* this thread's operands of instruction J have landed */                        \
+        cp_async_wait<PF - 1>(); /* this thread's operands of instruction J have landed */                        \
         const uint4 ci = lds128(sa_instr + (unsigned)(J) * 16u);                                                      \
         uint4 y;                                                                                                      \
         /* operand a: the previous result stays in acc, or acc is replaced by the fetched row */                      \
         lds128_if(acc, sa_ring + (2u * (S)) * slot_bytes, !(ci.w & D_APREV));                                         \
         y = lds128((ci.w & D_BSLOT) ? sa_stack + ci.y : sa_ring + (2u * (S) + 1u) * slot_bytes);                      \
-        LVB_ISSUE((J) + LVB_PF, ((S) + LVB_PF) % LVB_RING) /* refills the slot read one step ago */                   \
+        LVB_ISSUE((J) + PF, ((S) + PF) % RING) /* refills the slot read one step ago */                   \
         if (!(ci.w & D_NOP))                                                                                          \
         {                                                                                                             \
             const unsigned f = fitch_step(acc, y, acc) & amask;                                                       \
-            total += __popc(f);                                                                                       \
+            if (STORE)                                                                                                \
+            {                                                                                                         \
+                sts32_if(sa_cnt + (unsigned)(J) * cnt_step, __reduce_add_sync(0xffffffffu, __popc(f)), lane0);        \
+                stg_if(row_addr(ci.z, stride_b, colbase), acc, (ci.w & D_STORE) & active);                            \
+            }                                                                                                         \
+            else                                                                                                      \
+                total += __popc(f);                                                                                   \
             sts128_if(sa_stack + (ci.w & 0x0ffffff0u), acc, ci.w & D_PUSH);                                           \
         }                                                                                                             \
     }
 
-        LVB_ISSUE(0, 0)
-        LVB_ISSUE(1, 1)
-        LVB_ISSUE(2, 2)
-        for (int i = 0; i < m_pad; i += LVB_RING)
+#pragma unroll
+        for (int s = 0; s < PF; s++)
+            LVB_ISSUE(s, s)
+        for (int i = 0; i < m_pad; i += RING)
         {
-            LVB_SCORE_STEP(i, 0)
-            LVB_SCORE_STEP(i + 1, 1)
-            LVB_SCORE_STEP(i + 2, 2)
-            LVB_SCORE_STEP(i + 3, 3)
+#pragma unroll
+            for (int s = 0; s < RING; s++)
+                LVB_SCORE_STEP(i + s, s)
         }
         cp_async_wait<0>();
+        if (STORE)
+        {
+            __syncthreads();
+            for (int k = tid; k < m; k += nthr)
+            {
+                int sum = 0;
+                for (int w = 0; w < nwarps; w++)
+                    sum += s_cnt[k * nwarps + w];
+                if (sum)
+                    atomicAdd(&p.cnts[prog.instr_begin + base + k], sum);
+            }
+        }
 #undef LVB_SCORE_STEP
 #undef LVB_ISSUE
     }
 
+    if (STORE)
+    { /* the column block that finishes last folds the counts and publishes the length */
+        __shared__ unsigned s_last;
+        __syncthreads();
+        if (tid == 0)
+        {
+            __threadfence();
+            const unsigned last = atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u ? 1u : 0u;
+            if (last)
+                p.done[prog_id] = 0u;
+            s_last = last;
+        }
+        __syncthreads();
+        if (s_last)
+        {
+            __threadfence();
+            fitch_commit_finalize_body(instrs, progs, p.cnts, p.chg_rw, p.sum_chg_rw, p.n, p.n_internal, p.out, prog_id);
+        }
+        return;
+    }
     /* per-program length: block reduce, one 64-bit atomic per CTA */
     const unsigned w = __reduce_add_sync(0xffffffffu, total);
     if ((tid & 31) == 0 && w)
@@ -634,13 +689,25 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
 
 __global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
 {
-    fitch_score_body(p, p.prog, p.instr);
+    fitch_score_body<false, LVB_PF>(p, p.prog, p.instr);
 }
 template <int NP, int NI>
 __global__ void __launch_bounds__(256)
     fitch_score_kernel_inl(const __grid_constant__ ExecParams p, const __grid_constant__ InlineBatch<NP, NI> b)
 {
-    fitch_score_body(p, b.prog, b.instr);
+    fitch_score_body<false, LVB_PF>(p, b.prog, b.instr);
+}
+/* small batches: deep pipeline; STORE: single-level store batches */
+template <bool STORE>
+__global__ void __launch_bounds__(256) fitch_pipe_kernel(const ExecParams p)
+{
+    fitch_score_body<STORE, LVB_PF_DEEP>(p, p.prog, p.instr);
+}
+template <bool STORE, int NP, int NI>
+__global__ void __launch_bounds__(256)
+    fitch_pipe_kernel_inl(const __grid_constant__ ExecParams p, const __grid_constant__ InlineBatch<NP, NI> b)
+{
+    fitch_score_body<STORE, LVB_PF_DEEP>(p, b.prog, b.instr);
 }
 
 static size_t exec_smem_bytes(bool per_node, int n_slots, int block)
@@ -648,36 +715,69 @@ static size_t exec_smem_bytes(bool per_node, int n_slots, int block)
     return (size_t)(LVB_CHUNK + 2 + (per_node ? LVB_CHUNK * 8 / 4 : 0) + (size_t)n_slots * block) * sizeof(uint4);
 }
 
+static size_t pipe_smem_bytes(bool store, int pf, int n_slots, int block)
+{
+    return (size_t)(LVB_CHUNK + 2 * (pf + 1) + (store ? LVB_CHUNK * 8 / 4 : 0) + (size_t)(2 * (pf + 1) + n_slots) * block) *
+           sizeof(uint4);
+}
+/* small launches are latency-bound: the deep pipeline (and, for single-level store batches, the
+ * pipelined store kernel); LVB_GPU_DEEP=0 keeps the round-1 kernels for A/B runs */
+static bool deep_enabled()
+{
+    static const int on = [] {
+        const char *e = getenv("LVB_GPU_DEEP");
+        return (e && atoi(e) == 0) ? 0 : 1;
+    }();
+    return on != 0;
+}
+static bool small_grid(unsigned grid) { return grid <= 148u * 4u; }
+
+template <class K>
+static cudaError_t want_smem(K kernel, size_t smem)
+{
+    if (smem > 48 * 1024)
+        return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    return cudaSuccess;
+}
+
 cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cudaStream_t stream)
 {
     const size_t smem = exec_smem_bytes(per_node, p.n_slots, block);
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
+    const bool deep = deep_enabled() && small_grid(grid);
     cudaError_t e;
-    if (per_node)
+    if (per_node && p.fused_finalize && !p.dep && deep)
     {
-        if (smem > 48 * 1024 &&
-            (e = cudaFuncSetAttribute(fitch_exec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem)) != cudaSuccess)
+        const size_t sm = pipe_smem_bytes(true, LVB_PF_DEEP, p.n_slots, block);
+        if ((e = want_smem(fitch_pipe_kernel<true>, sm)) != cudaSuccess)
+            return e;
+        fitch_pipe_kernel<true><<<grid, block, sm, stream>>>(p);
+    }
+    else if (per_node)
+    {
+        if ((e = want_smem(fitch_exec_kernel<true>, smem)) != cudaSuccess)
             return e;
         fitch_exec_kernel<true><<<grid, block, smem, stream>>>(p);
     }
     else if (p.score_v1)
     {
-        if (smem > 48 * 1024 &&
-            (e = cudaFuncSetAttribute(fitch_exec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem)) != cudaSuccess)
+        if ((e = want_smem(fitch_exec_kernel<false>, smem)) != cudaSuccess)
             return e;
         fitch_exec_kernel<false><<<grid, block, smem, stream>>>(p);
     }
+    else if (deep)
+    {
+        const size_t sm = pipe_smem_bytes(false, LVB_PF_DEEP, p.n_slots, block);
+        if ((e = want_smem(fitch_pipe_kernel<false>, sm)) != cudaSuccess)
+            return e;
+        fitch_pipe_kernel<false><<<grid, block, sm, stream>>>(p);
+    }
     else
     {
-        const size_t smem2 =
-            (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(2 * LVB_RING + p.n_slots) * block) * sizeof(uint4);
-        if (smem2 > 48 * 1024 &&
-            (e = cudaFuncSetAttribute(fitch_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)) !=
-                cudaSuccess)
+        const size_t sm = pipe_smem_bytes(false, LVB_PF, p.n_slots, block);
+        if ((e = want_smem(fitch_score_kernel, sm)) != cudaSuccess)
             return e;
-        fitch_score_kernel<<<grid, block, smem2, stream>>>(p);
+        fitch_score_kernel<<<grid, block, sm, stream>>>(p);
     }
     return cudaGetLastError();
 }
@@ -706,26 +806,32 @@ bool inline_batch_fits(int n_prog, int n_cand, size_t n_instr)
 template <int NP, int NI>
 static cudaError_t launch_inline_t(const ExecParams &p, bool per_node, int block, cudaStream_t stream,
                                    const FitchProgram *prog, int n_prog, const FitchProgram *cand, int n_cand,
-                                   const FitchInstr *instr, size_t n_instr, bool finalize, int32_t *chg,
-                                   long long *sum_chg, long long *lengths, int max_instr)
+                                   const FitchInstr *instr, size_t n_instr, int32_t *chg, long long *sum_chg,
+                                   long long *lengths, int max_instr)
 {
     static thread_local InlineBatch<NP, NI> tb; /* host copy; the launch copies it into the command stream */
     memcpy(tb.prog, prog, (size_t)n_prog * sizeof(FitchProgram));
     memcpy(tb.cand, cand, (size_t)n_cand * sizeof(FitchProgram));
     memcpy(tb.instr, instr, n_instr * sizeof(FitchInstr));
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
+    const bool deep = deep_enabled();
     cudaError_t e;
-    if (per_node)
+    if (per_node && p.fused_finalize && deep)
+    {
+        const size_t sm = pipe_smem_bytes(true, LVB_PF_DEEP, p.n_slots, block);
+        if ((e = want_smem(fitch_pipe_kernel_inl<true, NP, NI>, sm)) != cudaSuccess)
+            return e;
+        fitch_pipe_kernel_inl<true, NP, NI><<<grid, block, sm, stream>>>(p, tb);
+    }
+    else if (per_node)
     {
         const size_t smem = exec_smem_bytes(true, p.n_slots, block);
-        if (smem > 48 * 1024 &&
-            (e = cudaFuncSetAttribute(fitch_exec_kernel_inl<true, NP, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem)) != cudaSuccess)
+        if ((e = want_smem(fitch_exec_kernel_inl<true, NP, NI>, smem)) != cudaSuccess)
             return e;
         fitch_exec_kernel_inl<true, NP, NI><<<grid, block, smem, stream>>>(p, tb);
         if ((e = cudaGetLastError()) != cudaSuccess)
             return e;
-        if (finalize && !p.fused_finalize)
+        if (!p.fused_finalize)
         {
             int threads = 32;
             while (threads < max_instr && threads < 1024)
@@ -734,15 +840,19 @@ static cudaError_t launch_inline_t(const ExecParams &p, bool per_node, int block
                                                                                     p.n_internal, lengths);
         }
     }
+    else if (deep)
+    {
+        const size_t sm = pipe_smem_bytes(false, LVB_PF_DEEP, p.n_slots, block);
+        if ((e = want_smem(fitch_pipe_kernel_inl<false, NP, NI>, sm)) != cudaSuccess)
+            return e;
+        fitch_pipe_kernel_inl<false, NP, NI><<<grid, block, sm, stream>>>(p, tb);
+    }
     else
     {
-        const size_t smem2 =
-            (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(2 * LVB_RING + p.n_slots) * block) * sizeof(uint4);
-        if (smem2 > 48 * 1024 &&
-            (e = cudaFuncSetAttribute(fitch_score_kernel_inl<NP, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem2)) != cudaSuccess)
+        const size_t sm = pipe_smem_bytes(false, LVB_PF, p.n_slots, block);
+        if ((e = want_smem(fitch_score_kernel_inl<NP, NI>, sm)) != cudaSuccess)
             return e;
-        fitch_score_kernel_inl<NP, NI><<<grid, block, smem2, stream>>>(p, tb);
+        fitch_score_kernel_inl<NP, NI><<<grid, block, sm, stream>>>(p, tb);
     }
     return cudaGetLastError();
 }
@@ -754,10 +864,9 @@ cudaError_t launch_fitch_inline(const ExecParams &p, bool per_node, int block, c
 {
     if (n_prog <= LVB_INL_SMALL_P && n_cand <= LVB_INL_SMALL_P && n_instr <= (size_t)LVB_INL_SMALL_I)
         return launch_inline_t<LVB_INL_SMALL_P, LVB_INL_SMALL_I>(p, per_node, block, stream, prog, n_prog, cand, n_cand,
-                                                                 instr, n_instr, per_node, chg, sum_chg, lengths,
-                                                                 max_instr);
+                                                                 instr, n_instr, chg, sum_chg, lengths, max_instr);
     return launch_inline_t<LVB_INL_LARGE_P, LVB_INL_LARGE_I>(p, per_node, block, stream, prog, n_prog, cand, n_cand, instr,
-                                                             n_instr, per_node, chg, sum_chg, lengths, max_instr);
+                                                             n_instr, chg, sum_chg, lengths, max_instr);
 }
 
 cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
