@@ -972,7 +972,10 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
         double prof[4] = {0, 0, 0, 0};
     };
     std::vector<GroupStat> stat((size_t)G);
-    const int inner = std::max(1, host_threads / G);
+    /* per-chain work of a round is tens of microseconds: beyond 16 threads a team costs more at its
+     * barriers than it gains (measured on a 32-core box, 64 chains on one GPU: the replay loop
+     * takes 3.2 s with a team of 32 against 0.35 s with 16; profiles/r01g_sa_config5_devices.log) */
+    const int inner = std::max(1, std::min(16, host_threads / G));
     if (G == 1)
         run_group(MSA, dev, chains, 0, R, std::min(inner, R), stat[0].score_launches, stat[0].rounds, stat[0].prof);
     else
