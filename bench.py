@@ -203,7 +203,7 @@ def nni_candidates(left, right, root, n, count, seed):
         parent[left[v]] = v
         parent[right[v]] = v
     rng = np.random.default_rng(seed)
-    out = []
+    out, index = [], []  # index: position of the candidate in lvb_gpu_nni_neighbourhood's output
     for u in rng.integers(n, B, size=count).tolist():
         v = int(parent[u])
         a, b = int(left[u]), int(right[u])
@@ -221,7 +221,8 @@ def nni_candidates(left, right, root, n, count, seed):
             dirty.append(w)
             w = int(parent[w])
         out.append(Topology(l2, r2, root, dirty))
-    return out
+        index.append(2 * (u - n) + (1 if swap_a else 0))
+    return out, index
 
 
 def main():
@@ -290,12 +291,12 @@ def main():
         from lvb_b200 import sharding
 
         w0, wc = sharding.word_block(nwords, rank, world)
-        eng.upload(enc, word_begin=w0, word_count=wc, max_trees=1)
+        eng.upload(enc, word_begin=w0, word_count=wc, max_trees=2)
         uid = [Engine.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         eng.comm_init(world, rank, uid[0])
     else:
-        eng.upload(enc, max_trees=1)
+        eng.upload(enc, max_trees=2)
     tree = eng.tree_create()
     # every rank its own trees in replica mode; the same tree on every rank in site-block mode
     tree_seed = 3 if siteblock else 3 + 1000 * rank
@@ -343,7 +344,7 @@ def main():
 
         # ---- SA candidate scoring: trees scored/s ----
         eng.commit(tree, topo)
-        cands = nni_candidates(left, right, root, n, args.candidates, seed=5 + rank)
+        cands, cand_index = nni_candidates(left, right, root, n, args.candidates, seed=5 + (0 if siteblock else rank))
         trees = [tree] * len(cands)
         got = eng.score_batch(trees, cands)
         barrier()
@@ -364,6 +365,20 @@ def main():
 
         rows_read = [int((compile_schedule(n, c, store=False)[0][:, :2] >= 0).sum()) for c in cands[:64]]
         rows_read_mean = float(np.mean(rows_read))
+
+        # ---- exhaustive NNI neighbourhood (deterministic_hillclimb's 2(n-3) candidates) in one call ----
+        scratch = eng.tree_create()
+        nn = eng.nni_neighbourhood(tree, scratch, topo)
+        barrier()
+        t0 = time.perf_counter()
+        reps_n = 3
+        for _ in range(reps_n):
+            nn = eng.nni_neighbourhood(tree, scratch, topo)
+        barrier()
+        wall_n = max_over_ranks(time.perf_counter() - t0)
+        nn_kernel_ms = eng.last_kernel_ms()
+        # the neighbourhood call and the dirty-path route must agree on the candidates they share
+        nn_ok = bool(np.array_equal(nn[np.asarray(cand_index)], np.asarray(got)))
 
     total_ranks = 1 if siteblock else world
     value = total_ranks * args.steps * updates_per_pass / wall_a
@@ -414,6 +429,12 @@ def main():
             "note": "SURVEY.md 8(d): 8 B x nwords x (clean rows read) per candidate, nothing written; candidates "
                     "of one tree share sibling rows, so part of this is served by L2 and the figure may exceed the "
                     "HBM peak",
+        },
+        "nni_neighbourhood": {
+            "candidates": int(len(nn)), "ms_per_call": wall_n / reps_n * 1e3,
+            "candidates_per_s": total_ranks * len(nn) / (wall_n / reps_n),
+            "four_row_kernel_ms": nn_kernel_ms, "agrees_with_score_batch": bool(nn_ok),
+            "api": "lvb_gpu_nni_neighbourhood: up-pass program + four-row kernel, host arrays in, 2(n-3) lengths out",
         },
         "length_check": int(length0), "e2e_lengths_head": [int(x) for x in lens[:3]],
     }

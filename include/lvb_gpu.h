@@ -194,9 +194,12 @@ int lvb_gpu_compile_pieces(int64_t n, const lvb_gpu_topology *topo, int piece_si
 /* Host-only: the up-pass program lvb_gpu_nni_neighbourhood runs — one store instruction per
  * internal node v, in pre-order, whose result is the Fitch set of the tree WITHOUT the subtree
  * below v.  Operand rows >= n are rows of the evaluated tree; results belong under the same node
- * numbers in the scratch tree. */
-int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int32_t *instr, int64_t cap, int64_t *n_instr,
-                            int64_t *n_slots);
+ * numbers in the scratch tree.
+ * piece_size > 0 cuts it into a top piece (level 0) and independent subtrees of at most piece_size
+ * nodes (level 1, run after level 0), reported as {instr_begin, n_instr, level} triples; an
+ * operand (2n-3) + (v - n) then names the row of v in the scratch tree. */
+int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,
+                            int64_t *n_instr, int64_t *n_slots, int32_t *pieces, int64_t pieces_cap, int64_t *n_pieces);
 
 #ifdef __cplusplus
 }

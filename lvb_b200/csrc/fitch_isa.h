@@ -16,7 +16,9 @@
 
 /* Operand encoding of FitchInstr::a / ::b
  *   v >= 0        state row of LVB node v (leaf: the alignment row; internal: the row the
- *                 program's tree currently holds for v) — read from HBM
+ *                 program's tree currently holds for v) — read from HBM.  Store programs that
+ *                 read one tree and write another (FitchProgram::src_tree1) name a row of the
+ *                 tree they write as (2n-3) + (v - n)
  *   OPER_PREV     the result of the previous instruction (still in registers)
  *   OPER_SLOT(s)  on-chip stack slot s (shared memory), written by an earlier push
  */

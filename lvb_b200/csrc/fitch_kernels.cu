@@ -269,15 +269,15 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
                     w |= D_APREV;
                     a = 0;
                 }
-                else if (a >= p.n)
-                    a += src_off;
+                else if (a >= p.n) /* rows >= n + I: the program's own (store) tree, see compile_up_pass */
+                    a = a >= p.n + p.n_internal ? a - p.n_internal + (int)tree_off : a + (int)src_off;
                 if (b < 0)
                 {
                     w |= D_BSLOT;
                     b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
                 }
                 else if (b >= p.n)
-                    b += src_off;
+                    b = b >= p.n + p.n_internal ? b - p.n_internal + (int)tree_off : b + (int)src_off;
                 d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
             }
             s_instr[i] = d;

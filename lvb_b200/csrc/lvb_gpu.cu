@@ -154,6 +154,7 @@ struct lvb_gpu_ctx
                                                         * OpenMP threads, >= grain candidates each */
     bool inline_ok = true;   /* small batches travel inside the kernel parameters (LVB_GPU_INLINE=0: always staged) */
     bool last_inline = false;
+    bool up_pieces = true;   /* the up-pass of lvb_gpu_nni_neighbourhood is cut into pieces (LVB_GPU_UP_PIECES=0: one program) */
     bool fuse_ok = true;     /* single-level store batches finalize inside the Fitch kernel (LVB_GPU_FUSE=0: own launch) */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
@@ -793,6 +794,8 @@ extern "C"
             c->compile_par_min = atoi(cp);
         const char *il = getenv("LVB_GPU_INLINE");
         c->inline_ok = !(il && atoi(il) == 0);
+        const char *up = getenv("LVB_GPU_UP_PIECES");
+        c->up_pieces = !(up && atoi(up) == 0);
         const char *fz = getenv("LVB_GPU_FUSE");
         c->fuse_ok = !(fz && atoi(fz) == 0);
         const char *v1 = getenv("LVB_GPU_SCORE_V1");
@@ -1121,8 +1124,20 @@ extern "C"
         std::vector<int32_t> parent, left, right;
         std::string err;
         int n_slots = 0;
-        if (!c->sc[0]->compile_up_pass(*topo, instr, n_slots, parent, left, right, err))
+        /* like a large commit, the up-pass is cut so that enough warps are resident: a top piece, then
+         * every cut-off subtree as a program of its own in a second launch */
+        std::vector<ScheduleCompiler::Piece> pcs;
+        int piece_size = 0;
+        if (c->I >= 64 && c->up_pieces)
+        {
+            const int64_t warps_per_piece = (c->stride_u4 + 31) / 32;
+            const int64_t want = std::max<int64_t>(1, c->target_warps / warps_per_piece);
+            if (want > 1)
+                piece_size = (int)std::max<int64_t>(16, (c->I + want - 1) / want);
+        }
+        if (!c->sc[0]->compile_up_pass(*topo, instr, n_slots, parent, left, right, err, piece_size, &pcs))
             return fail("%s", err.c_str());
+        const size_t n_pcs = pcs.size();
         const int64_t E = c->I;
         const size_t n_instr = instr.size();
         if (ensure_device_arrays(c, n_instr, 1))
@@ -1137,17 +1152,24 @@ extern "C"
             CU(cudaMalloc(&c->d_nni, c->cap_nni * sizeof(long long)));
             CU(cudaMallocHost(&c->h_nni, c->cap_nni * sizeof(long long)));
         }
-        const size_t bytes = 2 * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr) + (size_t)E * sizeof(uint4);
+        const size_t bytes = (n_pcs + 1) * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr) + (size_t)E * sizeof(uint4);
         int slot;
         if (acquire_slot(c, bytes, 1, &slot))
             return 1;
         Staging &st = c->ring[slot];
         FitchProgram *h_prog = reinterpret_cast<FitchProgram *>(st.h);
-        FitchInstr *h_instr = reinterpret_cast<FitchInstr *>(h_prog + 2);
+        FitchInstr *h_instr = reinterpret_cast<FitchInstr *>(h_prog + n_pcs + 1);
         uint4 *h_rows = reinterpret_cast<uint4 *>(h_instr + n_instr);
-        /* up-pass: operands from `tree`, stores (and the per-node counts nobody reads) into scratch_tree */
-        h_prog[0] = FitchProgram{0, (int32_t)n_instr, scratch_tree, 0, -1, 0, tree + 1, 0};
-        h_prog[1] = FitchProgram{0, (int32_t)n_instr, scratch_tree, 1, -1, 0, tree + 1, 0};
+        /* up-pass: operands from `tree`, stores (and the per-node counts nobody reads) into scratch_tree;
+         * pieces are in level order (the top piece first), the last record covers the whole program
+         * for the finalize step */
+        size_t n_level0 = 0;
+        for (size_t i = 0; i < n_pcs; i++)
+        {
+            h_prog[i] = FitchProgram{pcs[i].instr_begin, pcs[i].n_instr, scratch_tree, 0, -1, 0, tree + 1, 0};
+            n_level0 += pcs[i].level == 0 ? 1 : 0;
+        }
+        h_prog[n_pcs] = FitchProgram{0, (int32_t)n_instr, scratch_tree, 1, -1, 0, tree + 1, 0};
         if (n_instr)
             memcpy(h_instr, instr.data(), n_instr * sizeof(FitchInstr));
         const int64_t root = topo->root;
@@ -1162,7 +1184,7 @@ extern "C"
         CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
         c->tree_ready[scratch_tree] = 0; /* its rows now hold up sets, not an evaluated tree */
         const FitchProgram *d_prog = reinterpret_cast<const FitchProgram *>(st.d);
-        const FitchInstr *d_instr = reinterpret_cast<const FitchInstr *>(d_prog + 2);
+        const FitchInstr *d_instr = reinterpret_cast<const FitchInstr *>(d_prog + n_pcs + 1);
         const uint4 *d_rows = reinterpret_cast<const uint4 *>(d_instr + n_instr);
         const int block = pick_block(c);
         const int n_cb = (int)((c->stride_u4 + block - 1) / block);
@@ -1174,12 +1196,10 @@ extern "C"
             p.ncols = (int32_t)c->stride_u4;
             p.n = (int32_t)c->n;
             p.n_internal = (int32_t)c->I;
-            p.n_prog = 1;
             p.n_colblocks = n_cb;
             p.n_slots = n_slots;
             p.score_v1 = 0;
             p.instr = d_instr;
-            p.prog = d_prog;
             p.totals = c->d_totals;
             p.done = c->d_done;
             p.out = c->d_lengths;
@@ -1191,10 +1211,21 @@ extern "C"
             p.chg_rw = c->chg;
             p.sum_chg_rw = c->sum_chg;
             p.fused_finalize = 0;
-            CU(launch_fitch_exec(p, true, block, c->stream));
-            CU(launch_commit_finalize(d_instr, d_prog + 1, 1, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
+            const size_t level_first[2] = {0, n_level0}, level_count[2] = {n_level0, n_pcs - n_level0};
+            for (int lv = 0; lv < 2; lv++)
+            {
+                if (!level_count[lv])
+                    continue;
+                p.prog = d_prog + level_first[lv];
+                p.n_prog = (int32_t)level_count[lv];
+                if ((int64_t)p.n_prog * n_cb > (int64_t)INT32_MAX)
+                    return fail("lvb_gpu_nni_neighbourhood: %lld CTAs", (long long)p.n_prog * n_cb);
+                CU(launch_fitch_exec(p, true, block, c->stream));
+                c->launches++;
+            }
+            CU(launch_commit_finalize(d_instr, d_prog + n_pcs, 1, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I,
                                       c->d_lengths, (int)n_instr, c->stream));
-            c->launches += 2;
+            c->launches++;
         }
         CU(cudaMemsetAsync(c->d_nni, 0, (size_t)(2 * E) * sizeof(long long), c->stream));
         NniParams q;
@@ -1442,8 +1473,8 @@ extern "C"
         return 0;
     }
 
-    int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int32_t *instr, int64_t cap, int64_t *n_instr,
-                                int64_t *n_slots)
+    int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,
+                                int64_t *n_instr, int64_t *n_slots, int32_t *pieces, int64_t pieces_cap, int64_t *n_pieces)
     {
         if (!topo || !n_instr || !n_slots)
             return fail("lvb_gpu_compile_up_pass: null argument");
@@ -1454,10 +1485,24 @@ extern "C"
         std::vector<int32_t> parent, left, right;
         int slots = 0;
         std::string err;
-        if (!sc.compile_up_pass(*topo, out, slots, parent, left, right, err))
+        std::vector<ScheduleCompiler::Piece> pcs;
+        if (!sc.compile_up_pass(*topo, out, slots, parent, left, right, err, piece_size, &pcs))
             return fail("%s", err.c_str());
         *n_instr = (int64_t)out.size();
         *n_slots = slots;
+        if (n_pieces)
+            *n_pieces = (int64_t)pcs.size();
+        if (pieces)
+        {
+            if ((int64_t)pcs.size() > pieces_cap)
+                return fail("piece buffer too small: need %zu", pcs.size());
+            for (size_t i = 0; i < pcs.size(); i++)
+            {
+                pieces[3 * i] = pcs[i].instr_begin;
+                pieces[3 * i + 1] = pcs[i].n_instr;
+                pieces[3 * i + 2] = pcs[i].level;
+            }
+        }
         if (instr)
         {
             if ((int64_t)out.size() > cap)

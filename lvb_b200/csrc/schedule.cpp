@@ -295,8 +295,14 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
 
 bool ScheduleCompiler::compile_up_pass(const lvb_gpu_topology &topo, std::vector<FitchInstr> &out, int &n_slots,
                                        std::vector<int32_t> &parent, std::vector<int32_t> &left,
-                                       std::vector<int32_t> &right, std::string &err)
+                                       std::vector<int32_t> &right, std::string &err, int piece_size,
+                                       std::vector<Piece> *pieces)
 {
+    if (piece_size > 0 && !pieces)
+    {
+        err = "up-pass: pieces wanted but no place to put them";
+        return false;
+    }
     const int64_t root = topo.root;
     if (n_ < 4 || root < 0 || root >= n_)
     {
@@ -372,9 +378,32 @@ bool ScheduleCompiler::compile_up_pass(const lvb_gpu_topology &topo, std::vector
             need_[v] = std::max(std::max(na, nb), std::min(na, nb) + 1);
         else
             need_[v] = std::max(0, std::max(na, nb));
+        size_[v] = 1 + (a >= n_ ? size_[a] : 0) + (b >= n_ ? size_[b] : 0); /* internal nodes at and below v */
     }
+    /* pieces: the walk stops in front of every maximal subtree of at most piece_size internal
+     * nodes (tiny ones stay inline); up(c) of such a subtree's top c is still computed and stored
+     * by the piece above, and the subtree becomes a program of its own (level 1) that starts by
+     * reading that row back.  All level-1 programs are independent of each other. */
+    std::vector<uint8_t> is_cut;
+    std::vector<int32_t> cut_roots;
+    if (piece_size > 0)
+    {
+        is_cut.assign((size_t)B_, 0);
+        const int min_size = std::max(2, piece_size / 4);
+        for (int32_t v : order_)
+        {
+            const int32_t pv = parent[v];
+            const bool parent_big = pv == root || size_[pv] > piece_size;
+            if (parent_big && size_[v] <= piece_size && size_[v] >= min_size)
+            {
+                is_cut[(size_t)v] = 1;
+                cut_roots.push_back(v);
+            }
+        }
+    }
+    auto enter = [&](int32_t c, bool top_piece) { return !(top_piece && piece_size > 0 && is_cut[(size_t)c]); };
     int depth = 0, peak = 0;
-    auto walk = [&](int32_t top) { /* the instruction that produced up(top) was emitted last */
+    auto walk = [&](int32_t top, bool top_piece) { /* the instruction that produced up(top) was emitted last */
         frames_.clear();
         frames_.push_back(Frame{top, -1, -1, 0});
         while (!frames_.empty())
@@ -395,13 +424,17 @@ bool ScheduleCompiler::compile_up_pass(const lvb_gpu_topology &topo, std::vector
                     peak = std::max(peak, depth);
                     const int32_t c = f.first, o = f.second;
                     out.push_back(FitchInstr{LVB_OPER_PREV, o, c, LVB_CTL_STORE});
-                    frames_.push_back(Frame{c, -1, -1, 0});
+                    if (enter(c, top_piece))
+                        frames_.push_back(Frame{c, -1, -1, 0});
                 }
                 else if (ia || ib)
                 {
                     const int32_t c = ia ? a : b, o = ia ? b : a;
                     out.push_back(FitchInstr{LVB_OPER_PREV, o, c, LVB_CTL_STORE});
-                    f = Frame{c, -1, -1, 0}; /* tail call */
+                    if (enter(c, top_piece))
+                        f = Frame{c, -1, -1, 0}; /* tail call */
+                    else
+                        frames_.pop_back();
                 }
                 else
                     frames_.pop_back();
@@ -411,17 +444,33 @@ bool ScheduleCompiler::compile_up_pass(const lvb_gpu_topology &topo, std::vector
                 depth--;
                 const int32_t c = f.second, o = f.first;
                 out.push_back(FitchInstr{LVB_OPER_SLOT(depth), o, c, LVB_CTL_STORE});
-                f = Frame{c, -1, -1, 0};
+                if (enter(c, top_piece))
+                    f = Frame{c, -1, -1, 0};
+                else
+                    frames_.pop_back();
             }
         }
     };
+    const size_t begin0 = out.size();
     const int32_t rc[2] = {left[root], right[root]};
     for (int k = 0; k < 2; k++)
         if (rc[k] >= n_)
         {
             out.push_back(FitchInstr{(int32_t)root, rc[1 - k], rc[k], LVB_CTL_STORE});
-            walk(rc[k]);
+            if (enter(rc[k], true))
+                walk(rc[k], true);
         }
+    if (pieces)
+        pieces->push_back(Piece{(int32_t)begin0, (int32_t)(out.size() - begin0), 0});
+    /* level 1: operand B + (c - n) names the row of c in the tree the program STORES to */
+    const int32_t own = (int32_t)(B_ - n_);
+    for (int32_t c : cut_roots)
+    {
+        const size_t begin = out.size();
+        out.push_back(FitchInstr{c + own, c + own, -1, 0u}); /* up(c) into the previous-result register */
+        walk(c, false);
+        pieces->push_back(Piece{(int32_t)begin, (int32_t)(out.size() - begin), 1});
+    }
     if (peak > LVB_MAX_SLOTS)
     {
         err = "up-pass: program needs " + std::to_string(peak) + " stack slots";

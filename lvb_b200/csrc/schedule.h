@@ -53,10 +53,13 @@ class ScheduleCompiler
      * traversal is pre-order with up(parent) in the previous-result register or in a stack
      * slot, so no instruction reads a row the program itself stores.
      * parent receives the parent of every node (root: -1).  Used by the exhaustive NNI
-     * neighbourhood (src/Solve.c:64-142). */
+     * neighbourhood (src/Solve.c:64-142).
+     * piece_size > 0: the program is cut into a top piece (level 0) and independent subtrees of at
+     * most piece_size internal nodes (level 1, run after level 0); an operand B + (v - n) then names
+     * the row of v in the tree the program stores to (up(v), stored by the top piece). */
     bool compile_up_pass(const lvb_gpu_topology &topo, std::vector<FitchInstr> &out, int &n_slots,
                          std::vector<int32_t> &parent, std::vector<int32_t> &left, std::vector<int32_t> &right,
-                         std::string &err);
+                         std::string &err, int piece_size = 0, std::vector<Piece> *pieces = nullptr);
 
   private:
     struct Frame

@@ -81,7 +81,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_synchronize.argtypes = [vp]
     lib.lvb_gpu_compile_schedule.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64)]
     lib.lvb_gpu_compile_pieces.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64), vp, i64, C.POINTER(i64)]
-    lib.lvb_gpu_compile_up_pass.argtypes = [i64, C.POINTER(_Topo), vp, i64, C.POINTER(i64), C.POINTER(i64)]
+    lib.lvb_gpu_compile_up_pass.argtypes = [i64, C.POINTER(_Topo), C.c_int, vp, i64, C.POINTER(i64), C.POINTER(i64), vp, i64, C.POINTER(i64)]
     _lib = lib
     return lib
 
@@ -141,15 +141,18 @@ def compile_schedule(n: int, topo: Topology, store: bool = False):
     return out, int(slots.value)
 
 
-def compile_up_pass(n: int, topo: Topology):
-    """Host-only: the up-pass program of the NNI neighbourhood as an (n-3, 4) int32 array and its slot count."""
+def compile_up_pass(n: int, topo: Topology, piece_size: int = 0):
+    """Host-only: the up-pass program of the NNI neighbourhood: (instr (k,4) int32, slots, pieces (p,3)
+    int32 rows {instr_begin, n_instr, level})."""
     lib = load_library()
     ts = topo.as_struct()
-    k, slots = C.c_int64(0), C.c_int64(0)
-    _check(lib.lvb_gpu_compile_up_pass(n, C.byref(ts), None, 0, C.byref(k), C.byref(slots)))
+    k, slots, npc = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    _check(lib.lvb_gpu_compile_up_pass(n, C.byref(ts), piece_size, None, 0, C.byref(k), C.byref(slots), None, 0, C.byref(npc)))
     out = np.zeros((k.value, 4), dtype=np.int32)
-    _check(lib.lvb_gpu_compile_up_pass(n, C.byref(ts), out.ctypes.data, k.value, C.byref(k), C.byref(slots)))
-    return out, int(slots.value)
+    pieces = np.zeros((npc.value, 3), dtype=np.int32)
+    _check(lib.lvb_gpu_compile_up_pass(n, C.byref(ts), piece_size, out.ctypes.data, k.value, C.byref(k), C.byref(slots),
+                                       pieces.ctypes.data, npc.value, C.byref(npc)))
+    return out, int(slots.value), pieces
 
 
 def compile_pieces(n: int, topo: Topology, piece_size: int):

@@ -279,15 +279,27 @@ def test_up_pass_program_and_four_row_nni_lengths(n, m, shape):
     enc = synthetic.pack_states(st)
     left, right, root = synthetic.random_topology(n, seed=n + 1) if shape == "random" else synthetic.shaped_topology(n, shape)
     base, rows, _ = oracles.oracle_getplen(enc, left, right, root)
-    instr, slots = compile_up_pass(n, Topology(left, right, root))
+    instr, slots, pieces = compile_up_pass(n, Topology(left, right, root))
     B = 2 * n - 3
-    assert instr.shape == (n - 3, 4)
+    assert instr.shape == (n - 3, 4) and pieces.tolist() == [[0, n - 3, 0]]
     assert sorted(instr[:, 2].tolist()) == list(range(n, B))      # every internal node once
     assert np.all(instr[:, 3] & fitch_vm.CTL_STORE)
     assert slots <= max(1, int(np.ceil(np.log2(n))))
     # no instruction reads a row the program stores: internal operands are rows of the evaluated tree
     up = rows.copy()
-    fitch_vm.run_program(instr, _ReadLowWriteUp(rows, up), n, store=True)
+    fitch_vm.run_program(instr, _ReadLowWriteUp(rows, up, B, n), n, store=True)
+    # cut into a top piece and independent subtrees: same up sets, level 1 after level 0, any order inside
+    for piece_size in (2, 5, 16):
+        pi, _, pcs = compile_up_pass(n, Topology(left, right, root), piece_size)
+        assert pcs[0].tolist()[2] == 0 and all(p[2] == 1 for p in pcs[1:].tolist())
+        assert sum(p[1] for p in pcs.tolist()) == len(pi) == (n - 3) + (len(pcs) - 1)   # one loader per cut piece
+        stored = pi[pi[:, 2] >= 0]
+        assert sorted(stored[:, 2].tolist()) == list(range(n, B))
+        up2 = np.zeros_like(rows)
+        view = _ReadLowWriteUp(rows, up2, B, n)
+        for b, k, _lvl in [pcs[0].tolist()] + pcs[1:][::-1].tolist():
+            fitch_vm.run_program(pi[b:b + k], view, n, store=True)
+        assert np.array_equal(up2[n:], up[n:]), piece_size
     for u, v, a, b, c, l2, r2 in _nni_candidates(left, right, root, n):
         A, Bq, Cq = rows[a], rows[b], rows[c]
         D = rows[root] if v == root else up[v]
@@ -305,11 +317,12 @@ def test_up_pass_program_and_four_row_nni_lengths(n, m, shape):
 class _ReadLowWriteUp:
     """rows[] as the up-pass sees them: operands come from the evaluated tree, stores go to the scratch tree"""
 
-    def __init__(self, low, up):
-        self.low, self.up = low, up
+    def __init__(self, low, up, B, n):
+        self.low, self.up, self.B, self.n = low, up, B, n
 
     def __getitem__(self, v):
-        return self.low[v]
+        # B + (v - n): the row of v in the tree the program stores to (fitch_isa.h)
+        return self.up[v - self.B + self.n] if v >= self.B else self.low[v]
 
     def __setitem__(self, v, val):
         self.up[v] = val
