@@ -888,8 +888,10 @@ cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *
  * parent of u (its "up" set, produced by the up-pass program), the current tree is
  * ((A,B),(C,D)), the candidate for left == FALSE is ((A,C),(B,D)) and the one for left == TRUE
  * is ((B,C),(A,D)); the lengths inside A, B, C and D are common to all three.  One thread
- * reads its 16-byte column of the four rows and returns both length differences: 4 rows of
- * traffic per PAIR of candidates, whatever the depth of u. */
+ * reads its 16-byte column of the four rows (and of the two rows the current tree has for this
+ * branch) and returns both length differences: 6 rows of traffic per PAIR of candidates, whatever
+ * the depth of u.  The kernel is bound by integer issue, not by HBM (ncu: ALU pipe 86 %), so
+ * reading low(u)/up(u) instead of recomputing fitch(A,B)/fitch(C,D) is a net gain. */
 __device__ __forceinline__ unsigned fitch_lane_flags(unsigned x, unsigned y)
 {
     const unsigned t = x & y;
@@ -917,7 +919,7 @@ __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams 
     __shared__ int s_d[2];
     const int tid = threadIdx.x;
     /* column-block-major: the CTAs of neighbouring branches over the same columns run together,
-     * and a row is an operand of up to three branches (its own, its sister's, its children's) */
+     * and a row is an operand of up to four branches (its own, its sister's, its children's) */
     const int edge = blockIdx.x % p.n_edges;
     const int cb = blockIdx.x / p.n_edges;
     const int col = cb * blockDim.x + tid;
@@ -927,13 +929,19 @@ __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams 
     int d0 = 0, d1 = 0;
     if (col < p.ncols)
     {
-        const uint4 r = p.rows[edge]; /* pool rows of A, B, C, D */
+        const uint4 r = p.rows[edge];  /* pool rows of A, B, C, D */
+        const uint2 r2 = p.rows2[edge]; /* pool rows of low(u) = fitch(A,B) and up(u) = fitch(C,D) */
         const uint4 *base = p.pool + col;
         const uint4 A = __ldg(base + (size_t)r.x * p.stride_u4);
         const uint4 B = __ldg(base + (size_t)r.y * p.stride_u4);
         const uint4 C = __ldg(base + (size_t)r.z * p.stride_u4);
         const uint4 D = __ldg(base + (size_t)r.w * p.stride_u4);
-        const int cur = join_cost(A, B, C, D);
+        const uint4 LU = __ldg(base + (size_t)r2.x * p.stride_u4);
+        const uint4 UU = __ldg(base + (size_t)r2.y * p.stride_u4);
+        /* the current tree on this branch costs changes(A,B) + changes(C,D) + changes(low(u), up(u)):
+         * the first two are the cached counts of u in the two trees (subtracted once per branch
+         * below), both sets are rows already — only the third term is computed here */
+        const int cur = fitch_count(LU, UU);
         d0 = join_cost(A, C, B, D) - cur;
         d1 = join_cost(B, C, A, D) - cur;
     }
@@ -947,9 +955,14 @@ __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams 
             atomicAdd(&s_d[1], d1);
     }
     __syncthreads();
-    if (tid < 2 && s_d[tid])
-        atomicAdd(reinterpret_cast<unsigned long long *>(p.delta + 2 * (size_t)edge + tid),
-                  (unsigned long long)(long long)s_d[tid]);
+    if (tid < 2)
+    {
+        long long v = s_d[tid];
+        if (cb == 0)
+            v -= (long long)p.chg_low[edge] + (long long)p.chg_up[edge];
+        if (v)
+            atomicAdd(reinterpret_cast<unsigned long long *>(p.delta + 2 * (size_t)edge + tid), (unsigned long long)v);
+    }
 }
 
 cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t stream)

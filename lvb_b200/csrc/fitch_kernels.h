@@ -63,8 +63,9 @@ cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *
 
 /* Exhaustive NNI neighbourhood (Solve.c:64-142, TreeOperations.c:105-158): branch e joins the
  * pool rows rows[e] = {A, B, C, D}; delta[2e] += length(((A,C),(B,D))) - length(((A,B),(C,D))),
- * delta[2e+1] += length(((B,C),(A,D))) - the same, over this context's columns.  delta must be
- * zero before the launch. */
+ * delta[2e+1] += length(((B,C),(A,D))) - the same, over this context's columns.  The current
+ * arrangement is taken from what the two trees already hold for u (rows2, chg_low, chg_up).
+ * delta must be zero before the launch. */
 struct NniParams
 {
     const uint4 *pool;
@@ -72,8 +73,11 @@ struct NniParams
     int32_t ncols;
     int32_t n_edges;
     int32_t n_colblocks;
-    const uint4 *rows; /* [n_edges] */
-    long long *delta;  /* [2 * n_edges] */
+    const uint4 *rows;      /* [n_edges] A, B, C, D */
+    const uint2 *rows2;     /* [n_edges] low(u), up(u): the rows of u in the evaluated and in the scratch tree */
+    const int32_t *chg_low; /* [n_edges] cached counts of u in the evaluated tree = changes(A,B) over all columns */
+    const int32_t *chg_up;  /* [n_edges] the same in the scratch tree (left by the up-pass) = changes(C,D) */
+    long long *delta;       /* [2 * n_edges] */
 };
 cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t stream);
 

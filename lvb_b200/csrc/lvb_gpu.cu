@@ -1152,7 +1152,8 @@ extern "C"
             CU(cudaMalloc(&c->d_nni, c->cap_nni * sizeof(long long)));
             CU(cudaMallocHost(&c->h_nni, c->cap_nni * sizeof(long long)));
         }
-        const size_t bytes = (n_pcs + 1) * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr) + (size_t)E * sizeof(uint4);
+        const size_t bytes = (n_pcs + 1) * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr) +
+                             (size_t)E * (sizeof(uint4) + sizeof(uint2));
         int slot;
         if (acquire_slot(c, bytes, 1, &slot))
             return 1;
@@ -1160,6 +1161,7 @@ extern "C"
         FitchProgram *h_prog = reinterpret_cast<FitchProgram *>(st.h);
         FitchInstr *h_instr = reinterpret_cast<FitchInstr *>(h_prog + n_pcs + 1);
         uint4 *h_rows = reinterpret_cast<uint4 *>(h_instr + n_instr);
+        uint2 *h_rows2 = reinterpret_cast<uint2 *>(h_rows + E);
         /* up-pass: operands from `tree`, stores (and the per-node counts nobody reads) into scratch_tree;
          * pieces are in level order (the top piece first), the last record covers the whole program
          * for the finalize step */
@@ -1180,6 +1182,7 @@ extern "C"
             const int32_t sis = left[v] == u ? right[v] : left[v];
             const uint32_t up = v == root ? (uint32_t)root : (uint32_t)(v + (int64_t)scratch_tree * c->I);
             h_rows[e] = make_uint4(low_row(left[u]), low_row(right[u]), low_row(sis), up);
+            h_rows2[e] = make_uint2(low_row(u), (uint32_t)(u + (int64_t)scratch_tree * c->I));
         }
         CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
         c->tree_ready[scratch_tree] = 0; /* its rows now hold up sets, not an evaluated tree */
@@ -1235,6 +1238,9 @@ extern "C"
         q.n_edges = (int32_t)E;
         q.n_colblocks = n_cb;
         q.rows = d_rows;
+        q.rows2 = reinterpret_cast<const uint2 *>(d_rows + E);
+        q.chg_low = c->chg + (int64_t)tree * c->I;
+        q.chg_up = c->chg + (int64_t)scratch_tree * c->I;
         q.delta = c->d_nni;
         if ((int64_t)E * n_cb > (int64_t)INT32_MAX)
             return fail("lvb_gpu_nni_neighbourhood: %lld CTAs", (long long)E * n_cb);

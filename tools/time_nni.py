@@ -29,7 +29,7 @@ for _ in range(3):
     e.rerun_last_batch()
 e.synchronize()
 ms, k = e.kernel_time()
-rows = 4 * (n - 3)
+rows = 6 * (n - 3)  # A, B, C, D, low(u), up(u) per branch (operand rows; neighbouring branches share them through L2)
 print(json.dumps({
     "shape": [n, nwords * 16], "candidates": len(cands), "current_length": int(base), "best_delta": int(got.min() - base),
     "nni_call_ms": dt_call * 1e3, "nni_call_candidates_per_s": len(cands) / dt_call,
