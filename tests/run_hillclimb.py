@@ -4,7 +4,7 @@ printing one JSON line.
   --ref    the UNMODIFIED reference through oracle/_ref (the checker)
   --mock   the host layer with tests/mock_gpu.c answering lvb_gpu_* from the CPU oracle
   (none)   the host layer on the real library and a GPU
-usage: run_hillclimb.py [--ref|--mock] <npz:key> seed
+usage: run_hillclimb.py [--ref|--mock] <npz:key | synthetic:n:m:p> seed
 """
 import ctypes as C
 import hashlib
@@ -27,9 +27,18 @@ def main():
         args = args[1:]
     import numpy as np
 
-    name, key = args[0].split(":")
     seed = int(args[1])
-    rows = [bytes(r) for r in np.load(os.path.join(HERE, "golden", name))[key]]
+    if args[0].startswith("synthetic:"):  # synthetic:n:m:p — lvb_b200.synthetic alignment, generator seed 1
+        from lvb_b200 import synthetic
+
+        _, n_, m_, p_ = args[0].split(":")
+        rows = [bytes(r) for r in synthetic.text_rows(synthetic.states(int(n_), int(m_), 1, float(p_)))]
+    else:
+        name, key = args[0].split(":")
+        rows = [bytes(r) for r in np.load(os.path.join(HERE, "golden", name))[key]]
+    import time
+
+    t_start = time.perf_counter()
     with tempfile.TemporaryDirectory() as d:
         out = os.path.join(d, "outtree")
         if mode == "ref":
@@ -52,6 +61,7 @@ def main():
             msa.rinit(seed)
             t = msa.tree().random()
             doc = t.hillclimb(0, out)
+        doc["seconds"] = time.perf_counter() - t_start  # alignment set-up + start tree + hill climb + output
         doc["outtree_md5"] = hashlib.md5(open(out, "rb").read()).hexdigest()
     print(json.dumps(doc))
 

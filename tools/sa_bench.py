@@ -108,6 +108,29 @@ def budget_search(name: str, n: int, m: int, p: float, chains: int, budget: int,
     return res
 
 
+def hillclimb(name: str, n: int, m: int, p: float, seed: int, with_ref: bool) -> dict:
+    """deterministic_hillclimb (Solve.c:64-142) from the same random start tree: the host loop over
+    lvb_gpu_nni_neighbourhood against the reference's own function (oracle/_ref), each in a process of its own"""
+    res = dict(config=name, taxa=n, sites=m)
+    runner = os.path.join(ROOT, "tests", "run_hillclimb.py")
+    for key, flag in (("lvb_gpu", None), ("reference", "--ref")):
+        if flag and not (with_ref and oracles.have_ref()):
+            continue
+        cmd = [sys.executable, runner] + ([flag] if flag else []) + [f"synthetic:{n}:{m}:{p}", str(seed)]
+        t0 = time.time()
+        q = subprocess.run(cmd, capture_output=True, text=True, timeout=3000)
+        if q.returncode != 0:
+            res[key] = dict(rc=q.returncode, tail=(q.stdout + q.stderr)[-400:])
+            continue
+        res[key] = json.loads(q.stdout.strip().splitlines()[-1])
+        res[key]["wall_s"] = time.time() - t0
+    if "reference" in res and "seconds" in res.get("lvb_gpu", {}) and "seconds" in res["reference"]:
+        g, r = res["lvb_gpu"], res["reference"]
+        res["identical"] = all(g[k] == r[k] for k in ("length", "iterations", "trees", "outtree_md5"))
+        res["speedup"] = r["seconds"] / g["seconds"]
+    return res
+
+
 def main() -> None:
     out_path = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "sa_bench.json")
     which = sorted(set(sys.argv[2].split(","))) if len(sys.argv) > 2 else ["1", "2", "3", "5"]
@@ -137,6 +160,9 @@ def main() -> None:
         doc["results"].append(budget_search("config3 synthetic 500x100000, 1 chain", 500, 100000, 0.02, 1, 20000, 100, nproc))
     if "5" in which:
         doc["results"].append(budget_search("config5 synthetic 1000x200000, 64 chains on one GPU", 1000, 200000, 0.02, 64, 3000, 40, nproc))
+    if "h" in which:
+        doc["results"].append(hillclimb("hillclimb synthetic 200x20000", 200, 20000, 0.05, 3, True))
+        doc["results"].append(hillclimb("hillclimb synthetic 500x100000 (config 3 shape)", 500, 100000, 0.02, 3, False))
     json.dump(doc, open(out_path, "w"), indent=1)
     for r in doc["results"]:
         print(json.dumps(r))
