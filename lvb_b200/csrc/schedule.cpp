@@ -13,8 +13,8 @@ static inline int64_t strided(const int64_t *base, int64_t stride_bytes, int64_t
 
 ScheduleCompiler::ScheduleCompiler(int64_t n)
     : n_(n), B_(2 * n - 3), cur_(0), stamp_(B_ > 0 ? B_ : 0, 0), child_(stamp_.size(), 0), seen_(stamp_.size(), 0),
-      cut_(stamp_.size(), 0), need_(stamp_.size(), 0), size_(stamp_.size(), 0), level_(stamp_.size(), 0),
-      mod_(stamp_.size(), 0), mod_at_(stamp_.size(), 0)
+      cut_(stamp_.size(), 0), mod_(stamp_.size(), 0), mod_at_(stamp_.size(), 0), need_(stamp_.size(), 0),
+      size_(stamp_.size(), 0), level_(stamp_.size(), 0)
 {
 }
 

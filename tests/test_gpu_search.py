@@ -124,3 +124,16 @@ def test_matchange_on_the_device(monkeypatch):
     got = H.run_cli(H.example_input(), ["-s", "12345", "-a", "1"], mock=False)
     H.check_against(got, want, "example a=1, matchange on the device")
     assert "In total, 16 columns are excluded" in got["stdout"]
+
+
+@pytest.mark.parametrize("env", [{"LVB_GPU_INLINE": "0"}, {"LVB_GPU_FUSE": "0", "LVB_GPU_DEEP": "0"},
+                                 {"LVB_GPU_INLINE": "0", "LVB_GPU_FUSE": "0", "LVB_GPU_DEEP": "0"}])
+def test_staged_and_unfused_kernel_routes(monkeypatch, env):
+    """small batches normally ride in the kernel parameters, finalize inside the Fitch kernel and use
+    the deep pipeline; with the switches off the same search goes through the staged copy, the
+    separate finalize launch and the 3-deep / 1-deep kernels — same trajectory either way"""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    want = CLI_RUNS["test_treelength_6_thread_2"]
+    got = H.run_cli(H.cli_input("test_treelength_6_thread_2"), want["flags"], mock=False)
+    H.check_against(got, want, str(env))
