@@ -503,6 +503,8 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
     const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
+    /* store programs may read one tree and write another (up-pass), see fitch_exec_body */
+    const unsigned src_off = (STORE && prog.src_tree1 > 0) ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
     const FitchInstr *gi = instrs + prog.instr_begin;
     const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
     const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
@@ -548,14 +550,14 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
                     a = 0;
                 }
                 else if (a >= p.n)
-                    a += tree_off;
+                    a = a >= p.n + p.n_internal ? a - p.n_internal + (int)tree_off : a + (int)src_off;
                 if (b < 0)
                 {
                     w |= D_BSLOT;
                     b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
                 }
                 else if (b >= p.n)
-                    b += tree_off;
+                    b = b >= p.n + p.n_internal ? b - p.n_internal + (int)tree_off : b + (int)src_off;
                 d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
             }
             s_instr[i] = d;
@@ -619,6 +621,8 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
 #undef LVB_ISSUE
     }
 
+    if (STORE && !p.fused_finalize)
+        return; /* the finalize launch follows */
     if (STORE)
     { /* the column block that finishes last folds the counts and publishes the length */
         __shared__ unsigned s_last;
@@ -746,7 +750,7 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
     const bool deep = deep_enabled() && small_grid(grid);
     cudaError_t e;
-    if (per_node && p.fused_finalize && !p.dep && deep)
+    if (per_node && !p.dep && deep)
     {
         const size_t sm = pipe_smem_bytes(true, LVB_PF_DEEP, p.n_slots, block);
         if ((e = want_smem(fitch_pipe_kernel<true>, sm)) != cudaSuccess)
@@ -816,19 +820,22 @@ static cudaError_t launch_inline_t(const ExecParams &p, bool per_node, int block
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
     const bool deep = deep_enabled();
     cudaError_t e;
-    if (per_node && p.fused_finalize && deep)
+    if (per_node)
     {
-        const size_t sm = pipe_smem_bytes(true, LVB_PF_DEEP, p.n_slots, block);
-        if ((e = want_smem(fitch_pipe_kernel_inl<true, NP, NI>, sm)) != cudaSuccess)
-            return e;
-        fitch_pipe_kernel_inl<true, NP, NI><<<grid, block, sm, stream>>>(p, tb);
-    }
-    else if (per_node)
-    {
-        const size_t smem = exec_smem_bytes(true, p.n_slots, block);
-        if ((e = want_smem(fitch_exec_kernel_inl<true, NP, NI>, smem)) != cudaSuccess)
-            return e;
-        fitch_exec_kernel_inl<true, NP, NI><<<grid, block, smem, stream>>>(p, tb);
+        if (deep)
+        {
+            const size_t sm = pipe_smem_bytes(true, LVB_PF_DEEP, p.n_slots, block);
+            if ((e = want_smem(fitch_pipe_kernel_inl<true, NP, NI>, sm)) != cudaSuccess)
+                return e;
+            fitch_pipe_kernel_inl<true, NP, NI><<<grid, block, sm, stream>>>(p, tb);
+        }
+        else
+        {
+            const size_t smem = exec_smem_bytes(true, p.n_slots, block);
+            if ((e = want_smem(fitch_exec_kernel_inl<true, NP, NI>, smem)) != cudaSuccess)
+                return e;
+            fitch_exec_kernel_inl<true, NP, NI><<<grid, block, smem, stream>>>(p, tb);
+        }
         if ((e = cudaGetLastError()) != cudaSuccess)
             return e;
         if (!p.fused_finalize)

@@ -14,7 +14,8 @@ static inline int64_t strided(const int64_t *base, int64_t stride_bytes, int64_t
 ScheduleCompiler::ScheduleCompiler(int64_t n)
     : n_(n), B_(2 * n - 3), cur_(0), stamp_(B_ > 0 ? B_ : 0, 0), child_(stamp_.size(), 0), seen_(stamp_.size(), 0),
       cut_(stamp_.size(), 0), mod_(stamp_.size(), 0), mod_at_(stamp_.size(), 0), need_(stamp_.size(), 0),
-      size_(stamp_.size(), 0), level_(stamp_.size(), 0)
+      size_(stamp_.size(), 0), level_(stamp_.size(), 0), start_(stamp_.size(), 0), depth_(stamp_.size(), 0),
+      push_(stamp_.size(), 0)
 {
 }
 
@@ -178,90 +179,33 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
             cut_[v] = cur_;
     }
 
-    /* emission */
+    /* emission.  A piece is the post-order of its nodes: a node comes right after the subtrees of
+     * its dirty children, the child that needs more stack slots first (its result is parked in a
+     * slot while the other is evaluated).  So the place of every instruction follows from the
+     * subtree sizes, and the stream is written in ONE top-down sweep over the discovery order —
+     * no recursion, no explicit stack:
+     *   start(v) = first index of v's subtree, its own instruction sits at start(v) + size(v) - 1;
+     *   depth(v) = slots in use while v's subtree is evaluated. */
     const uint32_t node_ctl = store ? LVB_CTL_STORE : 0u;
-    int depth = 0, peak = 0;
-    auto emit_from = [&](int32_t top) {
-        /* v == -1 is the root step's first application: fitch(root.left, root.right), never stored */
-        frames_.clear();
-        frames_.push_back(Frame{top, -1, -1, 0});
-        while (!frames_.empty())
-        {
-            Frame &f = frames_.back();
-            const int32_t v = f.v;
-            const int64_t l = (v < 0) ? rl : L(v), r = (v < 0) ? rr : R(v);
-            const uint32_t ctl = (v < 0) ? 0u : node_ctl;
-            switch (f.stage)
-            {
-            case 0: {
-                const bool dl = inside(l), dr = inside(r);
-                if (dl && dr)
-                {
-                    const bool left_first = need_[l] >= need_[r];
-                    f.first = (int32_t)(left_first ? l : r);
-                    f.second = (int32_t)(left_first ? r : l);
-                    f.stage = 1;
-                    const int32_t c = f.first;
-                    frames_.push_back(Frame{c, -1, -1, 0});
-                }
-                else if (dl || dr)
-                {
-                    f.first = (int32_t)(dl ? l : r);
-                    f.stage = 3;
-                    const int32_t c = f.first;
-                    frames_.push_back(Frame{c, -1, -1, 0});
-                }
-                else
-                {
-                    out.push_back(FitchInstr{(int32_t)l, (int32_t)r, v, ctl});
-                    frames_.pop_back();
-                }
-                break;
-            }
-            case 1: { /* first child is in PREV: park it in a slot, then do the second */
-                out.back().ctl |= (uint32_t)(depth + 1) << LVB_CTL_PUSH_SHIFT;
-                depth++;
-                peak = std::max(peak, depth);
-                f.stage = 2;
-                const int32_t c = f.second;
-                frames_.push_back(Frame{c, -1, -1, 0});
-                break;
-            }
-            case 2: /* second child is in PREV, first in the top slot */
-                depth--;
-                out.push_back(FitchInstr{LVB_OPER_SLOT(depth), LVB_OPER_PREV, v, ctl});
-                frames_.pop_back();
-                break;
-            default: { /* 3: the one dirty child is in PREV, the other child is a clean row */
-                const int64_t other = (f.first == l) ? r : l;
-                out.push_back(FitchInstr{LVB_OPER_PREV, (int32_t)other, v, ctl});
-                frames_.pop_back();
-                break;
-            }
-            }
-        }
-    };
-    auto close_piece = [&](size_t begin, int level) {
-        if (pieces && out.size() > begin)
-            pieces->push_back(Piece{(int32_t)begin, (int32_t)(out.size() - begin), level});
-    };
-    /* pieces cut off below: each is a complete post-order program of its own */
-    int top_level = 0;
+    int peak = 0;
+    size_t cursor = out.size();
     if (piece_size > 0)
-    {
+    { /* pieces cut off below: each is a complete post-order program of its own */
         for (size_t k = order_.size(); k-- > 0;)
         {
             const int32_t v = order_[k];
             if (cut_[v] != cur_)
                 continue;
-            const size_t begin = out.size();
-            cut_[v] = 0; /* inside its own piece the root is an ordinary node */
-            emit_from(v);
-            cut_[v] = cur_;
-            close_piece(begin, level_[v]);
+            start_[v] = (int32_t)cursor;
+            depth_[v] = 0;
+            push_[v] = 0;
+            if (pieces)
+                pieces->push_back(Piece{(int32_t)cursor, size_[v], level_[v]});
+            cursor += (size_t)size_[v];
         }
     }
-    const size_t last_begin = out.size();
+    const size_t last_begin = cursor;
+    int top_level = 0;
     auto level_above = [&](int64_t v) {
         if (is_dirty(v))
             top_level = std::max(top_level, level_[v] + (cut_[v] == cur_ ? 1 : 0));
@@ -274,14 +218,58 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
         {
             level_above(v);
             if (cut_[v] != cur_)
-                emit_from(v);
+            {
+                start_[v] = (int32_t)cursor;
+                depth_[v] = 0;
+                push_[v] = 0;
+                cursor += (size_t)size_[v];
+            }
         }
-    /* root step, TreeEvaluation.c:238-264 */
+    /* root step, TreeEvaluation.c:238-264: fitch(root.left, root.right), never stored, then the
+     * count against the root's own row */
     level_above(rl);
     level_above(rr);
-    emit_from(-1);
-    out.push_back(FitchInstr{LVB_OPER_PREV, (int32_t)root, -1, LVB_CTL_COUNT_ONLY});
-    close_piece(last_begin, top_level);
+    const size_t root_start = cursor;
+    cursor += 1 + (size_t)(inside(rl) ? size_[rl] : 0) + (size_t)(inside(rr) ? size_[rr] : 0);
+    const size_t root_pos = cursor - 1;
+    cursor++; /* the count-only instruction */
+    out.resize(cursor);
+
+    /* one node: place the dirty children, write the node's own instruction at `pos` */
+    auto place = [&](int64_t l, int64_t r, int32_t node, uint32_t ctl, size_t start, int depth, size_t pos, uint32_t push) {
+        const bool dl = inside(l), dr = inside(r);
+        const uint32_t pushbits = push << LVB_CTL_PUSH_SHIFT;
+        if (dl && dr)
+        {
+            const bool left_first = need_[l] >= need_[r];
+            const int64_t first = left_first ? l : r, second = left_first ? r : l;
+            start_[first] = (int32_t)start;
+            depth_[first] = depth;
+            push_[first] = depth + 1; /* its result waits in slot `depth` */
+            start_[second] = (int32_t)(start + (size_t)size_[first]);
+            depth_[second] = depth + 1;
+            push_[second] = 0;
+            peak = std::max(peak, depth + 1);
+            out[pos] = FitchInstr{LVB_OPER_SLOT(depth), LVB_OPER_PREV, node, ctl | pushbits};
+        }
+        else if (dl || dr)
+        {
+            const int64_t c = dl ? l : r, other = dl ? r : l;
+            start_[c] = (int32_t)start;
+            depth_[c] = depth;
+            push_[c] = 0;
+            out[pos] = FitchInstr{LVB_OPER_PREV, (int32_t)other, node, ctl | pushbits};
+        }
+        else
+            out[pos] = FitchInstr{(int32_t)l, (int32_t)r, node, ctl | pushbits};
+    };
+    place(rl, rr, -1, 0u, root_start, 0, root_pos, 0u);
+    out[root_pos + 1] = FitchInstr{LVB_OPER_PREV, (int32_t)root, -1, LVB_CTL_COUNT_ONLY};
+    for (int32_t v : order_) /* parents before children: start/depth/push of v are set by now */
+        place(L(v), R(v), v, node_ctl, (size_t)start_[v], depth_[v], (size_t)start_[v] + (size_t)size_[v] - 1,
+              (uint32_t)push_[v]);
+    if (pieces && cursor > last_begin)
+        pieces->push_back(Piece{(int32_t)last_begin, (int32_t)(cursor - last_begin), top_level});
 
     if (peak > LVB_MAX_SLOTS)
     {

@@ -82,6 +82,9 @@ class ScheduleCompiler
     std::vector<int32_t> need_;     /* stack need per dirty node */
     std::vector<int32_t> size_;     /* nodes of the piece hanging under a dirty node */
     std::vector<int32_t> level_;    /* level of the piece a dirty node belongs to */
+    std::vector<int32_t> start_;    /* emission: index of the first instruction of a node's subtree */
+    std::vector<int32_t> depth_;    /* emission: stack slots in use while the subtree is evaluated */
+    std::vector<int32_t> push_;     /* emission: 1 + slot the node's result is parked in, 0 = none */
     std::vector<int32_t> order_;    /* scratch: discovery order */
     std::vector<int32_t> dirty_;    /* scratch: de-duplicated dirty list */
     std::vector<Frame> frames_;
