@@ -1,10 +1,10 @@
-"""dev tool: time the full-pass commit on the 2000 x 1M shape for several settings"""
+"""dev tool: time the full-pass commit (default 2000 x 1M; or `n nwords`, e.g. 2000 7813 = one of 8 site blocks) for several settings"""
 import os, sys, time
 sys.path.insert(0, '.'); sys.path.insert(0, 'tests')
 import numpy as np
 from lvb_b200 import Engine, Topology, synthetic
 
-n, nwords = 2000, 62500
+n, nwords = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (2000, 62500)
 enc = synthetic.random_packed(n, nwords, 1)
 l, r, root = synthetic.random_topology(n, 3)
 want = None
