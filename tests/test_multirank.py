@@ -69,6 +69,7 @@ def _mock_api():
     L.lvb_gpu_tree_commit.argtypes = [vp, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     L.lvb_gpu_score_batch.argtypes = [vp, i64, C.POINTER(C.c_int), C.POINTER(_Topo), C.POINTER(i64)]
     L.lvb_gpu_tree_changes.argtypes = [vp, C.c_int, vp]
+    L.lvb_gpu_nni_neighbourhood.argtypes = [vp, C.c_int, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     L.lvb_gpu_shutdown.argtypes = [vp]
     return L
 
@@ -87,7 +88,7 @@ def _siteblock_worker(rank: int, world: int, port: int, out_path: str) -> None:
         ctx = C.c_void_p()
         assert L.lvb_gpu_init(0, C.byref(ctx)) == 0
         w0, wc = sharding.word_block(nwords, rank, world)
-        assert L.lvb_gpu_matrix_upload_flat(ctx, n, nwords, enc.ctypes.data, w0, wc, 1) == 0, L.lvb_gpu_last_error()
+        assert L.lvb_gpu_matrix_upload_flat(ctx, n, nwords, enc.ctypes.data, w0, wc, 2) == 0, L.lvb_gpu_last_error()
         t = C.c_int(-1)
         assert L.lvb_gpu_tree_create(ctx, C.byref(t)) == 0
         full = Topology(g["random_left"], g["random_right"], int(g["random_root"]))
@@ -113,10 +114,17 @@ def _siteblock_worker(rank: int, world: int, port: int, out_path: str) -> None:
         assert L.lvb_gpu_score_batch(ctx, 2, trees, arr, out) == 0, L.lvb_gpu_last_error()
         sc = torch.tensor(list(out), dtype=torch.int64)
         dist.all_reduce(sc)
+        # the exhaustive NNI neighbourhood on the blocks: 2(n-3) partial lengths, summed over the ranks
+        s2 = C.c_int(-1)
+        assert L.lvb_gpu_tree_create(ctx, C.byref(s2)) == 0
+        nn = (C.c_int64 * (2 * (n - 3)))()
+        assert L.lvb_gpu_nni_neighbourhood(ctx, t.value, s2.value, C.byref(ts), nn) == 0, L.lvb_gpu_last_error()
+        nn_t = torch.tensor(list(nn), dtype=torch.int64)
+        dist.all_reduce(nn_t)
         L.lvb_gpu_shutdown(ctx)
         if rank == 0:
             json.dump({"block": [w0, wc], "partial": int(part.value), "length": int(lens[0]), "scores": sc.tolist(),
-                       "changes": chg_t.tolist()}, open(out_path, "w"))
+                       "changes": chg_t.tolist(), "neighbourhood": nn_t.tolist()}, open(out_path, "w"))
     finally:
         dist.destroy_process_group()
 
@@ -136,6 +144,15 @@ def test_site_blocks_two_ranks_gloo(tmp_path):
     assert got["scores"] == [11834, 11808]
     # per-node counts: every node's changes are the sum over blocks; only the root step is not cached
     assert got["changes"][g["enc"].shape[0]:] == [int(x) for x in chg[g["enc"].shape[0]:]]
+    # neighbourhood lengths over blocks add up to whole-alignment lengths (sample against the oracle)
+    from test_schedule import _nni_candidates
+
+    n = g["enc"].shape[0]
+    cands = list(_nni_candidates(g["random_left"], g["random_right"], int(g["random_root"]), n))
+    assert len(got["neighbourhood"]) == len(cands) == 2 * (n - 3)
+    for k in range(0, len(cands), 23):
+        u, v, a, b, c, l2, r2 = cands[k]
+        assert got["neighbourhood"][k] == oracles.oracle_getplen(g["enc"], l2, r2, int(g["random_root"]))[0], k
 
 
 def _replicate_worker(rank: int, world: int, port: int, out_path: str, seed: int, reps: int) -> None:
