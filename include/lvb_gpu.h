@@ -77,6 +77,11 @@ int lvb_gpu_matrix_upload_flat(lvb_gpu_ctx *ctx, int64_t n, int64_t nwords, cons
 int lvb_gpu_matrix_pack(lvb_gpu_ctx *ctx, int64_t n, int64_t m, const char *const *rows,
                         int64_t word_begin, int64_t word_count, int64_t max_trees);
 
+/* the alignment of another context (same or another GPU of this process), copied device to
+ * device: how the additional driver contexts of a many-chain run get their leaf rows without a
+ * second DNAToBinary + upload.  Same word block as `src`. */
+int lvb_gpu_matrix_clone(lvb_gpu_ctx *ctx, lvb_gpu_ctx *src, int64_t max_trees);
+
 /* ---- column scans of the text alignment, before it is packed: constchar
  * (DataOperations.c:272-307; matchange, :309-349, cuts the columns where keep[k] == 0) and
  * MinimumTreeLength (:53-105, literal-character semantics: ambiguity letters count as states of
@@ -129,6 +134,24 @@ int lvb_gpu_score_batch_submit(lvb_gpu_ctx *ctx, int64_t n_cand, const int *tree
                                int *ticket);
 int lvb_gpu_batch_wait(lvb_gpu_ctx *ctx, int ticket, int64_t *lengths);
 
+/* The same two calls for a caller that compiles the programs itself, on ITS threads: a driver of
+ * many SA chains generates a chain's proposals and compiles them (lvb_gpu_compile_schedule, which
+ * is thread-safe and keeps one compiler per calling thread) in the same parallel loop, so that the
+ * batch call only lays the batch out and launches it.  pre[k] is the program of topos[k] exactly as
+ * lvb_gpu_compile_schedule(n, &topos[k], store, ...) returned it (store = 1 for commit, 0 for
+ * score); pre[k].instr == NULL: compile topos[k] here, as the plain calls do (a first evaluation
+ * with n_dirty < 0 must take this route: it is cut into pieces). */
+typedef struct lvb_gpu_program_view
+{
+    const int32_t *instr; /* n_instr x {a, b, node, ctl} */
+    int64_t n_instr;
+    int64_t n_slots;
+} lvb_gpu_program_view;
+int lvb_gpu_commit_batch_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                             const lvb_gpu_program_view *pre, int64_t *lengths);
+int lvb_gpu_score_batch_submit_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                   const lvb_gpu_program_view *pre, int *ticket);
+
 /* ---- the exhaustive NNI neighbourhood of one evaluated tree, in one call: what the loop of
  * deterministic_hillclimb (Solve.c:100-111) computes with 2(n-3) x (mutate_deterministic,
  * TreeOperations.c:105-158, + getplen).  lengths[2*(u-n) + j] is the length getplen would return
@@ -179,8 +202,9 @@ int lvb_gpu_rerun_last_batch(lvb_gpu_ctx *ctx, int64_t *lengths);
 int lvb_gpu_synchronize(lvb_gpu_ctx *ctx);
 /* Host-only: compile `topo` into the instruction stream the kernels execute, without a device.
  * instr receives up to cap 16-byte instructions {a, b, node, ctl}; returns the count in *n_instr
- * and the number of on-chip stack slots in *n_slots.
- * Used by the CPU tests of the schedule compiler. */
+ * and the number of on-chip stack slots in *n_slots (at most n_dirty + 2 instructions).
+ * Thread-safe; used by callers that compile on their own threads (the *_pre calls) and by the CPU
+ * tests of the schedule compiler. */
 int lvb_gpu_compile_schedule(int64_t n, const lvb_gpu_topology *topo, int store, int32_t *instr, int64_t cap,
                              int64_t *n_instr, int64_t *n_slots);
 

@@ -734,7 +734,14 @@ static bool deep_enabled()
     }();
     return on != 0;
 }
-static bool small_grid(unsigned grid) { return grid <= 148u * 4u; }
+static bool small_grid(unsigned grid)
+{
+    static const unsigned limit = [] {
+        const char *e = getenv("LVB_GPU_SMALL_GRID"); /* CTAs up to which a launch counts as latency-bound */
+        return (e && atoi(e) > 0) ? (unsigned)atoi(e) : 148u * 4u;
+    }();
+    return grid <= limit;
+}
 
 template <class K>
 static cudaError_t want_smem(K kernel, size_t smem)

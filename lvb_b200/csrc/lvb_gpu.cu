@@ -425,7 +425,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
 
 /* compile + launch one batch; store: commit semantics, else score semantics */
 static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_topology *topos, bool store,
-                     int64_t *lengths, int *ticket = nullptr)
+                     int64_t *lengths, int *ticket = nullptr, const lvb_gpu_program_view *pre = nullptr)
 {
     if (!c->pool)
         return fail("no alignment on the device: call lvb_gpu_matrix_upload first");
@@ -470,11 +470,29 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
 #ifdef _OPENMP
     /* always the caller's whole team: libgomp re-creates threads when consecutive parallel regions
      * of one thread differ in size (measured: 3x slower rounds with teams alternating 8 / 16) */
-    if (K >= c->compile_par_min)
+    int64_t to_compile = K;
+    if (pre)
+        for (int64_t k = 0; k < K; k++)
+            to_compile -= pre[k].instr ? 1 : 0;
+    if (to_compile >= c->compile_par_min)
         nthreads = std::min<int>((int)c->sc.size(), omp_get_max_threads());
 #endif
     bool bad = false;
     auto compile_one = [&](int64_t k, ScheduleCompiler *sc) {
+        if (pre && pre[k].instr)
+        { /* compiled by the caller (lvb_gpu_compile_schedule on one of its threads): one piece */
+            const FitchInstr *src = reinterpret_cast<const FitchInstr *>(pre[k].instr);
+            c->c_instr[k].assign(src, src + pre[k].n_instr);
+            c->c_pieces[k].assign(1, ScheduleCompiler::Piece{0, (int32_t)pre[k].n_instr, 0});
+            c->c_err[k].clear();
+            c->c_slots[k] = (int)pre[k].n_slots;
+            if (pre[k].n_instr < 2 || pre[k].n_slots < 0 || pre[k].n_slots > LVB_MAX_SLOTS)
+            {
+                c->c_err[k] = "malformed precompiled program";
+                bad = true;
+            }
+            return;
+        }
         int piece_size = 0;
         if (want_pieces > 1)
         {
@@ -936,6 +954,27 @@ extern "C"
         if (!rc && bad)
             rc = fail("bad base symbol in data MSA: %c (cannot read data MSA)", (char)(bad - 1));
         return rc;
+    }
+
+    int lvb_gpu_matrix_clone(lvb_gpu_ctx *c, lvb_gpu_ctx *src, int64_t max_trees)
+    {
+        if (!c || !src || c == src)
+            return fail("lvb_gpu_matrix_clone: bad argument");
+        if (!src->pool)
+            return fail("lvb_gpu_matrix_clone: the source context holds no alignment");
+        if (alloc_matrix(c, src->n, src->nwords, src->word_begin, src->word_count, max_trees))
+            return 1;
+        /* leaf rows device to device (peer copy when the contexts sit on different GPUs) */
+        CU(cudaSetDevice(src->device));
+        CU(cudaStreamSynchronize(src->stream));
+        CU(cudaSetDevice(c->device));
+        const size_t bytes = (size_t)src->n * (size_t)src->stride_u4 * sizeof(uint4);
+        if (c->device == src->device)
+            CU(cudaMemcpyAsync(c->pool, src->pool, bytes, cudaMemcpyDeviceToDevice, c->stream));
+        else
+            CU(cudaMemcpyPeerAsync(c->pool, c->device, src->pool, src->device, bytes, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        return 0;
     }
 
     int lvb_gpu_column_stats(lvb_gpu_ctx *c, int64_t n, int64_t m, const char *const *rows, unsigned char *keep,
@@ -1462,11 +1501,18 @@ extern "C"
             return fail("lvb_gpu_compile_schedule: null argument");
         if (n < 3)
             return fail("lvb_gpu_compile_schedule: n too small");
-        ScheduleCompiler sc(n);
-        std::vector<FitchInstr> out;
+        /* one compiler per calling thread, kept between calls: O(dirty nodes) per call, no allocation */
+        static thread_local ScheduleCompiler *sc = nullptr;
+        static thread_local std::vector<FitchInstr> out;
+        if (!sc || sc->n() != n)
+        {
+            delete sc;
+            sc = new ScheduleCompiler(n);
+        }
+        out.clear();
         int slots = 0;
         std::string err;
-        if (!sc.compile(*topo, store != 0, out, slots, err))
+        if (!sc->compile(*topo, store != 0, out, slots, err))
             return fail("%s", err.c_str());
         *n_instr = (int64_t)out.size();
         *n_slots = slots;
@@ -1477,6 +1523,24 @@ extern "C"
             memcpy(instr, out.data(), out.size() * sizeof(FitchInstr));
         }
         return 0;
+    }
+
+    int lvb_gpu_commit_batch_pre(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                 const lvb_gpu_program_view *pre, int64_t *lengths)
+    {
+        if (!c || !trees || !topos || !pre)
+            return fail("lvb_gpu_commit_batch_pre: null argument");
+        return run_batch(c, n_cand, trees, topos, true, lengths, nullptr, pre);
+    }
+
+    int lvb_gpu_score_batch_submit_pre(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                       const lvb_gpu_program_view *pre, int *ticket)
+    {
+        if (!c || !trees || !topos || !pre || !ticket)
+            return fail("lvb_gpu_score_batch_submit_pre: null argument");
+        if (n_cand <= 0)
+            return fail("lvb_gpu_score_batch_submit_pre: empty batch");
+        return run_batch(c, n_cand, trees, topos, false, nullptr, ticket, pre);
     }
 
     int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,

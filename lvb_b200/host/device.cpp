@@ -65,6 +65,16 @@ void matchange_device(Dataptr MSA, const Parameters &rc, int device_index)
     matchange_apply(MSA, rc, keep.data(), (long)kept, (long)min_kept);
 }
 
+/* a further context on device_index with the alignment copied from `src` device to device */
+void device_open_clone(Device &dev, int device_index, const Device &src, int max_trees)
+{
+    dev.MSA = src.MSA;
+    dev.index = device_index;
+    dev.word_count = src.word_count;
+    gpu_check(lvb_gpu_init(device_index, &dev.ctx));
+    gpu_check(lvb_gpu_matrix_clone(dev.ctx, src.ctx, max_trees));
+}
+
 void device_close(Device &dev)
 {
     if (dev.ctx)

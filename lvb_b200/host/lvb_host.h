@@ -226,6 +226,7 @@ void device_open(Device &dev, int device_index, Dataptr MSA, int max_trees, int6
                  int64_t word_count = -1);
 void device_open_encoded(Device &dev, int device_index, Dataptr MSA, Lvb_bit_length *const *rows, int max_trees,
                          int64_t word_begin = 0, int64_t word_count = -1);
+void device_open_clone(Device &dev, int device_index, const Device &src, int max_trees);
 void device_close(Device &dev);
 
 /* ---- getplen: src/TreeEvaluation.c:49-270, same signature (the scratch pointers are

@@ -141,6 +141,15 @@ struct Chain
         TrajectoryRow row; /* log line if rejected (length filled in at replay) */
     };
     std::vector<Proposal> cand;
+    /* programs compiled on the thread that generated the proposals (lvb_gpu_compile_schedule) */
+    struct Compiled
+    {
+        std::vector<int32_t> instr;
+        int64_t n_instr = 0, n_slots = 0;
+        bool valid = false;
+    };
+    std::vector<Compiled> cprog; /* one per speculative proposal */
+    Compiled ccommit;            /* the pending commit request, if it is not a whole-tree one */
     ProposalScratch scratch;
     std::vector<Spec> spec;
     int n_spec = 0;
@@ -161,11 +170,57 @@ struct Chain
         k_now = prm.speculation > 0 ? kmax : 1;
         cur = treealloc(MSA, true);
         cand.resize((size_t)kmax);
+        cprog.resize((size_t)kmax);
         spec.resize((size_t)kmax);
         S.rng.rinit(rc.seed + chain_id); /* Main.c:104 */
         tree_minimum_length = (double)MSA->min_len_tree;
         log_eps = log_wrapper(LVB_EPS);
         log_grad_geom = log_wrapper(0.99);
+    }
+
+    /* the current tree with the links proposal pr rewired (pr == nullptr: the commit request) */
+    lvb_gpu_topology topology_of(const Proposal *pr) const
+    {
+        lvb_gpu_topology tp = lvb_gpu_topology();
+        tp.left = &cur[0].left;
+        tp.right = &cur[0].right;
+        tp.stride_bytes = (int64_t)sizeof(TREESTACK_TREE_NODES);
+        tp.root = root;
+        if (pr)
+        {
+            tp.dirty = pr->dirty.data();
+            tp.n_dirty = (int64_t)pr->dirty.size();
+            tp.mod_node = pr->mod_node.data();
+            tp.mod_left = pr->mod_left.data();
+            tp.mod_right = pr->mod_right.data();
+            tp.n_mod = (int64_t)pr->mod_node.size();
+        }
+        else
+        {
+            tp.dirty = commit.dirty.data();
+            tp.n_dirty = commit.all ? -1 : (int64_t)commit.dirty.size();
+        }
+        return tp;
+    }
+
+    void compile_into(Compiled &dst, const lvb_gpu_topology &tp, bool store)
+    {
+        const size_t cap = (size_t)tp.n_dirty + 2; /* one instruction per dirty node + the root step */
+        if (dst.instr.size() < 4 * cap)
+            dst.instr.resize(4 * cap);
+        if (lvb_gpu_compile_schedule(MSA->n, &tp, store ? 1 : 0, dst.instr.data(), (int64_t)cap, &dst.n_instr, &dst.n_slots) != 0)
+            crash("GPU error: %s", lvb_gpu_last_error());
+        dst.valid = true;
+    }
+
+    /* end of advance(): the programs of this round, compiled on the thread that owns the chain */
+    void compile_round()
+    {
+        ccommit.valid = false;
+        if (commit.used && !commit.all)
+            compile_into(ccommit, topology_of(nullptr), true);
+        for (int k = 0; k < n_spec; k++)
+            compile_into(cprog[(size_t)k], topology_of(&cand[(size_t)k]), false);
     }
 
     template <class It>
@@ -403,6 +458,7 @@ struct Chain
     void advance()
     {
         n_spec = 0;
+        ccommit.valid = false;
         if (S.phase == PH_DONE)
             return;
         if (S.phase == PH_ST_BEGIN)
@@ -517,6 +573,7 @@ struct Chain
         }
         spec_end = W;
         res.getplen_calls += n_spec;
+        compile_round();
     }
 
     /* ---- one round, second half: lengths are known ---- */
@@ -632,11 +689,10 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
         int ticket = -1;
         std::vector<int> trees, owner;
         std::vector<lvb_gpu_topology> topos;
+        std::vector<lvb_gpu_program_view> pre;
         std::vector<int64_t> lens, clen;
         std::vector<size_t> offsets;
     };
-    const size_t stride = sizeof(TREESTACK_TREE_NODES);
-    (void)MSA;
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto since = [](std::chrono::steady_clock::time_point a) {
         return std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
@@ -688,6 +744,7 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
             /* what the device trees must catch up with (at most one request per chain), one launch */
             h.trees.clear();
             h.topos.clear();
+            h.pre.clear();
             h.owner.clear();
             bool want = false;
             for (int r = h.a; r < h.b; r++)
@@ -695,23 +752,19 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
                 Chain &c = chains[(size_t)r];
                 if (!c.commit.used)
                     continue;
-                lvb_gpu_topology tp = lvb_gpu_topology();
-                tp.left = &c.cur[0].left;
-                tp.right = &c.cur[0].right;
-                tp.stride_bytes = (int64_t)stride;
-                tp.root = c.root;
-                tp.dirty = c.commit.dirty.data();
-                tp.n_dirty = c.commit.all ? -1 : (int64_t)c.commit.dirty.size();
                 h.trees.push_back(c.dev_tree);
-                h.topos.push_back(tp);
+                h.topos.push_back(c.topology_of(nullptr));
+                /* compiled in advance() unless it is a whole-tree evaluation (cut into pieces by the library) */
+                h.pre.push_back(c.ccommit.valid ? lvb_gpu_program_view{c.ccommit.instr.data(), c.ccommit.n_instr, c.ccommit.n_slots}
+                                                : lvb_gpu_program_view{nullptr, 0, 0});
                 h.owner.push_back(r);
                 want = want || c.commit.want_length;
             }
             if (!h.trees.empty())
             {
                 h.lens.resize(h.trees.size());
-                gpu_check(lvb_gpu_commit_batch(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
-                                               want ? h.lens.data() : nullptr));
+                gpu_check(lvb_gpu_commit_batch_pre(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
+                                                   h.pre.data(), want ? h.lens.data() : nullptr));
                 for (size_t i = 0; i < h.owner.size(); i++)
                 {
                     Chain &c = chains[(size_t)h.owner[i]];
@@ -728,6 +781,7 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
             /* proposals of all chains of the half in one launch */
             h.trees.clear();
             h.topos.clear();
+            h.pre.clear();
             h.offsets.resize((size_t)(h.b - h.a));
             for (int r = h.a; r < h.b; r++)
             {
@@ -735,27 +789,17 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
                 h.offsets[(size_t)(r - h.a)] = h.trees.size();
                 for (int k = 0; k < c.n_spec; k++)
                 {
-                    const Proposal &pr = c.cand[(size_t)k];
-                    lvb_gpu_topology tp = lvb_gpu_topology();
-                    tp.left = &c.cur[0].left; /* the current tree ... */
-                    tp.right = &c.cur[0].right;
-                    tp.stride_bytes = (int64_t)stride;
-                    tp.root = c.root;
-                    tp.dirty = pr.dirty.data();
-                    tp.n_dirty = (int64_t)pr.dirty.size();
-                    tp.mod_node = pr.mod_node.data(); /* ... with the links this proposal rewired */
-                    tp.mod_left = pr.mod_left.data();
-                    tp.mod_right = pr.mod_right.data();
-                    tp.n_mod = (int64_t)pr.mod_node.size();
+                    const Chain::Compiled &cp = c.cprog[(size_t)k];
                     h.trees.push_back(c.dev_tree);
-                    h.topos.push_back(tp);
+                    h.topos.push_back(c.topology_of(&c.cand[(size_t)k])); /* the current tree with the links this proposal rewired */
+                    h.pre.push_back(lvb_gpu_program_view{cp.instr.data(), cp.n_instr, cp.n_slots});
                 }
             }
             h.lens.resize(h.trees.size());
             if (!h.trees.empty())
             {
-                gpu_check(lvb_gpu_score_batch_submit(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
-                                                     &h.ticket));
+                gpu_check(lvb_gpu_score_batch_submit_pre(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
+                                                         h.pre.data(), &h.ticket));
                 score_launches++;
                 h.inflight = true;
             }
@@ -915,13 +959,16 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
     }
     const int host_threads = std::max(1, rc.n_processors_available);
     /* Replicates are spread over rc.devices GPUs (device, device+1, ...: no communication between
-     * them, BASELINE.json configs[4]); auto: ONE driver group per GPU, working its chains as two
-     * alternating halves with all of this GPU's share of the host threads (-p) on the per-chain
-     * work and on the schedule compile.  Measured on a 16-core host with one B200, 64 chains of
-     * 1000 x 200k (profiles/r01f_sa_host_profile.log): 1 group 1.60 s, 2 groups 1.95 s, 4 groups
-     * 2.1 s — more driver threads contend in the CUDA driver and for the cores.  -G overrides. */
+     * them, BASELINE.json configs[4]) and, on each GPU, over driver groups of at least 16 chains, at
+     * most 4: every group has its own context, stream and host thread (with its share of -p for the
+     * per-chain work) and works its chains as two alternating halves.  Rounds of a group are bound
+     * by the latency of its two launches (programs of up to ~300 dependent Fitch steps), so several
+     * groups keep the device busier: 64 chains of 1000 x 200k on one B200 with a 16-core host, search
+     * time without set-up 1.44 / 1.02 / 0.98 s with 1 / 2 / 4 groups once the programs are compiled
+     * in the chains' own loop (profiles/r01i_sa_config5_groups.log; before that, when every device
+     * call compiled its batch itself, one group was fastest: 1.60 / 1.95 / 2.1 s).  -G overrides. */
     const int ND = std::max(1, std::min(rc.devices, R));
-    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : 1;
+    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : std::max(1, std::min(4, R / ND / 16));
     per_dev = std::max(1, per_dev);
     int G = std::max(1, std::min(ND * per_dev, R));
     if (dev.word_count >= 0 && dev.word_count != MSA->nwords)
@@ -931,19 +978,13 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
     for (int g = 0; g <= G; g++)
         first[(size_t)g] = (int)((long)R * g / G);
     if (G > 1)
-    { /* the extra contexts hold their own copy of the leaf rows: encode once, upload G-1 times */
-        std::vector<Lvb_bit_length> flat((size_t)MSA->n * (size_t)MSA->nwords);
-        std::vector<Lvb_bit_length *> rows((size_t)MSA->n);
-        for (long i = 0; i < MSA->n; i++)
-            rows[(size_t)i] = flat.data() + (size_t)i * (size_t)MSA->nwords;
-        DNAToBinary(MSA, rows.data());
-        /* one thread per context: opening a device (CUDA context, pool allocation, 0.3 s each on the
-         * 8-GPU box) and uploading its copy of the leaf rows are independent of each other */
+    { /* the extra contexts hold their own copy of the leaf rows, taken from the first context device
+       * to device (no second DNAToBinary + upload); one thread per context: opening a device (CUDA
+       * context, pool allocation) takes 0.1-0.3 s each */
         std::vector<std::thread> openers;
         for (int g = 1; g < G; g++)
             openers.emplace_back([&, g] {
-                device_open_encoded(extra[(size_t)g], dev.index + g % ND, MSA, rows.data(),
-                                    first[(size_t)g + 1] - first[(size_t)g]);
+                device_open_clone(extra[(size_t)g], dev.index + g % ND, dev, first[(size_t)g + 1] - first[(size_t)g]);
             });
         for (auto &t : openers)
             t.join();

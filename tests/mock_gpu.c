@@ -111,6 +111,12 @@ int lvb_gpu_matrix_upload_flat(lvb_gpu_ctx *c, int64_t n, int64_t nwords, const 
     return rc;
 }
 
+int lvb_gpu_matrix_clone(lvb_gpu_ctx *c, lvb_gpu_ctx *src, int64_t max_trees)
+{
+    /* src->nwords is the block width; upload it as a whole alignment of that width */
+    return lvb_gpu_matrix_upload_flat(c, src->n, src->nwords, src->leaves, 0, src->nwords, max_trees);
+}
+
 /* cached change counts of all 2n-3 nodes of this context's block */
 int lvb_gpu_tree_changes(lvb_gpu_ctx *c, int tree, int64_t *changes)
 {
@@ -266,6 +272,20 @@ int lvb_gpu_batch_wait(lvb_gpu_ctx *c, int ticket, int64_t *lengths)
     memcpy(lengths, c->ticket_len[ticket], (size_t)c->ticket_n[ticket] * sizeof(int64_t));
     c->ticket_n[ticket] = 0;
     return 0;
+}
+
+/* precompiled programs: the mock evaluates the topologies and ignores the programs */
+int lvb_gpu_commit_batch_pre(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                             const lvb_gpu_program_view *pre, int64_t *lengths)
+{
+    (void)pre;
+    return lvb_gpu_commit_batch(c, n_cand, trees, topos, lengths);
+}
+int lvb_gpu_score_batch_submit_pre(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                   const lvb_gpu_program_view *pre, int *ticket)
+{
+    (void)pre;
+    return lvb_gpu_score_batch_submit(c, n_cand, trees, topos, ticket);
 }
 
 /* every mutate_deterministic candidate (TreeOperations.c:105-158), each by a FULL oracle pass:
