@@ -137,3 +137,21 @@ def test_staged_and_unfused_kernel_routes(monkeypatch, env):
     want = CLI_RUNS["test_treelength_6_thread_2"]
     got = H.run_cli(H.cli_input("test_treelength_6_thread_2"), want["flags"], mock=False)
     H.check_against(got, want, str(env))
+
+
+def test_driver_groups_on_gpu():
+    """8 chains in 2 driver groups (second context = device-to-device clone of the leaf rows,
+    lvb_gpu_matrix_clone; programs compiled in the chains' loop, lvb_gpu_*_pre) == single-chain runs"""
+    def run(seed, reps, groups):
+        p = subprocess.run([sys.executable, os.path.join(HERE, "run_host_search.py"), "treelength.npz:tl6_thread_2_text",
+                            str(seed), "1", "0", str(reps), "0", "4", str(groups)], capture_output=True, text=True, timeout=900)
+        assert p.returncode == 0, p.stderr[-2000:]
+        return json.loads(p.stdout.strip().splitlines()[-1])
+
+    multi = run(40, 8, 2)
+    assert multi["results"][0]["groups"] == 2
+    for r in (0, 5, 7):
+        single = run(40 + r, 1, 0)
+        for k in ("final_length", "rearrangements", "topologies", "initial_length", "start_temperature"):
+            assert multi["results"][r][k] == single["results"][0][k], (r, k)
+        assert multi["outtrees"][r] == single["outtrees"][0]
