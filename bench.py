@@ -407,6 +407,8 @@ def main():
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": traffic_src, "traffic_unit": "DRAM bytes per pass (ncu)",
+                     "traffic_gbs": (traffic / (kernel_ms * 1e-3) / 1e9) if traffic else None,
+                     "traffic_frac": (traffic / (kernel_ms * 1e-3) / 1e9 / peak) if traffic else None,
                      "peak_source": peak_src, "kernel": "fitch_exec_kernel<true> (one launch per pass)",
                      "timing": "CUDA events on the engine's stream around each launch, averaged over the timed steps",
                      "kernel_ms_per_pass": kernel_ms,
