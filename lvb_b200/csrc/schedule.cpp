@@ -13,14 +13,24 @@ static inline int64_t strided(const int64_t *base, int64_t stride_bytes, int64_t
 
 ScheduleCompiler::ScheduleCompiler(int64_t n)
     : n_(n), B_(2 * n - 3), cur_(0), stamp_(B_ > 0 ? B_ : 0, 0), child_(stamp_.size(), 0), seen_(stamp_.size(), 0),
-      cut_(stamp_.size(), 0), mod_(stamp_.size(), 0), mod_at_(stamp_.size(), 0), need_(stamp_.size(), 0),
-      size_(stamp_.size(), 0), level_(stamp_.size(), 0), start_(stamp_.size(), 0), depth_(stamp_.size(), 0),
-      push_(stamp_.size(), 0)
+      mod_(stamp_.size(), 0), mod_at_(stamp_.size(), 0), need_(stamp_.size(), 0), size_(stamp_.size(), 0),
+      cl_(stamp_.size(), 0), cr_(stamp_.size(), 0), pos_(stamp_.size(), 0), korder_(stamp_.size(), 0),
+      k0_(stamp_.size(), 0), k1_(stamp_.size(), 0), ksize_(stamp_.size(), 0), kneed_(stamp_.size(), 0),
+      klevel_(stamp_.size(), 0), kstart_(stamp_.size(), 0), kdepth_(stamp_.size(), 0), kpush_(stamp_.size(), 0),
+      kcut_(stamp_.size(), 0)
 {
 }
 
 bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::vector<FitchInstr> &out, int &n_slots,
                                std::string &err, int piece_size, std::vector<Piece> *pieces)
+{
+    return compile_impl(topo, store, out, n_slots, err, piece_size, pieces, topo.n_dirty < 0);
+}
+
+/* whole: try the whole-tree route (every internal node dirty, one sweep from the root's children);
+ * anything unusual there re-enters with whole = false, where the general route names the fault */
+bool ScheduleCompiler::compile_impl(const lvb_gpu_topology &topo, bool store, std::vector<FitchInstr> &out, int &n_slots,
+                                    std::string &err, int piece_size, std::vector<Piece> *pieces, bool whole)
 {
     if (piece_size > 0 && (!store || !pieces))
     {
@@ -37,7 +47,6 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
         std::fill(stamp_.begin(), stamp_.end(), 0u);
         std::fill(child_.begin(), child_.end(), 0u);
         std::fill(seen_.begin(), seen_.end(), 0u);
-        std::fill(cut_.begin(), cut_.end(), 0u);
         std::fill(mod_.begin(), mod_.end(), 0u);
         cur_ = 1;
     }
@@ -62,121 +71,165 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
     auto L = [&](int64_t v) { return mod_[v] == cur_ ? topo.mod_left[mod_at_[v]] : strided(topo.left, topo.stride_bytes, v); };
     auto R = [&](int64_t v) { return mod_[v] == cur_ ? topo.mod_right[mod_at_[v]] : strided(topo.right, topo.stride_bytes, v); };
 
-    /* the dirty set, de-duplicated */
-    dirty_.clear();
-    if (topo.n_dirty < 0)
+    const int64_t rl = L(root), rr = R(root);
+    const bool root_ok = !(rl < 0 || rl >= B_ || rr < 0 || rr >= B_ || rl == rr || rl == root || rr == root);
+    if (whole && !root_ok)
+        return compile_impl(topo, store, out, n_slots, err, piece_size, pieces, false);
+    /* whole-tree route: "dirty" is "internal"; no dirty list, no marks */
+    auto dirtyp = [&](int64_t v) { return whole ? v >= n_ : is_dirty(v); };
+    if (!whole)
     {
-        for (int64_t v = n_; v < B_; v++)
+        /* the dirty set, de-duplicated */
+        dirty_.clear();
+        if (topo.n_dirty < 0)
         {
-            stamp_[v] = cur_;
-            dirty_.push_back((int32_t)v);
-        }
-    }
-    else
-    {
-        for (int64_t k = 0; k < topo.n_dirty; k++)
-        {
-            const int64_t v = topo.dirty[k];
-            if (v < n_ || v >= B_)
-            {
-                err = "schedule: dirty node " + std::to_string(v) + " is not an internal node";
-                return false;
-            }
-            if (stamp_[v] != cur_)
+            dirty_.resize((size_t)(B_ - n_));
+            for (int64_t v = n_; v < B_; v++)
             {
                 stamp_[v] = cur_;
-                dirty_.push_back((int32_t)v);
+                dirty_[(size_t)(v - n_)] = (int32_t)v;
             }
         }
-    }
-    /* which dirty nodes hang under another dirty node */
-    for (int32_t v : dirty_)
-    {
-        const int64_t l = L(v), r = R(v);
-        if (l < 0 || l >= B_ || r < 0 || r >= B_ || l == r || l == v || r == v)
+        else
         {
-            err = "schedule: node " + std::to_string(v) + " has bad children " + std::to_string(l) + "," +
-                  std::to_string(r);
+            for (int64_t k = 0; k < topo.n_dirty; k++)
+            {
+                const int64_t v = topo.dirty[k];
+                if (v < n_ || v >= B_)
+                {
+                    err = "schedule: dirty node " + std::to_string(v) + " is not an internal node";
+                    return false;
+                }
+                if (stamp_[v] != cur_)
+                {
+                    stamp_[v] = cur_;
+                    dirty_.push_back((int32_t)v);
+                }
+            }
+        }
+        /* which dirty nodes hang under another dirty node; the child links are resolved (overlay,
+         * stride) once, here */
+        for (int32_t v : dirty_)
+        {
+            const int64_t l = L(v), r = R(v);
+            if (l < 0 || l >= B_ || r < 0 || r >= B_ || l == r || l == v || r == v)
+            {
+                err = "schedule: node " + std::to_string(v) + " has bad children " + std::to_string(l) + "," +
+                      std::to_string(r);
+                return false;
+            }
+            cl_[v] = (int32_t)l;
+            cr_[v] = (int32_t)r;
+            if (is_dirty(l))
+                child_[l] = cur_;
+            if (is_dirty(r))
+                child_[r] = cur_;
+        }
+        if (!root_ok)
+        {
+            err = "schedule: root " + std::to_string(root) + " has bad children";
             return false;
         }
-        if (is_dirty(l))
-            child_[l] = cur_;
-        if (is_dirty(r))
-            child_[r] = cur_;
-    }
-    const int64_t rl = L(root), rr = R(root);
-    if (rl < 0 || rl >= B_ || rr < 0 || rr >= B_ || rl == rr || rl == root || rr == root)
-    {
-        err = "schedule: root " + std::to_string(root) + " has bad children";
-        return false;
     }
 
-    /* discovery order of every dirty node, from the tops down (parents before children) */
-    order_.clear();
+    /* discovery order of every dirty node, from the tops down (parents before children,
+     * breadth first).  From here on a dirty node is named by its POSITION in that order: the two
+     * children of a node sit next to each other, so the sweeps below walk their arrays almost
+     * sequentially.  A child is kept as its position (dirty) or as ~row (clean operand row). */
+    size_t no = 0;
     auto discover = [&](int64_t top) -> bool {
-        if (!is_dirty(top))
+        if (!dirtyp(top))
             return true;
         if (seen_[top] == cur_)
             return false;
         seen_[top] = cur_;
-        size_t head = order_.size();
-        order_.push_back((int32_t)top);
-        while (head < order_.size())
+        size_t head = no;
+        pos_[top] = (int32_t)no;
+        korder_[no++] = (int32_t)top;
+        while (head < no)
         {
-            const int32_t v = order_[head++];
-            const int64_t c[2] = {L(v), R(v)};
+            const int32_t v = korder_[head];
+            int32_t kid[2];
+            if (whole)
+            { /* links are resolved and checked on the way */
+                const int64_t l = L(v), r = R(v);
+                if (l < 0 || l >= B_ || r < 0 || r >= B_ || l == r || l == v || r == v)
+                    return false;
+                kid[0] = (int32_t)l;
+                kid[1] = (int32_t)r;
+            }
+            else
+            {
+                kid[0] = cl_[v];
+                kid[1] = cr_[v];
+            }
             for (int k = 0; k < 2; k++)
             {
-                if (is_dirty(c[k]))
+                const int32_t c = kid[k];
+                if (dirtyp(c))
                 {
-                    if (seen_[c[k]] == cur_)
+                    if (seen_[c] == cur_)
                         return false;
-                    seen_[c[k]] = cur_;
-                    order_.push_back((int32_t)c[k]);
+                    seen_[c] = cur_;
+                    pos_[c] = (int32_t)no;
+                    kid[k] = (int32_t)no;
+                    korder_[no++] = c;
                 }
+                else
+                    kid[k] = ~c;
             }
+            k0_[head] = kid[0];
+            k1_[head] = kid[1];
+            head++;
         }
         return true;
     };
-    bool ok = true;
-    for (int32_t v : dirty_)
-        if (child_[v] != cur_)
-            ok = ok && discover(v);
-    if (!ok || order_.size() != dirty_.size())
+    if (whole)
+    { /* tops in ascending node order, as the general route meets them */
+        const int64_t t0 = std::min(rl, rr), t1 = std::max(rl, rr);
+        if (!discover(t0) || !discover(t1) || (int64_t)no != B_ - n_)
+            return compile_impl(topo, store, out, n_slots, err, piece_size, pieces, false);
+    }
+    else
     {
-        err = "schedule: dirty nodes do not form a forest (a node is reachable twice or lies on a cycle)";
-        return false;
+        bool ok = true;
+        for (int32_t v : dirty_)
+            if (child_[v] != cur_)
+                ok = ok && discover(v);
+        if (!ok || no != dirty_.size())
+        {
+            err = "schedule: dirty nodes do not form a forest (a node is reachable twice or lies on a cycle)";
+            return false;
+        }
     }
     /* bottom-up over the dirty forest: piece cuts, piece levels, stack need.
      * size: nodes of the current piece under v; a node whose piece reaches piece_size becomes
      * the root of a piece of its own (its row is stored, the parent reads it from HBM).
      * need: stack slots in use at the peak while v's part of the piece is evaluated. */
-    for (size_t k = order_.size(); k-- > 0;)
+    for (size_t k = no; k-- > 0;)
     {
-        const int32_t v = order_[k];
-        const int64_t c[2] = {L(v), R(v)};
+        const int32_t c[2] = {k0_[k], k1_[k]};
         int32_t sz = 1, lvl = 0, nd[2] = {-1, -1};
         for (int j = 0; j < 2; j++)
         {
-            if (!is_dirty(c[j]))
+            if (c[j] < 0)
                 continue;
-            if (cut_[c[j]] == cur_)
-                lvl = std::max(lvl, level_[c[j]] + 1);
+            if (kcut_[c[j]])
+                lvl = std::max(lvl, klevel_[c[j]] + 1);
             else
             {
-                sz += size_[c[j]];
-                lvl = std::max(lvl, level_[c[j]]);
-                nd[j] = need_[c[j]];
+                sz += ksize_[c[j]];
+                lvl = std::max(lvl, klevel_[c[j]]);
+                nd[j] = kneed_[c[j]];
             }
         }
         if (nd[0] >= 0 && nd[1] >= 0)
-            need_[v] = std::max(std::max(nd[0], nd[1]), std::min(nd[0], nd[1]) + 1);
+            kneed_[k] = std::max(std::max(nd[0], nd[1]), std::min(nd[0], nd[1]) + 1);
         else
-            need_[v] = std::max(0, std::max(nd[0], nd[1]));
-        size_[v] = sz;
-        level_[v] = lvl;
-        if (piece_size > 0 && sz >= piece_size)
-            cut_[v] = cur_;
+            kneed_[k] = std::max(0, std::max(nd[0], nd[1]));
+        ksize_[k] = sz;
+        klevel_[k] = lvl;
+        kcut_[k] = (piece_size > 0 && sz >= piece_size) ? 1 : 0;
     }
 
     /* emission.  A piece is the post-order of its nodes: a node comes right after the subtrees of
@@ -191,83 +244,87 @@ bool ScheduleCompiler::compile(const lvb_gpu_topology &topo, bool store, std::ve
     size_t cursor = out.size();
     if (piece_size > 0)
     { /* pieces cut off below: each is a complete post-order program of its own */
-        for (size_t k = order_.size(); k-- > 0;)
+        for (size_t k = no; k-- > 0;)
         {
-            const int32_t v = order_[k];
-            if (cut_[v] != cur_)
+            if (!kcut_[k])
                 continue;
-            start_[v] = (int32_t)cursor;
-            depth_[v] = 0;
-            push_[v] = 0;
+            kstart_[k] = (int32_t)cursor;
+            kdepth_[k] = 0;
+            kpush_[k] = 0;
             if (pieces)
-                pieces->push_back(Piece{(int32_t)cursor, size_[v], level_[v]});
-            cursor += (size_t)size_[v];
+                pieces->push_back(Piece{(int32_t)cursor, ksize_[k], klevel_[k]});
+            cursor += (size_t)ksize_[k];
         }
     }
     const size_t last_begin = cursor;
     int top_level = 0;
     auto level_above = [&](int64_t v) {
-        if (is_dirty(v))
-            top_level = std::max(top_level, level_[v] + (cut_[v] == cur_ ? 1 : 0));
+        if (dirtyp(v))
+            top_level = std::max(top_level, klevel_[pos_[v]] + (int)kcut_[pos_[v]]);
     };
     /* dirty subtrees that do not hang under the root's children (only for dirty sets that are
      * not closed towards the root; LVB's operators never produce them, getplen would still
      * recompute them) */
-    for (int32_t v : dirty_)
-        if (child_[v] != cur_ && v != rl && v != rr)
+    for (size_t i = 0; !whole && i < dirty_.size(); i++)
+        if (const int32_t v = dirty_[i]; child_[v] != cur_ && v != rl && v != rr)
         {
             level_above(v);
-            if (cut_[v] != cur_)
+            const int32_t k = pos_[v];
+            if (!kcut_[k])
             {
-                start_[v] = (int32_t)cursor;
-                depth_[v] = 0;
-                push_[v] = 0;
-                cursor += (size_t)size_[v];
+                kstart_[k] = (int32_t)cursor;
+                kdepth_[k] = 0;
+                kpush_[k] = 0;
+                cursor += (size_t)ksize_[k];
             }
         }
     /* root step, TreeEvaluation.c:238-264: fitch(root.left, root.right), never stored, then the
      * count against the root's own row */
     level_above(rl);
     level_above(rr);
+    const int32_t krl = dirtyp(rl) ? pos_[rl] : ~(int32_t)rl, krr = dirtyp(rr) ? pos_[rr] : ~(int32_t)rr;
+    auto inside = [&](int32_t c) { return c >= 0 && !kcut_[c]; }; /* evaluated inside the piece being emitted */
+    auto row_of = [&](int32_t c) { return c >= 0 ? korder_[c] : ~c; };
     const size_t root_start = cursor;
-    cursor += 1 + (size_t)(inside(rl) ? size_[rl] : 0) + (size_t)(inside(rr) ? size_[rr] : 0);
+    cursor += 1 + (size_t)(inside(krl) ? ksize_[krl] : 0) + (size_t)(inside(krr) ? ksize_[krr] : 0);
     const size_t root_pos = cursor - 1;
     cursor++; /* the count-only instruction */
     out.resize(cursor);
+    FitchInstr *const o = out.data();
 
-    /* one node: place the dirty children, write the node's own instruction at `pos` */
-    auto place = [&](int64_t l, int64_t r, int32_t node, uint32_t ctl, size_t start, int depth, size_t pos, uint32_t push) {
+    /* one node: place the dirty children, write the node's own instruction at `at` */
+    auto place = [&](int32_t l, int32_t r, int32_t node, uint32_t ctl, size_t start, int depth, size_t at, uint32_t push) {
         const bool dl = inside(l), dr = inside(r);
         const uint32_t pushbits = push << LVB_CTL_PUSH_SHIFT;
         if (dl && dr)
         {
-            const bool left_first = need_[l] >= need_[r];
-            const int64_t first = left_first ? l : r, second = left_first ? r : l;
-            start_[first] = (int32_t)start;
-            depth_[first] = depth;
-            push_[first] = depth + 1; /* its result waits in slot `depth` */
-            start_[second] = (int32_t)(start + (size_t)size_[first]);
-            depth_[second] = depth + 1;
-            push_[second] = 0;
+            const bool left_first = kneed_[l] >= kneed_[r];
+            const int32_t first = left_first ? l : r, second = left_first ? r : l;
+            kstart_[first] = (int32_t)start;
+            kdepth_[first] = depth;
+            kpush_[first] = depth + 1; /* its result waits in slot `depth` */
+            kstart_[second] = (int32_t)(start + (size_t)ksize_[first]);
+            kdepth_[second] = depth + 1;
+            kpush_[second] = 0;
             peak = std::max(peak, depth + 1);
-            out[pos] = FitchInstr{LVB_OPER_SLOT(depth), LVB_OPER_PREV, node, ctl | pushbits};
+            o[at] = FitchInstr{LVB_OPER_SLOT(depth), LVB_OPER_PREV, node, ctl | pushbits};
         }
         else if (dl || dr)
         {
-            const int64_t c = dl ? l : r, other = dl ? r : l;
-            start_[c] = (int32_t)start;
-            depth_[c] = depth;
-            push_[c] = 0;
-            out[pos] = FitchInstr{LVB_OPER_PREV, (int32_t)other, node, ctl | pushbits};
+            const int32_t c = dl ? l : r, other = dl ? r : l;
+            kstart_[c] = (int32_t)start;
+            kdepth_[c] = depth;
+            kpush_[c] = 0;
+            o[at] = FitchInstr{LVB_OPER_PREV, row_of(other), node, ctl | pushbits};
         }
         else
-            out[pos] = FitchInstr{(int32_t)l, (int32_t)r, node, ctl | pushbits};
+            o[at] = FitchInstr{row_of(l), row_of(r), node, ctl | pushbits};
     };
-    place(rl, rr, -1, 0u, root_start, 0, root_pos, 0u);
-    out[root_pos + 1] = FitchInstr{LVB_OPER_PREV, (int32_t)root, -1, LVB_CTL_COUNT_ONLY};
-    for (int32_t v : order_) /* parents before children: start/depth/push of v are set by now */
-        place(L(v), R(v), v, node_ctl, (size_t)start_[v], depth_[v], (size_t)start_[v] + (size_t)size_[v] - 1,
-              (uint32_t)push_[v]);
+    place(krl, krr, -1, 0u, root_start, 0, root_pos, 0u);
+    o[root_pos + 1] = FitchInstr{LVB_OPER_PREV, (int32_t)root, -1, LVB_CTL_COUNT_ONLY};
+    for (size_t k = 0; k < no; k++) /* parents before children: start/depth/push of k are set by now */
+        place(k0_[k], k1_[k], korder_[k], node_ctl, (size_t)kstart_[k], kdepth_[k], (size_t)kstart_[k] + (size_t)ksize_[k] - 1,
+              (uint32_t)kpush_[k]);
     if (pieces && cursor > last_begin)
         pieces->push_back(Piece{(int32_t)last_begin, (int32_t)(cursor - last_begin), top_level});
 

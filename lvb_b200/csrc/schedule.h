@@ -62,6 +62,8 @@ class ScheduleCompiler
                          std::string &err, int piece_size = 0, std::vector<Piece> *pieces = nullptr);
 
   private:
+    bool compile_impl(const lvb_gpu_topology &topo, bool store, std::vector<FitchInstr> &out, int &n_slots,
+                      std::string &err, int piece_size, std::vector<Piece> *pieces, bool whole);
     struct Frame
     {
         int32_t v;
@@ -69,23 +71,29 @@ class ScheduleCompiler
         int32_t stage;
     };
     bool is_dirty(int64_t v) const { return v >= n_ && v < B_ && stamp_[v] == cur_; }
-    /* dirty and evaluated inside the piece that is being emitted (not the root of another piece) */
-    bool inside(int64_t v) const { return is_dirty(v) && cut_[v] != cur_; }
     int64_t n_, B_;
     uint32_t cur_;
+    /* indexed by node */
     std::vector<uint32_t> stamp_;   /* dirty marks */
     std::vector<uint32_t> child_;   /* "is a child of a dirty node" marks */
     std::vector<uint32_t> seen_;    /* visited marks (cycle / duplicate guard) */
-    std::vector<uint32_t> cut_;     /* "is the root of a piece of its own" marks */
     std::vector<uint32_t> mod_;     /* "child links come from the overlay" marks */
     std::vector<int32_t> mod_at_;   /* index into the overlay arrays */
-    std::vector<int32_t> need_;     /* stack need per dirty node */
-    std::vector<int32_t> size_;     /* nodes of the piece hanging under a dirty node */
-    std::vector<int32_t> level_;    /* level of the piece a dirty node belongs to */
-    std::vector<int32_t> start_;    /* emission: index of the first instruction of a node's subtree */
-    std::vector<int32_t> depth_;    /* emission: stack slots in use while the subtree is evaluated */
-    std::vector<int32_t> push_;     /* emission: 1 + slot the node's result is parked in, 0 = none */
-    std::vector<int32_t> order_;    /* scratch: discovery order */
+    std::vector<int32_t> need_;     /* up-pass: stack need per node */
+    std::vector<int32_t> size_;     /* up-pass: internal nodes at and below a node */
+    std::vector<int32_t> cl_, cr_;  /* resolved child links of the dirty nodes */
+    std::vector<int32_t> pos_;      /* position of a dirty node in the discovery order */
+    /* indexed by position in the discovery order (compile) */
+    std::vector<int32_t> korder_;   /* the node at a position */
+    std::vector<int32_t> k0_, k1_;  /* children: position of a dirty child, or ~row of a clean one */
+    std::vector<int32_t> ksize_;    /* nodes of the piece hanging under the node */
+    std::vector<int32_t> kneed_;    /* stack need */
+    std::vector<int32_t> klevel_;   /* level of the piece the node belongs to */
+    std::vector<int32_t> kstart_;   /* emission: index of the first instruction of the node's subtree */
+    std::vector<int32_t> kdepth_;   /* emission: stack slots in use while the subtree is evaluated */
+    std::vector<int32_t> kpush_;    /* emission: 1 + slot the node's result is parked in, 0 = none */
+    std::vector<uint8_t> kcut_;     /* the node is the root of a piece of its own */
+    std::vector<int32_t> order_;    /* scratch (up-pass): discovery order */
     std::vector<int32_t> dirty_;    /* scratch: de-duplicated dirty list */
     std::vector<Frame> frames_;
 };
