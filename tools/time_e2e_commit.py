@@ -40,8 +40,8 @@ lib = load_library()
 out = np.zeros((4 * n, 4), dtype=np.int32); pcs = np.zeros((4 * n, 3), dtype=np.int32)
 k, sl, npc = C.c_int64(0), C.c_int64(0), C.c_int64(0)
 structs = [tp.as_struct() for tp in topos]
-for ps in (0, 77):
+for what, seq in (('a new topology every call', structs), ('the same topology every call', [structs[0]] * steps)):
     t0 = time.perf_counter()
-    for ts in structs:
-        lib.lvb_gpu_compile_pieces(n, C.byref(ts), ps, out.ctypes.data, 4 * n, C.byref(k), C.byref(sl), pcs.ctypes.data, 4 * n, C.byref(npc))
-    print('compile_pieces(piece_size %d) %.1f us per tree, %d pieces' % (ps, (time.perf_counter() - t0) / steps * 1e6, npc.value))
+    for ts in seq:
+        lib.lvb_gpu_compile_schedule(n, C.byref(ts), 1, out.ctypes.data, 4 * n, C.byref(k), C.byref(sl))
+    print('lvb_gpu_compile_schedule (persistent compiler), %s: %.1f us per tree' % (what, (time.perf_counter() - t0) / steps * 1e6))
