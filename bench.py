@@ -1,27 +1,29 @@
 #!/usr/bin/env python
-"""bench.py — Fitch node x site updates/s (BASELINE.json metric) on B200.
+"""bench.py — Fitch node x site updates/s and SA trees scored/s (BASELINE.json metric) on B200.
 
-Workload (config.workload): BASELINE.json configs[3] shape, 2000 taxa x 1,000,000 sites,
-which fits one GPU (1.0 GB alignment + 2.0 GB of state rows).  A step is one full getplen
-pass (every internal node dirty: n-3 stored Fitch combinations + the 2 root-step
-applications = (n-1) * m node x site updates) of one tree of that shape.
+Workload (config.workload): BASELINE.json configs[3] shape, 2000 taxa x 1,000,000 sites.  A step is
+one full getplen pass (every internal node dirty: n-3 stored Fitch combinations + the 2 root-step
+applications = (n-1) * m node x site updates) of ONE tree of that shape.
 
+N = 1
   value  device-resident: the program of the tree is already on the device, the step is the
-         launch(es) of the Fitch kernel (+ the tiny count-finalise kernel), CUDA events on the
-         engine's stream.
-  e2e    through the C-ABI (lvb_gpu_tree_commit) with HOST topology arrays: host schedule
-         compile, pinned H2D of the program, kernels, D2H of the tree length, every step, each
-         step a different random tree.
-  extra  SA trees scored/s: batches of candidate trees (NNI neighbourhood of the current tree)
-         through lvb_gpu_score_batch, the other half of BASELINE.json's metric.
+         launch of the Fitch kernel (counts are folded inside it), CUDA events on the engine's stream.
+  e2e    through the C-ABI (lvb_gpu_tree_commit) with HOST topology arrays: host schedule compile,
+         H2D of the program, kernel, D2H of the tree length, every step, each step a different tree.
+N > 1 (the driver's torchrun command, one rank per GPU) — the two partitions north_star names:
+  value  BASELINE configs[3]: the SAME one tree, its words sharded over the ranks in site blocks
+         (the reference's OpenMP decomposition, TreeEvaluation.c:95-97), partial lengths summed by
+         the all-reduce inside the C-ABI; "scaling": "strong".  The all-reduced length must equal
+         the single-GPU length of the same tree (asserted).
+  replicas       sub-record: one whole tree per GPU per step, no collective (weak scaling).
+  sa_replicates  sub-record, BASELINE configs[4]: 64 SA chains (seeds 1000+r) on 1000 x 200k through
+         the C++ SA driver (lvb_b200/host/solve.cpp), chains sharded over the ranks
+         (sharding.replicate_shard), fixed rearrangement budget per chain; trees scored/s and
+         rearrangements/s summed over ranks.  Printed only if sampled result trees re-evaluate to the
+         reported lengths on the CPU oracle in the same run.
 
-N > 1 (torchrun, one rank per GPU): BASELINE configs[4] style replicas — every rank holds the
-alignment and evaluates its own trees, no data-path collective ("scaling": "weak").
-`--mode siteblock` instead shards the words of ONE tree over the ranks with an NCCL all-reduce
-of the partial lengths inside the C-ABI (BASELINE configs[3]); that is "strong" scaling.
-
---impl reference times the reference's own CPU getplen (oracle/_ref, OpenMP, all host cores)
-on a bounded column sample of the same workload.
+--impl reference times the reference's own CPU getplen (oracle/_ref, OpenMP, all host cores) on the
+same 2000 x 1M alignment and tree.
 """
 from __future__ import annotations
 
@@ -30,6 +32,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -48,12 +51,21 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--mode", default="replicas", choices=["replicas", "siteblock"])
+    ap.add_argument("--mode", default="auto", choices=["auto", "replicas", "siteblock"],
+                    help="headline at N > 1: auto/siteblock = one tree in site blocks + all-reduce; replicas = one tree per GPU")
     ap.add_argument("--taxa", type=int, default=2000)
     ap.add_argument("--sites", type=int, default=1_000_000)
-    ap.add_argument("--cpu-sample-sites", type=int, default=100_000)
+    ap.add_argument("--cpu-sample-sites", type=int, default=0,
+                    help="CPU legs on a column sample of this many sites (0 = the full alignment; a sample is only "
+                         "taken by itself when host memory is short)")
     ap.add_argument("--candidates", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sa-chains", type=int, default=64)
+    ap.add_argument("--sa-taxa", type=int, default=1000)
+    ap.add_argument("--sa-sites", type=int, default=200_000)
+    ap.add_argument("--sa-rearrangements", type=int, default=3000)
+    ap.add_argument("--no-sa", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="headline only (no candidate scoring / NNI / SA sub-records)")
     return ap.parse_args()
 
 
@@ -64,14 +76,24 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_from_profile():
-    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+def traffic_from_profile(key="dram_bytes_per_pass"):
+    """DRAM bytes per launch of a kernel from the committed `ncu --set full` capture
     (profiles/ncu_traffic.json, written by tools/ncu_summary.py); None if there is none."""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if not os.path.exists(p):
         return None, None
     d = json.load(open(p))
-    return d.get("dram_bytes_per_pass"), d.get("source")
+    return d.get(key), d.get("source")
+
+
+def host_memory_gb() -> float:
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
 
 
 class ClockSampler:
@@ -144,53 +166,53 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.samples), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
-def unpack_text(enc: np.ndarray, sites: int):
-    """first `sites` sites of the packed one-hot alignment as text rows (for the CPU reference)"""
-    lut = np.zeros(16, dtype=np.uint8)
-    lut[[1, 2, 4, 8]] = np.frombuffer(b"ACGT", dtype=np.uint8)
-    lut[15] = ord("N")
-    words = (sites + 15) // 16
-    rows = []
-    for i in range(enc.shape[0]):
-        b = enc[i, :words].view(np.uint8)
-        nib = np.empty(b.size * 2, dtype=np.uint8)
-        nib[0::2] = b & 15
-        nib[1::2] = b >> 4
-        rows.append(bytes(lut[nib[:sites]]))
-    return rows
-
-
-def cpu_reference_leg(enc, left, right, root, sample_sites, threads, seconds_budget=12.0):
-    """Reference getplen (oracle/_ref) on a column sample: full passes, all host threads."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracles
-
-    if not oracles.have_ref():
-        return None
-    n = enc.shape[0]
-    rows = unpack_text(enc, sample_sites)
-    msa = oracles.RefMSA.from_rows(rows, threads=threads)
-    t = msa.tree()
+def parent_of(left, right, root, n):
     B = 2 * n - 3
     parent = np.full(B, -1, dtype=np.int64)
     for v in list(range(n, B)) + [root]:
         parent[left[v]] = v
         parent[right[v]] = v
-    t.set_topology(parent, left, right, root)
-    L = oracles.ref()
+    return parent
+
+
+def cpu_reference_leg(enc, m, left, right, root, threads, passes, warm=1):
+    """The reference's own getplen (oracle/_ref, unmodified, OpenMP) on `enc`: `passes` timed full
+    passes of the tree after `warm` untimed ones.  Returns None if the reference was not built."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracles
+
+    if not oracles.have_ref():
+        return None
     import ctypes as C
 
+    n = enc.shape[0]
+    msa = oracles.RefMSA.from_packed(enc, m, threads=threads)
+    t = msa.tree()
+    t.set_topology(parent_of(left, right, root, n), left, right, root)
+    L = oracles.ref()
     length = C.c_long(0)
-    one = L.ref_time_full_passes(msa.h, t.t, root, 1, C.byref(length))  # warm-up + calibration
-    reps = max(2, min(200, int(seconds_budget / max(one, 1e-4))))
-    secs = L.ref_time_full_passes(msa.h, t.t, root, reps, C.byref(length))
-    updates = (n - 1) * msa.m * reps
+    if warm > 0:
+        L.ref_time_full_passes(msa.h, t.t, root, warm, C.byref(length))
+    secs = L.ref_time_full_passes(msa.h, t.t, root, passes, C.byref(length))
+    updates = (n - 1) * msa.m * passes
     return {
         "value": updates / secs, "unit": UNIT, "cores": int(msa.n_threads), "kind": "reference",
-        "sample": f"{reps} full getplen passes (unmodified reference, OpenMP team of {msa.n_threads}) on the first "
-                  f"{msa.m} of the sites of the same {n}-taxon alignment and tree; {secs / reps * 1e3:.2f} ms/pass",
-        "ms_per_pass": secs / reps * 1e3, "length": int(length.value), "sites": int(msa.m),
+        "sample": f"{passes} full getplen passes (unmodified reference, OpenMP team of {msa.n_threads}, slices of "
+                  f"{msa.slice} words) of the same tree on {n} taxa x {msa.m} sites; {secs / passes * 1e3:.1f} ms/pass",
+        "ms_per_pass": secs / passes * 1e3, "length": int(length.value), "sites": int(msa.m),
     }
+
+
+def cpu_workload(args, n, m):
+    """(enc, sites) the CPU legs run on: the full alignment unless memory is short or a sample was asked for"""
+    from lvb_b200 import synthetic
+
+    sites = m
+    if args.cpu_sample_sites > 0:
+        sites = min(m, args.cpu_sample_sites)
+    elif host_memory_gb() < 12.0 and m > 100_000:
+        sites = 100_000  # 2000 x 1M needs 1 GB packed + 2 GB of reference tree rows (+ this process)
+    return sites
 
 
 def nni_candidates(left, right, root, n, count, seed):
@@ -198,10 +220,7 @@ def nni_candidates(left, right, root, n, count, seed):
     from lvb_b200 import Topology
 
     B = 2 * n - 3
-    parent = np.full(B, -1, dtype=np.int64)
-    for v in list(range(n, B)) + [root]:
-        parent[left[v]] = v
-        parent[right[v]] = v
+    parent = parent_of(left, right, root, n)
     rng = np.random.default_rng(seed)
     out, index = [], []  # index: position of the candidate in lvb_gpu_nni_neighbourhood's output
     for u in rng.integers(n, B, size=count).tolist():
@@ -225,6 +244,135 @@ def nni_candidates(left, right, root, n, count, seed):
     return out, index
 
 
+# ---------------------------------------------------------------------------------------------
+# SA replicates (BASELINE configs[4]) through the C++ SA driver
+# ---------------------------------------------------------------------------------------------
+def newick_topologies(text: str, titles):
+    """trees of an `outtree` file as LVB arrays (left, right, root): lvb_treeprint writes
+    (rootleaf,subtree,subtree); — src/TreeOperations.c:1144-1220"""
+    index = {t: i for i, t in enumerate(titles)}
+    n = len(titles)
+    out = []
+    for line in text.split(";"):
+        s = line.strip()
+        if not s:
+            continue
+        left = np.full(2 * n - 3, -1, dtype=np.int64)
+        right = np.full(2 * n - 3, -1, dtype=np.int64)
+        nxt = [n]
+        pos = [0]
+
+        def parse():
+            if s[pos[0]] == "(":
+                pos[0] += 1
+                kids = [parse()]
+                while s[pos[0]] == ",":
+                    pos[0] += 1
+                    kids.append(parse())
+                assert s[pos[0]] == ")"
+                pos[0] += 1
+                return kids
+            j = pos[0]
+            while s[j] not in ",()":
+                j += 1
+            name = s[pos[0]:j].strip()
+            pos[0] = j
+            return index[name]
+
+        def build(node):
+            if not isinstance(node, list):
+                return node
+            assert len(node) == 2
+            a, b = build(node[0]), build(node[1])
+            v = nxt[0]
+            nxt[0] += 1
+            left[v], right[v] = a, b
+            return v
+
+        top = parse()
+        assert isinstance(top, list) and len(top) == 3 and not isinstance(top[0], list)
+        root = top[0]
+        left[root], right[root] = build(top[1]), build(top[2])
+        assert nxt[0] == 2 * n - 3
+        out.append((left, right, int(root)))
+    return out
+
+
+class c_stdout_to_stderr:
+    """the C++ search prints LVB's progress table with printf; bench.py's stdout carries ONE JSON line"""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        import ctypes
+
+        ctypes.CDLL(None).fflush(None)
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
+def sa_replicates_record(args, rank, world, local_rank, barrier, gather):
+    """64 chains of 1000 x 200k sharded over the ranks; returns the sub-record on rank 0 (None elsewhere)"""
+    from lvb_b200 import host, sharding, synthetic
+
+    n, m, R = args.sa_taxa, args.sa_sites, args.sa_chains
+    st = synthetic.survey_alignment(n, m, 1, 0.02)
+    rows = synthetic.text_rows(st)
+    msa = host.HostMSA.from_rows(rows)
+    seed0, count = sharding.replicate_shard(1000, R, rank, world)
+    threads = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
+    with tempfile.TemporaryDirectory() as td, c_stdout_to_stderr():
+        outtree = os.path.join(td, "outtree")
+        # warm-up: CUDA context, kernels, pools (a short search of the same shape)
+        msa.search(seed0, algorithm=1, device=local_rank, replicates=min(count, 4), max_rearrangements=100,
+                   host_threads=threads)
+        barrier()
+        t0 = time.perf_counter()
+        res = msa.search(seed0, algorithm=1, device=local_rank, replicates=count, max_rearrangements=args.sa_rearrangements,
+                         host_threads=threads, outtree_path=outtree)
+        wall = time.perf_counter() - t0
+        barrier()
+        # parity gate of this very run: the best tree of the rank's first and last chain, re-evaluated by the CPU oracle
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracles
+
+        enc = msa.enc()
+        titles = [msa.title(i) for i in range(msa.n)]
+        checked, ok = [], True
+        for r in sorted({0, count - 1}):
+            path = outtree if r == 0 else f"{outtree}.r{r}"
+            left, right, root = newick_topologies(open(path).read(), titles)[0]
+            want = oracles.oracle_getplen(enc, left, right, root)[0]
+            checked.append({"chain": seed0 - 1000 + r, "reported": res[r]["final_length"], "oracle": want})
+            ok = ok and want == res[r]["final_length"]
+    mine = {"rank": rank, "chains": count, "search_s": res[0]["seconds"], "wall_s": wall, "host_threads": threads,
+            "trees_scored": sum(r["trees_scored"] for r in res), "rearrangements": sum(r["rearrangements"] for r in res),
+            "groups": res[0]["groups"], "checked": checked, "ok": ok,
+            "final_lengths_head": [r["final_length"] for r in res[:2]]}
+    allr = gather(mine)
+    msa.close()
+    if rank != 0:
+        return None
+    if not all(r["ok"] for r in allr):
+        return {"refused": "a sampled result tree did not re-evaluate to the reported length on the oracle",
+                "checked": [c for r in allr for c in r["checked"]]}
+    secs = max(r["wall_s"] for r in allr)
+    return {
+        "workload": f"{R} SA chains (seeds 1000..{1000 + R - 1}), {n} taxa x {m} sites, {args.sa_rearrangements} rearrangements "
+                    f"per chain, algorithm 1; chains sharded over {world} rank(s), one process per GPU, no collective",
+        "trees_scored_per_s": sum(r["trees_scored"] for r in allr) / secs,
+        "rearrangements_per_s": sum(r["rearrangements"] for r in allr) / secs,
+        "seconds": secs, "timing": "wall clock of the search call (host-driven loop), max over ranks, between barriers",
+        "per_rank": [{k: r[k] for k in ("rank", "chains", "search_s", "wall_s", "host_threads", "groups")} for r in allr],
+        "parity": {"oracle_checked": [c for r in allr for c in r["checked"]], "ok": True},
+        "api": "lvb_b200/host/solve.cpp GetSolnBatched (speculative batches over lvb_gpu_score_batch_submit_pre / "
+               "lvb_gpu_commit_batch_pre)",
+    }
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -239,24 +387,31 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        enc = synthetic.random_packed(n, (args.cpu_sample_sites + 15) // 16, seed=1)
-        left, right, root = synthetic.random_topology(n, seed=3)
         t0 = time.time()
-        # W warm-up + K timed "steps": each step is a bounded sample (one pass on the column sample)
-        leg = cpu_reference_leg(enc, left, right, root, args.cpu_sample_sites, nproc,
-                                seconds_budget=max(1.0, 0.05 * args.steps))
+        sites = cpu_workload(args, n, m)
+        enc = synthetic.random_packed(n, nwords, seed=1)
+        if sites != m:
+            enc = np.ascontiguousarray(enc[:, : (sites + 15) // 16])
+        left, right, root = synthetic.random_topology(n, seed=3)
+        # every step is one full pass of the tree; W warm-up passes, then K timed ones (bounded: the whole run
+        # stays within minutes at ~0.1-0.2 s per pass)
+        passes = max(1, min(args.steps, 60))
+        leg = cpu_reference_leg(enc, sites, left, right, root, nproc, passes, warm=max(1, min(args.warmup, 5)))
         if leg is None:
             print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built on this box"}))
             return
         line = {
             "impl": "reference", "metric": METRIC, "value": leg["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": leg["ms_per_pass"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": f"full getplen passes, {n} taxa x {leg['sites']} sites (column sample of the "
-                                   f"{n} x {m} workload), reference CPU build, {leg['cores']} OpenMP threads"},
+            "steps": passes, "warmup": max(1, min(args.warmup, 5)), "ms_per_step": leg["ms_per_pass"],
+            "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None,
+            "dtype": "u64 (4-bit state sets, 64-bit SWAR words)", "data": "synthetic",
+            "config": {"workload": f"full getplen pass, {n} taxa x {leg['sites']} sites"
+                                   + ("" if leg["sites"] == m else f" (column sample of the {n} x {m} workload)")
+                                   + f", one tree, reference CPU build, {leg['cores']} OpenMP threads",
+                       "taxa": n, "sites": leg["sites"], "same_config_as_b200_arm": leg["sites"] == m},
             "cpu_baseline": {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": leg["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "wall_s": time.time() - t0,
+            "length_check": leg["length"], "wall_s": time.time() - t0,
         }
         print(json.dumps(line))
         return
@@ -282,58 +437,77 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def gather(obj):
+        if dist is None:
+            return [obj]
+        out = [None] * world
+        dist.all_gather_object(out, obj)
+        return out
+
     from lvb_b200 import Engine, Topology
 
-    siteblock = args.mode == "siteblock" and world > 1
-    eng = Engine(local_rank)
+    siteblock = world > 1 and args.mode in ("auto", "siteblock")
     enc = synthetic.random_packed(n, nwords, seed=1)
-    if siteblock:
-        from lvb_b200 import sharding
-
-        w0, wc = sharding.word_block(nwords, rank, world)
-        eng.upload(enc, word_begin=w0, word_count=wc, max_trees=2)
-        uid = [Engine.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        eng.comm_init(world, rank, uid[0])
-    else:
-        eng.upload(enc, max_trees=2)
-    tree = eng.tree_create()
-    # every rank its own trees in replica mode; the same tree on every rank in site-block mode
-    tree_seed = 3 if siteblock else 3 + 1000 * rank
-    left, right, root = synthetic.random_topology(n, seed=tree_seed)
+    left, right, root = synthetic.random_topology(n, seed=3)
     topo = Topology(left, right, root)
     updates_per_pass = (n - 1) * m  # real sites; the reference's count
-    my_words = eng.word_count
-    algo_bytes_per_pass = (3 * n - 6) * 8 * my_words  # 24 B per node-word update, SURVEY.md §8(d)
+    peak, peak_src = peaks()
 
-    length0 = eng.commit(tree, topo)
-    warm = max(3, args.warmup)
-    for _ in range(warm):
-        eng.rerun_last_batch()
-    eng.synchronize()
-
-    with ClockSampler(local_rank) as clocks:
-        # ---- region A: device-resident; CUDA events on the engine's own stream ----
+    def timed_passes(eng, steps):
+        """`steps` device-resident passes of the batch resident on eng: (seconds by CUDA events on the engine's
+        stream [max over ranks], this rank's mean kernel ms, launches)"""
         ext = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local_rank))
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = eng.launches
         eng.kernel_time(reset=True)
         barrier()
         ev0.record(ext)
-        for _ in range(args.steps):
+        for _ in range(steps):
             eng.rerun_last_batch()
         ev1.record(ext)
         eng.synchronize()
         barrier()
-        wall_a = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
+        mine = ev0.elapsed_time(ev1) * 1e-3
         k_ms, k_launch = eng.kernel_time()
-        gpu_launches = eng.launches - l0
-        kernel_ms = max_over_ranks(k_ms / max(1, k_launch))
+        return max_over_ranks(mine), mine, k_ms / max(1, k_launch), eng.launches - l0
+
+    warm = max(3, args.warmup)
+    extras = {}
+    with ClockSampler(local_rank) as clocks:
+        # =================== headline ===================
+        eng = Engine(local_rank)
+        if siteblock:
+            from lvb_b200 import sharding
+
+            w0, wc = sharding.word_block(nwords, rank, world)
+            eng.upload(enc, word_begin=w0, word_count=wc, max_trees=2)
+            uid = [Engine.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            eng.comm_init(world, rank, uid[0])
+            tree_seed = 3
+        else:
+            eng.upload(enc, max_trees=2)
+            tree_seed = 3 + 1000 * rank  # replicas: every rank its own trees
+            if rank:
+                left, right, root = synthetic.random_topology(n, seed=tree_seed)
+                topo = Topology(left, right, root)
+        my_words = eng.word_count
+        tree = eng.tree_create()
+        length0 = eng.commit(tree, topo)
+        for _ in range(warm):
+            eng.rerun_last_batch()
+        eng.synchronize()
+        # ---- region A: device-resident ----
+        wall_a, wall_a_mine, kernel_ms_mine, gpu_launches = timed_passes(eng, args.steps)
+        kernel_ms = max_over_ranks(kernel_ms_mine)
+        per_rank = gather({"rank": rank, "kernel_ms": kernel_ms_mine, "stream_ms_per_step": wall_a_mine / args.steps * 1e3,
+                           "words": int(my_words), "length": int(length0)})
+        if siteblock:  # every rank got the all-reduced length of the one tree
+            assert all(r["length"] == per_rank[0]["length"] for r in per_rank), per_rank
 
         # ---- region B: end to end through the C-ABI, host topology arrays in, length out ----
-        topos = [Topology(*synthetic.random_topology(n, seed=tree_seed + 17 * (s + 1))) for s in range(args.steps)]
-        if siteblock:
-            topos = [Topology(*synthetic.random_topology(n, seed=3 + 17 * (s + 1))) for s in range(args.steps)]
+        e2e_seed = 3 if siteblock else tree_seed
+        topos = [Topology(*synthetic.random_topology(n, seed=e2e_seed + 17 * (s + 1))) for s in range(args.steps)]
         for s in range(min(3, args.steps)):
             eng.commit(tree, topos[s])
         barrier()
@@ -342,52 +516,103 @@ def main():
         barrier()
         wall_b = max_over_ranks(time.perf_counter() - t0)
 
-        # ---- SA candidate scoring: trees scored/s ----
-        eng.commit(tree, topo)
-        cands, cand_index = nni_candidates(left, right, root, n, args.candidates, seed=5 + (0 if siteblock else rank))
-        trees = [tree] * len(cands)
-        got = eng.score_batch(trees, cands)
-        barrier()
-        t0 = time.perf_counter()
-        reps_c = 3
-        for _ in range(reps_c):
+        total_ranks = 1 if siteblock else world
+        value = total_ranks * args.steps * updates_per_pass / wall_a
+        e2e_value = total_ranks * args.steps * updates_per_pass / wall_b
+
+        if not args.no_extras and world == 1:
+            # ---- SA candidate scoring: trees scored/s ----
+            eng.commit(tree, topo)
+            cands, cand_index = nni_candidates(left, right, root, n, args.candidates, seed=5)
+            trees = [tree] * len(cands)
             got = eng.score_batch(trees, cands)
-        barrier()
-        wall_c = max_over_ranks(time.perf_counter() - t0)
-        eng.kernel_time(reset=True)
-        for _ in range(reps_c):
-            eng.rerun_last_batch()
-        eng.synchronize()
-        c_ms, c_launch = eng.kernel_time()
-        dirty_mean = float(np.mean([len(c.dirty) for c in cands]))
-        # rows each candidate's program reads from HBM/L2 (operands >= 0), from the host compiler
-        from lvb_b200 import compile_schedule
+            t0 = time.perf_counter()
+            reps_c = 3
+            for _ in range(reps_c):
+                got = eng.score_batch(trees, cands)
+            wall_c = time.perf_counter() - t0
+            eng.kernel_time(reset=True)
+            for _ in range(reps_c):
+                eng.rerun_last_batch()
+            eng.synchronize()
+            c_ms, c_launch = eng.kernel_time()
+            dirty_mean = float(np.mean([len(c.dirty) for c in cands]))
+            from lvb_b200 import compile_schedule
 
-        rows_read = [int((compile_schedule(n, c, store=False)[0][:, :2] >= 0).sum()) for c in cands[:64]]
-        rows_read_mean = float(np.mean(rows_read))
-
-        # ---- exhaustive NNI neighbourhood (deterministic_hillclimb's 2(n-3) candidates) in one call ----
-        scratch = eng.tree_create()
-        nn = eng.nni_neighbourhood(tree, scratch, topo)
-        barrier()
-        t0 = time.perf_counter()
-        reps_n = 3
-        for _ in range(reps_n):
+            rows_read = [int((compile_schedule(n, c, store=False)[0][:, :2] >= 0).sum()) for c in cands[:64]]
+            rows_read_mean = float(np.mean(rows_read))
+            score_ms = c_ms / max(1, c_launch)
+            score_traffic, score_src = traffic_from_profile("score_dram_bytes_per_batch")
+            extras["sa_trees_scored_per_s"] = {
+                "e2e": reps_c * len(cands) / wall_c, "device": len(cands) / (score_ms * 1e-3),
+                "batch": len(cands), "mean_dirty_nodes": dirty_mean,
+                "api": "lvb_gpu_score_batch: NNI candidates of the current tree, one launch per batch (Python binding, "
+                       "serial compile; the C++ SA driver is measured in sa_replicates)",
+            }
+            operand_gbs = rows_read_mean * 8 * my_words * len(cands) / (score_ms * 1e-3) / 1e9
+            extras["roofline_score"] = {
+                "bound": "hbm (L2-assisted)", "unit": "GB/s", "peak": peak,
+                "achieved": (score_traffic / (score_ms * 1e-3) / 1e9) if score_traffic else None,
+                "frac": (score_traffic / (score_ms * 1e-3) / 1e9 / peak) if score_traffic else None,
+                "traffic": score_traffic, "traffic_source": score_src,
+                "operand_gbs": operand_gbs, "operand_frac": operand_gbs / peak,
+                "rows_read_per_candidate": rows_read_mean, "kernel": "fitch_score_kernel", "kernel_ms_per_batch": score_ms,
+                "note": "achieved/frac = DRAM bytes of the committed ncu capture / this run's kernel time; operand_* = "
+                        "8 B x nwords x (clean rows read) per candidate (SURVEY 8(d)), part of which L2 serves",
+            }
+            # ---- exhaustive NNI neighbourhood (deterministic_hillclimb's 2(n-3) candidates) in one call ----
+            scratch = eng.tree_create()
             nn = eng.nni_neighbourhood(tree, scratch, topo)
-        barrier()
-        wall_n = max_over_ranks(time.perf_counter() - t0)
-        nn_kernel_ms = eng.last_kernel_ms()
-        # the neighbourhood call and the dirty-path route must agree on the candidates they share
-        nn_ok = bool(np.array_equal(nn[np.asarray(cand_index)], np.asarray(got)))
+            t0 = time.perf_counter()
+            reps_n = 3
+            for _ in range(reps_n):
+                nn = eng.nni_neighbourhood(tree, scratch, topo)
+            wall_n = time.perf_counter() - t0
+            nn_ok = bool(np.array_equal(nn[np.asarray(cand_index)], np.asarray(got)))
+            extras["nni_neighbourhood"] = {
+                "candidates": int(len(nn)), "ms_per_call": wall_n / reps_n * 1e3,
+                "candidates_per_s": len(nn) / (wall_n / reps_n), "four_row_kernel_ms": eng.last_kernel_ms(),
+                "agrees_with_score_batch": nn_ok,
+                "api": "lvb_gpu_nni_neighbourhood: up-pass program + four-row kernel, host arrays in, 2(n-3) lengths out",
+            }
+        eng.close()
 
-    total_ranks = 1 if siteblock else world
-    value = total_ranks * args.steps * updates_per_pass / wall_a
-    e2e_value = total_ranks * args.steps * updates_per_pass / wall_b
-    peak, peak_src = peaks()
-    achieved = algo_bytes_per_pass / (kernel_ms * 1e-3) / 1e9
-    instr_bytes = (n - 1) * 16
+        # =================== N > 1: the weak-scaling sub-record (one whole tree per GPU) ===================
+        if siteblock and not args.no_extras:
+            eng2 = Engine(local_rank)
+            eng2.upload(enc, max_trees=1)
+            t2 = eng2.tree_create()
+            l2, r2, root2 = synthetic.random_topology(n, seed=3 + 1000 * rank)
+            eng2.commit(t2, Topology(l2, r2, root2))
+            for _ in range(warm):
+                eng2.rerun_last_batch()
+            eng2.synchronize()
+            w_all, w_mine, k_mine, _ = timed_passes(eng2, args.steps)
+            rr = gather({"rank": rank, "kernel_ms": k_mine, "stream_ms_per_step": w_mine / args.steps * 1e3})
+            extras["replicas"] = {
+                "value": world * args.steps * updates_per_pass / w_all, "unit": UNIT, "scaling": "weak",
+                "ms_per_step": w_all / args.steps * 1e3, "per_rank": rr,
+                "workload": f"one whole {n} x {m} tree per GPU per step, alignment replicated, no collective",
+            }
+            eng2.close()
 
+    # =================== SA replicates (config 5) ===================
+    if not args.no_sa and not args.no_extras:
+        try:
+            rec = sa_replicates_record(args, rank, world, local_rank, barrier, gather)
+        except Exception as exc:  # a sub-record never takes the headline down
+            rec = {"failed": f"{type(exc).__name__}: {exc}"[:300]}
+        if rank == 0:
+            extras["sa_replicates"] = rec
+
+    # =================== the line ===================
+    algo_bytes_per_pass = (3 * n - 6) * 8 * my_words  # 24 B per node-word update, SURVEY.md §8(d)
+    fused_bytes_per_pass = (2 * n - 3) * 8 * my_words  # every leaf row read once, every internal row written once
     traffic, traffic_src = traffic_from_profile()
+    if traffic is not None and world > 1:
+        traffic = traffic * my_words / nwords  # the capture is of the whole-width pass
+    phys = traffic if traffic is not None else fused_bytes_per_pass
+    achieved = phys / (kernel_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
         "ms_per_step": wall_a / args.steps * 1e3, "higher_is_better": True,
@@ -395,63 +620,56 @@ def main():
         "data": "synthetic",
         "config": {
             "workload": f"full getplen pass, {n} taxa x {m} sites (BASELINE.json configs[3] shape), "
-                        + ("site blocks over ranks + NCCL all-reduce of lengths" if siteblock else
-                           "one tree per step per GPU, alignment replicated per GPU"),
+                        + ("ONE tree, words of every row in site blocks over the ranks, partial lengths all-reduced "
+                           "inside the C-ABI" if siteblock else "one tree per step per GPU, alignment resident on the GPU"),
             "taxa": n, "sites": m, "words_per_row": nwords, "state_bytes_per_tree": (2 * n - 3) * 8 * nwords,
-            "l2": "inputs larger than L2: 1.0 GB alignment + 2.0 GB state rows per pass vs 126 MB L2",
-            "parallelism": f"{args.mode}{world}",
+            "l2": "inputs larger than L2: 1.0 GB alignment + 2.0 GB state rows per pass vs 126 MB L2"
+                  + ("" if not siteblock else f" ({3.0 / world:.2f} GB per rank)"),
+            "parallelism": ("siteblock" if siteblock else "replicas") + str(world),
         },
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": instr_bytes + 64, "d2h_bytes_per_step": 8,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (n - 1) * 16 + 64, "d2h_bytes_per_step": 8,
                 "ms_per_step": wall_b / args.steps * 1e3,
                 "api": "lvb_gpu_tree_commit(host left/right/root -> length), a different random tree every step"},
         "gpu_launches": gpu_launches,
+        "per_rank": per_rank,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "traffic_source": traffic_src, "traffic_unit": "DRAM bytes per pass (ncu)",
-                     "traffic_gbs": (traffic / (kernel_ms * 1e-3) / 1e9) if traffic else None,
-                     "traffic_frac": (traffic / (kernel_ms * 1e-3) / 1e9 / peak) if traffic else None,
-                     "peak_source": peak_src, "kernel": "fitch_exec_kernel<true> (one launch per pass)",
-                     "timing": "CUDA events on the engine's stream around each launch, averaged over the timed steps",
-                     "kernel_ms_per_pass": kernel_ms,
+                     "traffic": traffic, "traffic_source": traffic_src if traffic is not None else None,
+                     "traffic_unit": "DRAM bytes per pass (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
+                     "bytes_used": phys,
+                     "bytes_used_is": "measured DRAM traffic (ncu)" if traffic is not None else
+                                      "floor of the fused algorithm: (2n-3) rows x 8 B x words",
                      "algorithmic_bytes_per_pass": algo_bytes_per_pass,
-                     "note": "algorithmic = 24 B per node-word update (2 reads + 1 write); the kernel keeps "
-                             "intermediate rows on chip, so its real DRAM traffic is ~16 B per node-word"},
+                     "algorithmic_gbs": algo_bytes_per_pass / (kernel_ms * 1e-3) / 1e9,
+                     "algorithmic_frac": algo_bytes_per_pass / (kernel_ms * 1e-3) / 1e9 / peak,
+                     "peak_source": peak_src, "kernel": "the store kernel of the pass (one launch per pass)",
+                     "timing": "CUDA events on the engine's stream around each launch, mean over the timed steps, max over ranks",
+                     "kernel_ms_per_pass": kernel_ms,
+                     "note": "frac = physical DRAM bytes / kernel time / peak.  SURVEY 8(d)'s 24 B per node-word (2 reads + "
+                             "1 write) is kept as algorithmic_*: the kernel keeps interior operands on chip and moves ~16 B "
+                             "per node-word, so algorithmic_frac can exceed 1"},
         "clocks": clocks.summary(),
-        "sa_trees_scored_per_s": {
-            "e2e": total_ranks * reps_c * len(cands) / wall_c,
-            "device": total_ranks * len(cands) / (c_ms / max(1, c_launch) * 1e-3),
-            "batch": len(cands), "mean_dirty_nodes": dirty_mean,
-            "api": "lvb_gpu_score_batch: NNI candidates of the current tree, one launch per batch",
-        },
-        "roofline_score": {
-            "bound": "hbm (L2-assisted)", "unit": "GB/s", "peak": peak,
-            "achieved": rows_read_mean * 8 * my_words * len(cands) / (c_ms / max(1, c_launch) * 1e-3) / 1e9,
-            "frac": rows_read_mean * 8 * my_words * len(cands) / (c_ms / max(1, c_launch) * 1e-3) / 1e9 / peak,
-            "rows_read_per_candidate": rows_read_mean,
-            "kernel": "fitch_score_kernel", "kernel_ms_per_batch": c_ms / max(1, c_launch),
-            "note": "SURVEY.md 8(d): 8 B x nwords x (clean rows read) per candidate, nothing written; candidates "
-                    "of one tree share sibling rows, so part of this is served by L2 and the figure may exceed the "
-                    "HBM peak",
-        },
-        "nni_neighbourhood": {
-            "candidates": int(len(nn)), "ms_per_call": wall_n / reps_n * 1e3,
-            "candidates_per_s": total_ranks * len(nn) / (wall_n / reps_n),
-            "four_row_kernel_ms": nn_kernel_ms, "agrees_with_score_batch": bool(nn_ok),
-            "api": "lvb_gpu_nni_neighbourhood: up-pass program + four-row kernel, host arrays in, 2(n-3) lengths out",
-        },
         "length_check": int(length0), "e2e_lengths_head": [int(x) for x in lens[:3]],
     }
+    line.update(extras)
+    if siteblock:
+        line["length_expected_single_gpu"] = 1101822927 if (n, m) == (2000, 1_000_000) else None
+        if line["length_expected_single_gpu"] is not None:
+            assert int(length0) == line["length_expected_single_gpu"], (length0, line["length_expected_single_gpu"])
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            cw = (args.cpu_sample_sites + 15) // 16
-            leg = cpu_reference_leg(enc[:, :cw].copy(), left, right, root, args.cpu_sample_sites, nproc)
+            sites = cpu_workload(args, n, m)
+            cenc = enc if sites == m else np.ascontiguousarray(enc[:, : (sites + 15) // 16])
+            leg = cpu_reference_leg(cenc, sites, left, right, root, nproc, passes=8 if sites == m else 40)
             if leg is not None:
                 line["cpu_baseline"] = {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample")}
+                if sites == m:
+                    line["length_match"] = bool(leg["length"] == int(length0))
+                    line["cpu_baseline"]["length"] = leg["length"]
         except Exception as exc:  # the baseline is reported, never required
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": nproc, "kind": "reference",
                                     "sample": f"failed: {exc}"}
     if rank == 0:
         print(json.dumps(line))
-    eng.close()
     if dist is not None:
         dist.destroy_process_group()
 

@@ -20,11 +20,13 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 namespace lvbgpu
 {
 
 #define LVB_CHUNK 128 /* instructions staged in shared memory at a time */
+#define LVB_MAX_DEVICES 64
 
 /* An instruction as the inner loop wants it (decoded once per CTA while the chunk is staged):
  *   x = operand a: pool ROW number (tree offset applied); ignored if D_APREV (a = previous result)
@@ -171,6 +173,142 @@ __device__ __forceinline__ void fitch_commit_finalize_body(const FitchInstr *ins
     }
 }
 
+
+/* ---- dependent pieces in one launch (store mode) -------------------------------------------
+ * A piece waits, per column block, for the pieces whose stored rows it reads.  CTAs are numbered
+ * in the order they START (pieces are sorted by level, children before parents), so a waiting CTA
+ * never occupies a slot that a CTA it waits for still needs. */
+__device__ __forceinline__ unsigned piece_start_ticket(const ExecParams &p)
+{
+    __shared__ unsigned s_vb;
+    if (threadIdx.x == 0)
+    {
+        const unsigned t = atomicAdd(p.ticket, 1u);
+        if (t == gridDim.x - 1)
+            *p.ticket = 0u; /* every ticket is taken: ready for the next launch */
+        s_vb = t;
+    }
+    __syncthreads();
+    return s_vb;
+}
+/* The wait is bounded: after spin_limit polls (or as soon as another CTA gave up) the CTA records
+ * 1 + its piece in the mapped host word p.err and leaves; the host turns that into an error
+ * instead of a hung launch.  Returns false when the wait was abandoned. */
+__device__ __forceinline__ bool piece_wait_children(const ExecParams &p, int prog_id, int cb, int n_wait)
+{
+    __shared__ unsigned s_abort;
+    if (threadIdx.x == 0)
+    {
+        volatile unsigned *f = p.dep + (size_t)prog_id * p.n_colblocks + cb;
+        unsigned spins = 0, ab = 0;
+        while (*f < (unsigned)n_wait)
+        {
+            __nanosleep(100);
+            if ((++spins & 1023u) == 0u && (spins >= p.spin_limit || *(volatile unsigned *)p.err != 0u))
+            {
+                ab = 1u;
+                break;
+            }
+        }
+        if (ab)
+            atomicCAS(p.err, 0u, 1u + (unsigned)prog_id);
+        else
+        {
+            *f = 0u;
+            __threadfence();
+        }
+        s_abort = ab;
+    }
+    __syncthreads();
+    return s_abort == 0u;
+}
+/* after the CTA's last row store: let the piece that reads this piece's top row go on */
+__device__ __forceinline__ void piece_release_parent(const ExecParams &p, const FitchProgram &prog, int cb)
+{
+    if (prog.parent < 0)
+        return;
+    __syncthreads(); /* every thread's row stores are ordered before the release below */
+    if (threadIdx.x == 0)
+    {
+        __threadfence();
+        atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
+    }
+}
+/* fused finalize of a launch of dependent pieces: the column block of a piece that finishes last
+ * folds that piece's counts into chg / sum_chg (what fitch_commit_finalize_body does for a whole
+ * program), and the piece of a candidate that is folded last publishes the candidate's length —
+ * no second launch, and the folding of the lower pieces overlaps the upper ones.
+ * p.done[q] counts the column blocks of piece q, p.done[n_prog + k] the pieces of candidate k,
+ * p.totals[k] collects the root-step counts of candidate k; all are left zero. */
+__device__ __forceinline__ void piece_finalize(const ExecParams &p, const FitchInstr *instrs, const FitchProgram &prog,
+                                               int prog_id)
+{
+    __shared__ unsigned s_last;
+    __shared__ long long s_delta, s_root;
+    const int tid = threadIdx.x;
+    __syncthreads(); /* this CTA's count atomics are issued */
+    if (tid == 0)
+    {
+        __threadfence();
+        const unsigned last = atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u ? 1u : 0u;
+        if (last)
+            p.done[prog_id] = 0u;
+        s_last = last;
+        s_delta = 0;
+        s_root = 0;
+    }
+    __syncthreads();
+    if (!s_last)
+        return;
+    __threadfence();
+    int32_t *tchg = p.chg_rw + (int64_t)prog.tree * p.n_internal;
+    long long delta = 0, rootc = 0;
+    for (int i = tid; i < prog.n_instr; i += blockDim.x)
+    {
+        const int node = instrs[prog.instr_begin + i].node;
+        const int c = __ldcg(&p.cnts[prog.instr_begin + i]);
+        p.cnts[prog.instr_begin + i] = 0; /* ready for the next store batch */
+        if (node >= 0)
+        {
+            delta += (long long)c - tchg[node - p.n];
+            tchg[node - p.n] = c;
+        }
+        else
+            rootc += c; /* root step: never cached (TreeEvaluation.c:238-264) */
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        delta += __shfl_xor_sync(0xffffffffu, delta, o);
+        rootc += __shfl_xor_sync(0xffffffffu, rootc, o);
+    }
+    if ((tid & 31) == 0)
+    {
+        if (delta)
+            atomicAdd((unsigned long long *)&s_delta, (unsigned long long)delta);
+        if (rootc)
+            atomicAdd((unsigned long long *)&s_root, (unsigned long long)rootc);
+    }
+    __syncthreads();
+    if (tid == 0)
+    {
+        const int k = prog.pad1;
+        const int ctree = p.cand[k].tree;
+        const unsigned n_pieces = (unsigned)p.cand[k].n_wait;
+        if (s_delta)
+            atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], (unsigned long long)s_delta);
+        if (s_root)
+            atomicAdd(&p.totals[k], (unsigned long long)s_root);
+        __threadfence();
+        if (atomicAdd(&p.done[p.n_prog + k], 1u) == n_pieces - 1u)
+        {
+            __threadfence();
+            p.done[p.n_prog + k] = 0u;
+            const long long sum = (long long)atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], 0ull);
+            p.out[k] = sum + (long long)atomicExch(&p.totals[k], 0ull);
+        }
+    }
+}
+
 template <bool PER_NODE>
 __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const FitchProgram *progs, const FitchInstr *instrs)
 {
@@ -185,20 +323,7 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
     const int nwarps = nthr >> 5;
     unsigned vb = blockIdx.x;
     if (PER_NODE && p.dep)
-    {
-        /* dependent pieces in one launch: a piece waits for the pieces below it, so CTAs are
-         * numbered in the order they START (children are sorted before their parents) */
-        __shared__ unsigned s_vb;
-        if (tid == 0)
-        {
-            const unsigned t = atomicAdd(p.ticket, 1u);
-            if (t == gridDim.x - 1)
-                *p.ticket = 0u; /* every ticket is taken: ready for the next launch */
-            s_vb = t;
-        }
-        __syncthreads();
-        vb = s_vb;
-    }
+        vb = piece_start_ticket(p);
     /* independent programs: column-block-major, CTAs of different programs over the same columns
      * run together, so rows shared between candidates of one tree are served from L2.
      * dependent pieces: piece-major (pieces are sorted by level), so that by the time a piece
@@ -207,18 +332,8 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
     const int prog_id = piece_major ? vb / p.n_colblocks : vb % p.n_prog;
     const int cb = piece_major ? vb % p.n_colblocks : vb / p.n_prog;
     const FitchProgram prog = progs[prog_id];
-    if (PER_NODE && p.dep && prog.n_wait > 0)
-    {
-        if (tid == 0)
-        {
-            volatile unsigned *f = p.dep + (size_t)prog_id * p.n_colblocks + cb;
-            while (*f < (unsigned)prog.n_wait)
-                __nanosleep(100);
-            *f = 0u;
-            __threadfence();
-        }
-        __syncthreads();
-    }
+    if (PER_NODE && p.dep && prog.n_wait > 0 && !piece_wait_children(p, prog_id, cb, prog.n_wait))
+        return;
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
@@ -341,14 +456,12 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
 
     if (PER_NODE)
     { /* store mode: lengths come from the per-instruction counts (commit_finalize) */
-        if (p.dep && prog.parent >= 0)
+        if (p.dep)
         {
-            __syncthreads(); /* every thread's row stores are ordered before the release below */
-            if (tid == 0)
-            {
-                __threadfence();
-                atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
-            }
+            piece_release_parent(p, prog, cb);
+            if (p.fused_finalize)
+                piece_finalize(p, instrs, prog, prog_id);
+            return;
         }
         if (p.fused_finalize)
         { /* single-level batch (program == candidate): the column block that finishes last folds the
@@ -495,10 +608,17 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     __shared__ unsigned long long s_total;
 
     /* column-block-major: CTAs of different programs over the same columns run together, so
-     * rows shared between candidates of one tree are served from L2 */
-    const int prog_id = blockIdx.x % p.n_prog;
-    const int cb = blockIdx.x / p.n_prog;
+     * rows shared between candidates of one tree are served from L2.  Dependent pieces of a store
+     * launch: piece-major in start order, see fitch_exec_body */
+    const bool piece_major = STORE && p.dep;
+    unsigned vb = blockIdx.x;
+    if (piece_major)
+        vb = piece_start_ticket(p);
+    const int prog_id = piece_major ? vb / p.n_colblocks : vb % p.n_prog;
+    const int cb = piece_major ? vb % p.n_colblocks : vb / p.n_prog;
     const FitchProgram prog = progs[prog_id];
+    if (piece_major && prog.n_wait > 0 && !piece_wait_children(p, prog_id, cb, prog.n_wait))
+        return;
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
@@ -621,6 +741,13 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
 #undef LVB_ISSUE
     }
 
+    if (STORE && p.dep)
+    {
+        piece_release_parent(p, prog, cb);
+        if (p.fused_finalize)
+            piece_finalize(p, instrs, prog, prog_id);
+        return;
+    }
     if (STORE && !p.fused_finalize)
         return; /* the finalize launch follows */
     if (STORE)
@@ -714,6 +841,15 @@ __global__ void __launch_bounds__(256)
     fitch_score_body<STORE, LVB_PF_DEEP>(p, b.prog, b.instr);
 }
 
+/* store launches of dependent pieces (a first pass, a re-root of a big tree) through the cp.async
+ * ring with PF instructions of look-ahead: every HBM operand of a piece is a row that was complete
+ * before the piece started, so its loads can run any distance ahead of the arithmetic */
+template <int PF>
+__global__ void __launch_bounds__(256) fitch_store_pipe_kernel(const ExecParams p)
+{
+    fitch_score_body<true, PF>(p, p.prog, p.instr);
+}
+
 static size_t exec_smem_bytes(bool per_node, int n_slots, int block)
 {
     return (size_t)(LVB_CHUNK + 2 + (per_node ? LVB_CHUNK * 8 / 4 : 0) + (size_t)n_slots * block) * sizeof(uint4);
@@ -757,7 +893,19 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
     const bool deep = deep_enabled() && small_grid(grid);
     cudaError_t e;
-    if (per_node && !p.dep && deep)
+    if (per_node && p.dep && p.pipe_pf > 0)
+    {
+        const int pf = p.pipe_pf >= 7 ? 7 : p.pipe_pf >= 5 ? 5 : p.pipe_pf >= 3 ? 3 : 2;
+        const size_t sm = pipe_smem_bytes(true, pf, p.n_slots, block);
+        void (*k)(const ExecParams) = pf == 7   ? fitch_store_pipe_kernel<7>
+                                      : pf == 5 ? fitch_store_pipe_kernel<5>
+                                      : pf == 3 ? fitch_store_pipe_kernel<3>
+                                                : fitch_store_pipe_kernel<2>;
+        if ((e = want_smem(k, sm)) != cudaSuccess)
+            return e;
+        k<<<grid, block, sm, stream>>>(p);
+    }
+    else if (per_node && !p.dep && deep)
     {
         const size_t sm = pipe_smem_bytes(true, LVB_PF_DEEP, p.n_slots, block);
         if ((e = want_smem(fitch_pipe_kernel<true>, sm)) != cudaSuccess)
@@ -1034,15 +1182,27 @@ __global__ void __launch_bounds__(256) pack_dna_kernel(const unsigned char *text
 cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int64_t word_begin, int64_t word_count,
                             uint4 *pool, int64_t stride_u4, int *bad, cudaStream_t stream)
 {
-    static bool table_done = false;
-    if (!table_done)
+    /* __constant__ memory is per device: the table is installed once on every GPU this process
+     * packs an alignment on (lvb_gpu -D 2 opens its contexts from several host threads) */
+    static std::mutex table_mutex;
+    static bool table_done[LVB_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return e;
     {
-        unsigned char t[256];
-        build_state_table(t);
-        cudaError_t e = cudaMemcpyToSymbol(c_state_of, t, 256);
-        if (e != cudaSuccess)
-            return e;
-        table_done = true;
+        std::lock_guard<std::mutex> lock(table_mutex);
+        if (dev < 0 || dev >= LVB_MAX_DEVICES || !table_done[dev])
+        {
+            unsigned char t[256];
+            build_state_table(t);
+            if ((e = cudaMemcpyToSymbolAsync(c_state_of, t, 256, 0, cudaMemcpyHostToDevice, stream)) != cudaSuccess)
+                return e;
+            if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) /* t lives on this stack frame */
+                return e;
+            if (dev >= 0 && dev < LVB_MAX_DEVICES)
+                table_done[dev] = true;
+        }
     }
     dim3 grid((unsigned)((word_count + 255) / 256), (unsigned)(n < 65535 ? n : 65535));
     pack_dna_kernel<<<grid, 256, 0, stream>>>(text, n, m, word_begin, word_count, pool, stride_u4, bad);

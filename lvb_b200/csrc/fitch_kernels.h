@@ -29,11 +29,22 @@ struct ExecParams
     long long *out;              /* [n_prog] score mode: the length, written by the last column block
                                   * (pinned host memory mapped into the device, or device memory) */
     int32_t *cnts;               /* [n_instr of batch] per-instruction counts (store mode); zeroed by finalize */
-    unsigned *ticket;            /* store mode, dependent pieces: CTA start-order counter (left zero by the kernel) */
+    unsigned *ticket;            /* store mode, dependent pieces: ticket[0] CTA start-order counter (left zero by the
+                                  * kernel) */
     unsigned *dep;               /* store mode: [n_prog][n_colblocks] finished child pieces per column block
                                   * (left zero by the kernel); NULL: pieces of the launch are independent */
-    int32_t fused_finalize;      /* store mode, single-level batch: the last column block of a program runs the
-                                  * finalize step (chg_rw / sum_chg_rw / out) instead of a second launch */
+    int32_t fused_finalize;      /* store mode: the finalize step (chg_rw / sum_chg_rw / out) runs inside the Fitch
+                                  * kernel instead of a second launch.  Single-level batch: by the last column block
+                                  * of a program.  Dependent pieces: the last column block of a PIECE folds that
+                                  * piece's counts, the last piece of a candidate publishes its length */
+    const FitchProgram *cand;    /* store mode, dependent pieces, fused finalize: [n_cand] one record per candidate;
+                                  * cand[k].n_wait = number of pieces of candidate k; a piece names its candidate
+                                  * in FitchProgram::pad1 */
+    int32_t n_cand;
+    int32_t pipe_pf;             /* store mode, dependent pieces: 0 = register-pipelined kernel (fitch_exec_kernel),
+                                  * 2/3/5/7 = cp.async ring with that many instructions of look-ahead */
+    unsigned *err;               /* mapped host word: 1 + piece whose dependency wait was abandoned (0 = none) */
+    unsigned spin_limit;         /* polls of a dependency counter after which the wait is abandoned */
     int32_t *chg_rw;             /* = chg, writable (fused finalize) */
     long long *sum_chg_rw;       /* = sum_chg, writable */
     const int32_t *chg;          /* [trees][I] cached per-node change counts */

@@ -158,6 +158,12 @@ struct lvb_gpu_ctx
     bool fuse_ok = true;     /* single-level store batches finalize inside the Fitch kernel (LVB_GPU_FUSE=0: own launch) */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
+    int store_pf = 0;                                  /* dependent-piece store launches: 0 = register-pipelined kernel,
+                                                        * 2/3/5/7 = cp.async ring with that look-ahead (LVB_GPU_STORE_PF) */
+    unsigned spin_limit = 1u << 26;                    /* polls (>= 100 ns each) before a dependency wait is abandoned */
+    unsigned *h_err = nullptr, *d_err = nullptr;       /* mapped host word the kernels report an abandoned wait in */
+    int fault_dep = 0;                                 /* LVB_GPU_FAULT=dep: the next dependent launch gets a wait that
+                                                        * can never be satisfied (test of the bounded wait) */
     bool last_dep = false;
     std::vector<int32_t> owner_stamp, owner_piece;     /* (tree, node) -> piece that stores it in the current batch */
     int32_t owner_cur = 0;
@@ -309,6 +315,31 @@ static int drain_kernel_events(lvb_gpu_ctx *c)
     return 0;
 }
 
+/* after a host-side wait: did a kernel abandon a dependency wait?  If so the scratch counters of
+ * that launch are in an unknown state: clear them, forget the resident batch, report. */
+static int check_device_error(lvb_gpu_ctx *c)
+{
+    if (!c->h_err || *c->h_err == 0u)
+        return 0;
+    const unsigned piece = *c->h_err - 1u;
+    cudaStreamSynchronize(c->stream);
+    *c->h_err = 0u;
+    if (c->d_dep)
+        cudaMemsetAsync(c->d_dep, 0, (c->cap_dep + 1) * sizeof(unsigned), c->stream);
+    if (c->d_totals)
+        cudaMemsetAsync(c->d_totals, 0, c->cap_tot * sizeof(unsigned long long), c->stream);
+    if (c->d_done)
+        cudaMemsetAsync(c->d_done, 0, c->cap_tot * sizeof(unsigned), c->stream);
+    if (c->d_cnts)
+        cudaMemsetAsync(c->d_cnts, 0, c->cap_cnts * sizeof(int32_t), c->stream);
+    cudaStreamSynchronize(c->stream);
+    c->last_K = 0;
+    /* the trees of the batch hold partly written rows: they must be evaluated from scratch */
+    std::fill(c->tree_ready.begin(), c->tree_ready.end(), 0);
+    return fail("device error: piece %u gave up waiting for the rows of the pieces below it (a CTA of the launch "
+                "faulted or never ran); every device tree must be committed again with n_dirty < 0", piece);
+}
+
 /* launch the batch that is resident in staging slot c->last_slot */
 static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always = false, bool defer = false)
 {
@@ -343,9 +374,15 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     p.sum_chg = c->sum_chg;
     p.chg_rw = c->chg;
     p.sum_chg_rw = c->sum_chg;
-    /* a store batch without pieces: program == candidate, the kernel finalizes by itself */
-    const bool fused = store && !c->last_dep && c->levels.size() == 1 && c->last_n_prog == (size_t)K && c->fuse_ok;
+    /* a store batch without pieces (program == candidate) or one launch of dependent pieces: the
+     * kernel finalizes by itself */
+    const bool fused = store && c->fuse_ok && c->levels.size() == 1 && (c->last_dep || c->last_n_prog == (size_t)K);
     p.fused_finalize = fused ? 1 : 0;
+    p.cand = d_cand;
+    p.n_cand = (int32_t)K;
+    p.pipe_pf = c->store_pf;
+    p.err = c->d_err;
+    p.spin_limit = c->spin_limit;
 
     const double ts0 = c->profile ? wall_now() : 0;
     int slot = -1;
@@ -417,6 +454,8 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
         if (c->profile)
             c->t_wait += wall_now() - ts1;
         st.pending = false;
+        if (check_device_error(c))
+            return 1;
         for (int64_t k = 0; k < K; k++)
             lengths[k] = (int64_t)st.h_len[k];
     }
@@ -537,7 +576,7 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     }
     if (n_instr > (size_t)INT32_MAX)
         return fail("batch too large: %zu instructions", n_instr);
-    if (ensure_device_arrays(c, n_instr, (size_t)K))
+    if (ensure_device_arrays(c, n_instr, n_prog + (size_t)K))
         return 1;
     const size_t bytes = (n_prog + (size_t)K) * sizeof(FitchProgram) + n_instr * sizeof(FitchInstr);
     int slot;
@@ -555,10 +594,12 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         memcpy(h_instr + off, ins.data(), ins.size() * sizeof(FitchInstr));
         for (const auto &pc : c->c_pieces[k])
         {
-            c->prog.push_back(FitchProgram{(int32_t)(off + pc.instr_begin), pc.n_instr, trees[k], pc.level, -1, 0, 0, 0});
+            c->prog.push_back(FitchProgram{(int32_t)(off + pc.instr_begin), pc.n_instr, trees[k], pc.level, -1, 0, 0, (int32_t)k});
             multilevel = multilevel || pc.level != 0;
         }
-        h_cand[k] = FitchProgram{(int32_t)off, (int32_t)ins.size(), trees[k], store ? 1 : 0, -1, 0, 0, 0};
+        /* n_wait of a candidate record: the number of its pieces (fused finalize of dependent pieces) */
+        h_cand[k] = FitchProgram{(int32_t)off, (int32_t)ins.size(), trees[k], store ? 1 : 0, -1,
+                                 (int32_t)c->c_pieces[k].size(), 0, 0};
         off += ins.size();
     }
     /* pieces sorted by level.  Either one launch per level, or (default) ONE launch in which a
@@ -639,6 +680,11 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
                 CU(cudaMalloc(&c->d_dep, (cap + 1) * sizeof(unsigned)));
                 CU(cudaMemsetAsync(c->d_dep, 0, (cap + 1) * sizeof(unsigned), c->stream));
                 c->cap_dep = cap;
+            }
+            if (c->fault_dep)
+            { /* test hook: the top piece waits for a child that does not exist */
+                c->prog.back().n_wait++;
+                c->fault_dep = 0;
             }
             c->last_dep = true;
             c->levels.push_back({0, (int32_t)c->prog.size()});
@@ -824,6 +870,17 @@ extern "C"
             c->timing = true;
         const char *ll = getenv("LVB_GPU_LEVEL_LAUNCHES");
         c->level_launches = ll && atoi(ll) != 0;
+        const char *spf = getenv("LVB_GPU_STORE_PF");
+        if (spf)
+            c->store_pf = atoi(spf);
+        const char *sl = getenv("LVB_GPU_SPIN_LIMIT");
+        if (sl && atoll(sl) >= 1024)
+            c->spin_limit = (unsigned)std::min<long long>(atoll(sl), 0xffffffffll);
+        const char *ft = getenv("LVB_GPU_FAULT");
+        c->fault_dep = ft && strcmp(ft, "dep") == 0;
+        CU(cudaHostAlloc(&c->h_err, sizeof(unsigned), cudaHostAllocMapped));
+        *c->h_err = 0u;
+        CU(cudaHostGetDevicePointer(&c->d_err, c->h_err, 0));
         const char *b = getenv("LVB_GPU_BLOCK");
         if (b)
         {
@@ -861,6 +918,8 @@ extern "C"
         cudaFree(c->d_nni);
         if (c->h_nni)
             cudaFreeHost(c->h_nni);
+        if (c->h_err)
+            cudaFreeHost(c->h_err);
         for (auto &st : c->ring)
         {
             cudaFreeHost(st.h);
@@ -1131,6 +1190,11 @@ extern "C"
         if (c->profile)
             c->t_wait += wall_now() - t0;
         st.pending = false;
+        if (check_device_error(c))
+        {
+            st.unclaimed = 0;
+            return 1;
+        }
         for (int64_t k = 0; k < st.unclaimed; k++)
             lengths[k] = (int64_t)st.h_len[k];
         st.unclaimed = 0;
@@ -1253,6 +1317,11 @@ extern "C"
             p.chg_rw = c->chg;
             p.sum_chg_rw = c->sum_chg;
             p.fused_finalize = 0;
+            p.cand = nullptr;
+            p.n_cand = 0;
+            p.pipe_pf = 0;
+            p.err = c->d_err;
+            p.spin_limit = c->spin_limit;
             const size_t level_first[2] = {0, n_level0}, level_count[2] = {n_level0, n_pcs - n_level0};
             for (int lv = 0; lv < 2; lv++)
             {
@@ -1491,7 +1560,7 @@ extern "C"
             return fail("lvb_gpu_synchronize: null argument");
         CU(cudaSetDevice(c->device));
         CU(cudaStreamSynchronize(c->stream));
-        return 0;
+        return check_device_error(c);
     }
 
     int lvb_gpu_compile_schedule(int64_t n, const lvb_gpu_topology *topo, int store, int32_t *instr, int64_t cap,

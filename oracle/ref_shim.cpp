@@ -90,6 +90,51 @@ extern "C"
 		return h;
 	}
 
+	/* The same for an alignment that is ALREADY packed (DNAToBinary's layout, n x words_per_row(m)
+	 * words): used to time getplen at 2000 x 1M, where making 2 GB of text and scanning it twice
+	 * (matchange: constchar + MinimumTreeLength) would add minutes of set-up.  The fields matchange
+	 * derives from m (DataOperations.c:336-340) are set by the reference's own functions; the row
+	 * strings stay empty and min_len_tree is not computed (getplen reads neither). */
+	void *ref_msa_from_packed(long n, long m, const Lvb_bit_length *enc, int nthreads)
+	{
+		RefHandle *h = (RefHandle *)calloc(1, sizeof(RefHandle));
+		defaults_params(&h->rc);
+		h->rc.n_processors_available = nthreads;
+		h->rc.verbose = LVB_FALSE;
+		lvb_initialize();
+		h->msa = (Dataptr)calloc(1, sizeof(DataStructure));
+		Dataptr d = h->msa;
+		d->m = m;
+		d->original_m = m;
+		d->n = n;
+		d->numberofpossiblebranches = 2 * n - 3;
+		d->max_length_seq_name = 10;
+		d->nsets = n - 3;
+		d->mssz = n - 2;
+		d->rowtitle = (char **)malloc(n * sizeof(char *));
+		d->row = (char **)malloc(n * sizeof(char *));
+		for (long i = 0; i < n; i++)
+		{
+			d->rowtitle[i] = (char *)calloc(16, 1);
+			snprintf(d->rowtitle[i], 16, "T%ld", i);
+			d->row[i] = (char *)calloc(1, 1);
+		}
+		d->bytes = bytes_per_row(d->m);
+		d->nwords = words_per_row(d->m);
+		d->tree_bytes = tree_bytes(d);
+		d->tree_bytes_without_sitestate = tree_bytes_without_sitestate(d);
+		d->min_len_tree = 0;
+		calc_distribution_processors(d, h->rc); /* MemoryOperations.c:135 */
+		h->enc = (Lvb_bit_length **)malloc(n * sizeof(Lvb_bit_length *));
+		for (long i = 0; i < n; i++)
+		{
+			h->enc[i] = (Lvb_bit_length *)malloc(d->bytes);
+			memcpy(h->enc[i], enc + i * d->nwords, d->bytes);
+		}
+		alloc_memory_to_getplen(d, &h->todo, &h->sums, &h->runs);
+		return h;
+	}
+
 	void ref_msa_free(void *hv)
 	{
 		RefHandle *h = (RefHandle *)hv;

@@ -343,3 +343,35 @@ int lvb_gpu_synchronize(lvb_gpu_ctx *c)
     (void)c;
     return 0;
 }
+
+/* parity helpers the Python binding (lvb_b200/gpu.py: Engine) calls; they let the logic of the
+ * `-m gpu` tests be tried on a CPU box by pointing the binding at this library */
+int lvb_gpu_set_timing(lvb_gpu_ctx *c, int on)
+{
+    (void)c;
+    (void)on;
+    return 0;
+}
+int lvb_gpu_download_row(lvb_gpu_ctx *c, int tree, int64_t node, uint64_t *out)
+{
+    if (node < 0 || node >= c->B)
+        return fail("node out of range");
+    memcpy(out, (node < c->n ? c->leaves : c->rows[tree]) + (size_t)node * c->nwords, (size_t)c->nwords * 8);
+    return 0;
+}
+/* entry points the mock does not model: present so that the binding loads, failing loudly */
+#define ABSENT return fail("not modelled by the mock device")
+int lvb_gpu_comm_init(lvb_gpu_ctx *c, int nranks, int rank, const void *id) { (void)c; (void)nranks; (void)rank; (void)id; ABSENT; }
+int lvb_gpu_comm_unique_id(void *id) { (void)id; ABSENT; }
+/* the host-only compilers (lvb_gpu_compile_schedule/_pieces/_up_pass) are NOT overridden: the host
+ * layer uses the product's own, which need no device */
+int lvb_gpu_kernel_time(lvb_gpu_ctx *c, double *ms, int64_t *k, int reset) { (void)c; (void)ms; (void)k; (void)reset; ABSENT; }
+int lvb_gpu_last_kernel_ms(lvb_gpu_ctx *c, float *ms) { (void)c; (void)ms; ABSENT; }
+int lvb_gpu_matrix_pack(lvb_gpu_ctx *c, int64_t n, int64_t m, const char *const *rows, int64_t wb, int64_t wc, int64_t mt)
+{ (void)c; (void)n; (void)m; (void)rows; (void)wb; (void)wc; (void)mt; ABSENT; }
+int lvb_gpu_rerun_last_batch(lvb_gpu_ctx *c, int64_t *lengths) { (void)c; (void)lengths; ABSENT; }
+void *lvb_gpu_stream(lvb_gpu_ctx *c)
+{
+    (void)c;
+    return NULL;
+}

@@ -65,6 +65,8 @@ def ref() -> C.CDLL:
         L.ref_msa_load.argtypes = [C.c_char_p, C.c_int, C.c_int]
         L.ref_msa_from_rows.restype = _vp
         L.ref_msa_from_rows.argtypes = [_l, _l, C.POINTER(C.c_char_p), C.c_int]
+        L.ref_msa_from_packed.restype = _vp
+        L.ref_msa_from_packed.argtypes = [_l, _l, _vp, C.c_int]
         L.ref_msa_free.argtypes = [_vp]
         L.ref_msa_dims.argtypes = [_vp, _lp]
         L.ref_msa_set_threads.argtypes = [_vp, C.c_int]
@@ -126,6 +128,13 @@ class RefMSA:
         rows = [r if isinstance(r, bytes) else bytes(r) for r in rows]
         arr = (C.c_char_p * len(rows))(*rows)
         return cls(ref().ref_msa_from_rows(len(rows), len(rows[0]), arr, threads))
+
+    @classmethod
+    def from_packed(cls, enc: np.ndarray, m: int, threads: int = 1) -> "RefMSA":
+        """an alignment that is already packed (no text, no matchange): timing at large shapes"""
+        enc = np.ascontiguousarray(enc, dtype=np.uint64)
+        assert enc.shape[1] == (m + 15) // 16
+        return cls(ref().ref_msa_from_packed(enc.shape[0], m, enc.ctypes.data, threads))
 
     def set_threads(self, threads: int) -> None:
         self.L.ref_msa_set_threads(self.h, threads)
