@@ -512,9 +512,23 @@ def main():
             eng.commit(tree, topos[s])
         barrier()
         t0 = time.perf_counter()
-        lens = [eng.commit(tree, tp) for tp in topos]
+        # what a caller that scores many trees does: tree s+1 is compiled and enqueued (lvb_gpu_commit_batch_submit)
+        # while the device works on tree s; every length is read back (lvb_gpu_batch_wait)
+        lens, inflight = [], []
+        for tp in topos:
+            inflight.append(eng.commit_batch_submit([tree], [tp]))
+            if len(inflight) > 2:
+                lens.append(int(eng.batch_wait(inflight.pop(0))[0]))
+        while inflight:
+            lens.append(int(eng.batch_wait(inflight.pop(0))[0]))
         barrier()
         wall_b = max_over_ranks(time.perf_counter() - t0)
+        # the same, one tree at a time (submit, wait, next): the latency of a single call
+        t0 = time.perf_counter()
+        for tp in topos[: max(1, args.steps // 4)]:
+            eng.commit(tree, tp)
+        barrier()
+        wall_b_sync = max_over_ranks(time.perf_counter() - t0) / max(1, args.steps // 4)
 
         total_ranks = 1 if siteblock else world
         value = total_ranks * args.steps * updates_per_pass / wall_a
@@ -628,8 +642,10 @@ def main():
             "parallelism": ("siteblock" if siteblock else "replicas") + str(world),
         },
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (n - 1) * 16 + 64, "d2h_bytes_per_step": 8,
-                "ms_per_step": wall_b / args.steps * 1e3,
-                "api": "lvb_gpu_tree_commit(host left/right/root -> length), a different random tree every step"},
+                "ms_per_step": wall_b / args.steps * 1e3, "ms_per_call_unpipelined": wall_b_sync * 1e3,
+                "api": "lvb_gpu_commit_batch_submit(host left/right/root) + lvb_gpu_batch_wait(-> length), a different "
+                       "random tree every step, up to 3 calls in flight (host compile of tree s+1 under the kernel of "
+                       "tree s); ms_per_call_unpipelined = lvb_gpu_tree_commit one call at a time"},
         "gpu_launches": gpu_launches,
         "per_rank": per_rank,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -134,6 +134,13 @@ int lvb_gpu_score_batch_submit(lvb_gpu_ctx *ctx, int64_t n_cand, const int *tree
                                int *ticket);
 int lvb_gpu_batch_wait(lvb_gpu_ctx *ctx, int ticket, int64_t *lengths);
 
+/* lvb_gpu_commit_batch in the same two halves: a caller that evaluates many independent trees (start
+ * trees of replicates, the trees of a stack) compiles and enqueues tree k+1 while the device still
+ * works on tree k, and collects the lengths with lvb_gpu_batch_wait.  Commits run in submission
+ * order on the context's stream. */
+int lvb_gpu_commit_batch_submit(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                int *ticket);
+
 /* The same two calls for a caller that compiles the programs itself, on ITS threads: a driver of
  * many SA chains generates a chain's proposals and compiles them (lvb_gpu_compile_schedule, which
  * is thread-safe and keeps one compiler per calling thread) in the same parallel loop, so that the

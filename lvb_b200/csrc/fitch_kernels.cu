@@ -1281,4 +1281,54 @@ cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m,
     return cudaGetLastError();
 }
 
+/* ---- all-reduce of partial lengths over peer memory (site-block mode) ---- */
+__global__ void __launch_bounds__(256) p2p_allreduce_kernel(const __grid_constant__ P2PParams q)
+{
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= q.K)
+        return;
+    const unsigned long long v = (unsigned long long)q.in[k];
+    const unsigned long long tag = (unsigned long long)q.seq << 32;
+    const unsigned long long w0 = tag | (v & 0xffffffffull), w1 = tag | (v >> 32);
+    const size_t mine = 2 * (((size_t)q.slot * q.nranks + q.rank) * (size_t)q.kmax + (size_t)k);
+    for (int r = 0; r < q.nranks; r++)
+    {
+        /* start with the next rank so that the ranks do not all write to rank 0 first */
+        const int d = (q.rank + 1 + r) % q.nranks;
+        volatile unsigned long long *dst = q.peer[d] + mine;
+        dst[0] = w0;
+        dst[1] = w1;
+    }
+    long long sum = 0;
+    for (int r = 0; r < q.nranks; r++)
+    {
+        const volatile unsigned long long *e =
+            q.peer[q.rank] + 2 * (((size_t)q.slot * q.nranks + r) * (size_t)q.kmax + (size_t)k);
+        unsigned long long a = e[0], b = e[1];
+        unsigned spins = 0;
+        while ((a >> 32) != q.seq || (b >> 32) != q.seq)
+        {
+            __nanosleep(50);
+            if ((++spins & 1023u) == 0u && (spins >= q.spin_limit || *(volatile unsigned *)q.err != 0u))
+            {
+                atomicCAS(q.err, 0u, 0x80000000u | (unsigned)r);
+                return;
+            }
+            a = e[0];
+            b = e[1];
+        }
+        sum += (long long)(((b & 0xffffffffull) << 32) | (a & 0xffffffffull));
+    }
+    q.out[k] = sum;
+    if (q.out2)
+        q.out2[k] = sum;
+}
+
+cudaError_t launch_p2p_allreduce(const P2PParams &p, cudaStream_t stream)
+{
+    const unsigned grid = (unsigned)((p.K + 255) / 256);
+    p2p_allreduce_kernel<<<grid, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
 } // namespace lvbgpu

@@ -104,5 +104,31 @@ cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int
 cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *sums,
                                 cudaStream_t stream);
 
+/* Sum of K int64 over the ranks of a site-block run through PEER MEMORY (NVLink / NVSwitch loads and
+ * stores between the GPUs of one box) instead of a collective library call: every rank owns a slab
+ * that all ranks have mapped (CUDA IPC); rank r writes its K partial values into its own row of slot
+ * (seq mod slots) of EVERY rank's slab, then sums the nranks rows that arrived in its own slab.
+ * An entry is two 8-byte words {low half | seq << 32}, {high half | seq << 32}: an 8-byte store is
+ * atomic, so the sequence number doubles as the arrival flag (no separate flag, no fence between
+ * data and flag).  Every rank adds the rows in the same order.  A rank can run at most one call
+ * ahead of the slowest one, so two slots would do; there are four. */
+#define LVB_P2P_MAX_RANKS 16
+#define LVB_P2P_SLOTS 4
+struct P2PParams
+{
+    unsigned long long *peer[LVB_P2P_MAX_RANKS]; /* peer[r]: rank r's slab as mapped on this rank (peer[rank] = own) */
+    int32_t nranks, rank;
+    int32_t slot;               /* seq % LVB_P2P_SLOTS */
+    uint32_t seq;               /* call number, never 0 */
+    int64_t kmax;               /* entries per row */
+    int64_t K;
+    const long long *in;        /* [K] this rank's partial values */
+    long long *out;             /* [K] the sums (may alias in) */
+    long long *out2;            /* optional second destination (mapped host memory), or NULL */
+    unsigned *err;              /* mapped host word: set to 0x80000000 | rank that did not arrive */
+    unsigned spin_limit;
+};
+cudaError_t launch_p2p_allreduce(const P2PParams &p, cudaStream_t stream);
+
 } // namespace lvbgpu
 #endif

@@ -67,12 +67,14 @@ struct NcclApi
     int (*GetUniqueId)(void *) = nullptr;
     int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
     int (*CommDestroy)(void *) = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
 };
 static NcclApi g_nccl;
 enum
 {
+    kNcclInt8 = 0,
     kNcclInt32 = 2,
     kNcclInt64 = 4,
     kNcclSum = 0
@@ -94,6 +96,7 @@ static int nccl_load()
     *(void **)&g_nccl.GetUniqueId = dlsym(g_nccl.lib, "ncclGetUniqueId");
     *(void **)&g_nccl.CommInitRank = dlsym(g_nccl.lib, "ncclCommInitRank");
     *(void **)&g_nccl.AllReduce = dlsym(g_nccl.lib, "ncclAllReduce");
+    *(void **)&g_nccl.AllGather = dlsym(g_nccl.lib, "ncclAllGather");
     *(void **)&g_nccl.CommDestroy = dlsym(g_nccl.lib, "ncclCommDestroy");
     *(void **)&g_nccl.GetErrorString = dlsym(g_nccl.lib, "ncclGetErrorString");
     if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy)
@@ -193,6 +196,13 @@ struct lvb_gpu_ctx
 
     void *comm = nullptr;
     int nranks = 1, rank = 0;
+    /* all-reduce of partial lengths through peer memory (see fitch_kernels.h: P2PParams); falls back to
+     * ncclAllReduce when the slabs cannot be mapped (LVB_GPU_P2P=0 forces that) */
+    bool p2p = false;
+    unsigned long long *p2p_slab = nullptr;
+    unsigned long long *p2p_peer[LVB_P2P_MAX_RANKS] = {};
+    int64_t p2p_kmax = 8192;
+    uint32_t p2p_seq = 0;
 
     /* LVB_GPU_PROFILE=1: host seconds per stage of commit/score calls, printed at shutdown */
     bool profile = false;
@@ -321,7 +331,8 @@ static int check_device_error(lvb_gpu_ctx *c)
 {
     if (!c->h_err || *c->h_err == 0u)
         return 0;
-    const unsigned piece = *c->h_err - 1u;
+    const unsigned code = *c->h_err;
+    const unsigned piece = code - 1u;
     cudaStreamSynchronize(c->stream);
     *c->h_err = 0u;
     if (c->d_dep)
@@ -336,8 +347,48 @@ static int check_device_error(lvb_gpu_ctx *c)
     c->last_K = 0;
     /* the trees of the batch hold partly written rows: they must be evaluated from scratch */
     std::fill(c->tree_ready.begin(), c->tree_ready.end(), 0);
+    if (code & 0x80000000u)
+        return fail("device error: the partial lengths of rank %u never arrived in this rank's slab (peer-memory "
+                    "all-reduce): the ranks did not make the same calls, or a rank died; every device tree must be "
+                    "committed again with n_dirty < 0", code & 0x7fffffffu);
     return fail("device error: piece %u gave up waiting for the rows of the pieces below it (a CTA of the launch "
                 "faulted or never ran); every device tree must be committed again with n_dirty < 0", piece);
+}
+
+/* sum buf[0..K) over the ranks, in place, on the context's stream; host_out (optional, mapped host
+ * memory) also receives the sums */
+static int allreduce_i64(lvb_gpu_ctx *c, long long *buf, int64_t K, long long *host_out, bool *wrote_host)
+{
+    if (wrote_host)
+        *wrote_host = false;
+    if (c->p2p && K <= c->p2p_kmax)
+    {
+        P2PParams q;
+        for (int r = 0; r < LVB_P2P_MAX_RANKS; r++)
+            q.peer[r] = c->p2p_peer[r];
+        q.nranks = c->nranks;
+        q.rank = c->rank;
+        if (++c->p2p_seq == 0u)
+            c->p2p_seq = 1u;
+        q.seq = c->p2p_seq;
+        q.slot = (int32_t)(c->p2p_seq % LVB_P2P_SLOTS);
+        q.kmax = c->p2p_kmax;
+        q.K = K;
+        q.in = buf;
+        q.out = buf;
+        q.out2 = host_out;
+        q.err = c->d_err;
+        q.spin_limit = c->spin_limit;
+        CU(launch_p2p_allreduce(q, c->stream));
+        c->launches++;
+        if (wrote_host && host_out)
+            *wrote_host = true;
+        return 0;
+    }
+    int r = g_nccl.AllReduce(buf, buf, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
+    if (r != 0)
+        return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 0;
 }
 
 /* launch the batch that is resident in staging slot c->last_slot */
@@ -435,10 +486,10 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     }
     if (c->comm && (lengths || !store || reduce_always || defer))
     {
-        int r = g_nccl.AllReduce(c->d_lengths, c->d_lengths, (size_t)K, kNcclInt64, kNcclSum, c->comm, c->stream);
-        if (r != 0)
-            return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
-        if (lengths || defer)
+        bool wrote = false;
+        if (allreduce_i64(c, c->d_lengths, K, (lengths || defer) ? st.d_len : nullptr, &wrote))
+            return 1;
+        if ((lengths || defer) && !wrote)
             CU(cudaMemcpyAsync(st.h_len, c->d_lengths, K * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
     }
     CU(cudaEventRecord(st.done, c->stream));
@@ -907,6 +958,10 @@ extern "C"
                 fprintf(stderr, "[lvb_gpu profile] %s kernel: %.3f s on the device, %lld launches, %lld programs, %lld instructions\n",
                         kd ? "store" : "score", c->kind_ms[kd] * 1e-3, (long long)c->kind_launches[kd],
                         (long long)c->kind_cand[kd], (long long)c->kind_instr[kd]);
+        for (int r = 0; r < LVB_P2P_MAX_RANKS; r++)
+            if (r != c->rank && c->p2p_peer[r])
+                cudaIpcCloseMemHandle(c->p2p_peer[r]);
+        cudaFree(c->p2p_slab);
         if (c->comm && g_nccl.CommDestroy)
             g_nccl.CommDestroy(c->comm);
         free_matrix(c);
@@ -1177,6 +1232,16 @@ extern "C"
         return run_batch(c, n_cand, trees, topos, false, nullptr, ticket);
     }
 
+    int lvb_gpu_commit_batch_submit(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                    int *ticket)
+    {
+        if (!c || !trees || !topos || !ticket)
+            return fail("lvb_gpu_commit_batch_submit: null argument");
+        if (n_cand <= 0)
+            return fail("lvb_gpu_commit_batch_submit: empty batch");
+        return run_batch(c, n_cand, trees, topos, true, nullptr, ticket);
+    }
+
     int lvb_gpu_batch_wait(lvb_gpu_ctx *c, int ticket, int64_t *lengths)
     {
         if (!c || !lengths || ticket < 0 || ticket >= lvb_gpu_ctx::kRing)
@@ -1372,15 +1437,13 @@ extern "C"
             c->ev1 = c->ring1[ev];
             c->timed = true;
         }
-        if (c->comm)
-        {
-            int r = g_nccl.AllReduce(c->d_nni, c->d_nni, (size_t)(2 * E), kNcclInt64, kNcclSum, c->comm, c->stream);
-            if (r != 0)
-                return fail("ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
-        }
+        if (c->comm && allreduce_i64(c, c->d_nni, 2 * E, nullptr, nullptr))
+            return 1;
         CU(cudaMemcpyAsync(c->h_nni, c->d_nni, (size_t)(2 * E) * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
         CU(cudaEventRecord(st.done, c->stream));
         CU(cudaEventSynchronize(st.done));
+        if (check_device_error(c))
+            return 1;
         for (int64_t k = 0; k < 2 * E; k++)
             lengths[k] = base_len + (int64_t)c->h_nni[k];
         return 0;
@@ -1465,6 +1528,79 @@ extern "C"
         }
         c->nranks = nranks;
         c->rank = rank;
+        /* peer-memory all-reduce: one slab per rank, mapped by every rank through CUDA IPC; the 64-byte
+         * handles travel through the communicator that was just made */
+        const char *pp = getenv("LVB_GPU_P2P");
+        c->p2p = false;
+        if (!(pp && atoi(pp) == 0) && nranks <= LVB_P2P_MAX_RANKS && g_nccl.AllGather)
+        {
+            const size_t slab_bytes = (size_t)LVB_P2P_SLOTS * (size_t)nranks * (size_t)c->p2p_kmax * 16;
+            unsigned char *d_h = nullptr;
+            std::vector<cudaIpcMemHandle_t> hs((size_t)nranks);
+            bool ok = cudaMalloc(&c->p2p_slab, slab_bytes) == cudaSuccess &&
+                      cudaMemset(c->p2p_slab, 0, slab_bytes) == cudaSuccess &&
+                      cudaMalloc(&d_h, (size_t)nranks * sizeof(cudaIpcMemHandle_t)) == cudaSuccess;
+            if (ok && nranks > 1)
+            {
+                ok = cudaIpcGetMemHandle(&hs[(size_t)rank], c->p2p_slab) == cudaSuccess &&
+                     cudaMemcpy(d_h + (size_t)rank * sizeof(cudaIpcMemHandle_t), &hs[(size_t)rank], sizeof(cudaIpcMemHandle_t),
+                                cudaMemcpyHostToDevice) == cudaSuccess;
+                /* every rank takes part in the gather whether or not its own set-up worked: a handle of
+                 * zeros tells the others */
+                if (!ok)
+                    cudaMemset(d_h + (size_t)rank * sizeof(cudaIpcMemHandle_t), 0, sizeof(cudaIpcMemHandle_t));
+                int gr = g_nccl.AllGather(d_h + (size_t)rank * sizeof(cudaIpcMemHandle_t), d_h, sizeof(cudaIpcMemHandle_t),
+                                          kNcclInt8, c->comm, c->stream);
+                ok = ok && gr == 0 && cudaStreamSynchronize(c->stream) == cudaSuccess &&
+                     cudaMemcpy(hs.data(), d_h, (size_t)nranks * sizeof(cudaIpcMemHandle_t), cudaMemcpyDeviceToHost) == cudaSuccess;
+                for (int r = 0; ok && r < nranks; r++)
+                {
+                    if (r == rank)
+                        continue;
+                    static const cudaIpcMemHandle_t zero = {};
+                    void *ptr = nullptr;
+                    if (memcmp(&hs[(size_t)r], &zero, sizeof zero) == 0 ||
+                        cudaIpcOpenMemHandle(&ptr, hs[(size_t)r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+                        ok = false;
+                    c->p2p_peer[r] = (unsigned long long *)ptr;
+                }
+                /* all ranks must agree on the route: one more tiny gather of the outcome */
+                unsigned char mine = ok ? 1 : 0;
+                std::vector<unsigned char> all((size_t)nranks, 0);
+                if (cudaMemcpy(d_h + rank, &mine, 1, cudaMemcpyHostToDevice) == cudaSuccess &&
+                    g_nccl.AllGather(d_h + rank, d_h, 1, kNcclInt8, c->comm, c->stream) == 0 &&
+                    cudaStreamSynchronize(c->stream) == cudaSuccess &&
+                    cudaMemcpy(all.data(), d_h, (size_t)nranks, cudaMemcpyDeviceToHost) == cudaSuccess)
+                {
+                    for (int r = 0; r < nranks; r++)
+                        ok = ok && all[(size_t)r] == 1;
+                }
+                else
+                    ok = false;
+            }
+            (void)cudaGetLastError(); /* a failed IPC attempt must not poison later calls */
+            cudaFree(d_h);
+            if (ok)
+            {
+                c->p2p_peer[rank] = c->p2p_slab;
+                c->p2p = true;
+            }
+            else
+            {
+                for (int r = 0; r < nranks; r++)
+                    if (r != rank && c->p2p_peer[r])
+                    {
+                        cudaIpcCloseMemHandle(c->p2p_peer[r]);
+                        c->p2p_peer[r] = nullptr;
+                    }
+                cudaFree(c->p2p_slab);
+                c->p2p_slab = nullptr;
+                (void)cudaGetLastError();
+            }
+        }
+        if (getenv("LVB_GPU_PROFILE"))
+            fprintf(stderr, "[lvb_gpu] rank %d/%d: all-reduce of partial lengths through %s\n", rank, nranks,
+                    c->p2p ? "peer memory (CUDA IPC slabs over NVLink)" : "ncclAllReduce");
         return 0;
     }
 

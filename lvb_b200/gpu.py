@@ -67,6 +67,7 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_score_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_score_batch_submit.argtypes = [vp, i64, i32p, C.POINTER(_Topo), i32p]
     lib.lvb_gpu_batch_wait.argtypes = [vp, C.c_int, C.POINTER(i64)]
+    lib.lvb_gpu_commit_batch_submit.argtypes = [vp, i64, i32p, C.POINTER(_Topo), i32p]
     lib.lvb_gpu_nni_neighbourhood.argtypes = [vp, C.c_int, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_download_row.argtypes = [vp, C.c_int, i64, vp]
     lib.lvb_gpu_tree_changes.argtypes = [vp, C.c_int, vp]
@@ -270,6 +271,18 @@ class Engine:
             tp.fill(sarr[i])
         ticket = C.c_int(-1)
         _check(self.lib.lvb_gpu_score_batch_submit(self.ctx, k, tarr, sarr, C.byref(ticket)))
+        return ticket.value, k
+
+    def commit_batch_submit(self, trees: Sequence[int], topos: Sequence[Topology]):
+        """enqueue a commit batch; returns (ticket, n) for batch_wait (the topologies must stay alive
+        only for the duration of this call: they are compiled here)"""
+        k = len(topos)
+        tarr = (C.c_int * k)(*[int(t) for t in trees])
+        sarr = (_Topo * k)()
+        for i, tp in enumerate(topos):
+            tp.fill(sarr[i])
+        ticket = C.c_int(-1)
+        _check(self.lib.lvb_gpu_commit_batch_submit(self.ctx, k, tarr, sarr, C.byref(ticket)))
         return ticket.value, k
 
     def batch_wait(self, ticket) -> np.ndarray:

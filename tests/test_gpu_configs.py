@@ -142,9 +142,12 @@ def _nni_candidates(left, right, root, n, count, seed):
     return bench.nni_candidates(left, right, root, n, count, seed)
 
 
-def test_nccl_single_rank_communicator():
-    """the NCCL all-reduce calls of the site-block mode (commit, score_batch, nni_neighbourhood,
-    tree_changes) executed with a one-rank communicator: same numbers as without one"""
+@pytest.mark.parametrize("route", ["p2p", "nccl"])
+def test_nccl_single_rank_communicator(monkeypatch, route):
+    """the all-reduce of the site-block mode (commit, score_batch, nni_neighbourhood, tree_changes)
+    executed with a one-rank communicator, through both routes — the peer-memory kernel (default) and
+    ncclAllReduce (LVB_GPU_P2P=0): same numbers as without a communicator"""
+    monkeypatch.setenv("LVB_GPU_P2P", "1" if route == "p2p" else "0")
     n, m = 150, 20_000
     enc = synthetic.packed(n, m, seed=5)
     left, right, root = synthetic.random_topology(n, seed=9)
@@ -178,17 +181,22 @@ def _gpu_count() -> int:
     return k.value
 
 
-@pytest.mark.skipif(_gpu_count() < 2, reason="needs two GPUs (the NCCL site-block path with two ranks)")
-def test_nccl_two_ranks_site_blocks():
+@pytest.mark.skipif(_gpu_count() < 2, reason="needs two GPUs (the site-block path with two ranks)")
+@pytest.mark.parametrize("route", ["p2p", "nccl"])
+def test_nccl_two_ranks_site_blocks(route):
     """BASELINE.json configs[3] in small on two GPUs: each rank holds half of the words of every row,
-    lengths are all-reduced inside the C-ABI; both ranks must report the oracle's numbers"""
+    lengths are all-reduced inside the C-ABI (peer-memory kernel, or ncclAllReduce with LVB_GPU_P2P=0);
+    both ranks must report the oracle's numbers"""
+    env = dict(os.environ, LVB_GPU_P2P="1" if route == "p2p" else "0", LVB_GPU_PROFILE="1")
     with tempfile.TemporaryDirectory() as td:
         procs = [subprocess.Popen([sys.executable, os.path.join(HERE, "run_siteblock_rank.py"), str(r), "2", td],
-                                  stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(2)]
+                                  stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env) for r in range(2)]
         outs = [p.communicate(timeout=600) for p in procs]
         for p, (o, e) in zip(procs, outs):
             assert p.returncode == 0, e[-2000:]
         res = [json.loads(o.strip().splitlines()[-1]) for o, _ in outs]
+        for _, e in outs:  # the route that was asked for is the one that ran
+            assert ("through peer memory" in e) == (route == "p2p"), e[-600:]
     n, m = 300, 60_000
     enc = synthetic.packed(n, m, seed=5)
     left, right, root = synthetic.random_topology(n, seed=9)
@@ -239,3 +247,30 @@ def test_pack_on_every_device():
                 assert np.array_equal(got, want), dev
             finally:
                 eng.close()
+
+
+def test_commit_submit_and_wait():
+    """lvb_gpu_commit_batch_submit + lvb_gpu_batch_wait: several whole-tree evaluations in flight
+    (compile of tree k+1 under the kernel of tree k) give the lengths of one-at-a-time commits"""
+    n, m = 200, 30_000
+    enc = synthetic.packed(n, m, seed=8)
+    topos = [Topology(*synthetic.random_topology(n, seed=20 + s)) for s in range(9)]
+    want = [oracles.oracle_getplen(enc, tp.left, tp.right, tp.root)[0] for tp in topos]
+    eng = Engine(0)
+    try:
+        eng.upload(enc, max_trees=2)
+        t0, t1 = eng.tree_create(), eng.tree_create()
+        got, inflight = [], []
+        for s, tp in enumerate(topos):
+            inflight.append(eng.commit_batch_submit([t0 if s % 2 == 0 else t1], [tp]))
+            if len(inflight) > 3:
+                got.append(int(eng.batch_wait(inflight.pop(0))[0]))
+        while inflight:
+            got.append(int(eng.batch_wait(inflight.pop(0))[0]))
+        assert got == want
+        # the trees hold the last topologies committed to them
+        _, _, chg = oracles.oracle_getplen(enc, topos[8].left, topos[8].right, topos[8].root)
+        assert np.array_equal(eng.changes(t0)[n:], chg[n:])
+        assert eng.score_batch([t1], [Topology(topos[7].left, topos[7].right, topos[7].root, [])]).tolist() == [want[7]]
+    finally:
+        eng.close()
