@@ -97,7 +97,8 @@ def host_memory_gb() -> float:
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed regions (NVML, every 20 ms;
+    """SM clock and throttle reasons sampled DURING the timed regions only (NVML, every 4 ms while
+    `active` is set — the device idles between the regions, and idle clocks say nothing about the run;
     nvidia-smi as a fallback)."""
 
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -105,6 +106,7 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.samples, self.stop = index, [], threading.Event()
+        self.active = False
         self.thread = threading.Thread(target=self.run, daemon=True)
         self.nvml = None
         try:
@@ -130,15 +132,21 @@ class ClockSampler:
                     ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
                     ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap)]
             while not self.stop.is_set():
+                if not self.active:
+                    self.stop.wait(0.001)
+                    continue
                 try:
                     sm = nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
                     r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
                     self.samples.append([str(sm), str(self.max_sm)] + ["Active" if r & b else "Not Active" for _, b in bits])
                 except Exception:
                     pass
-                self.stop.wait(0.02)
+                self.stop.wait(0.004)
             return
         while not self.stop.is_set():
+            if not self.active:
+                self.stop.wait(0.001)
+                continue
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
                                       str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
@@ -461,11 +469,13 @@ def main():
         l0 = eng.launches
         eng.kernel_time(reset=True)
         barrier()
+        clocks.active = True
         ev0.record(ext)
         for _ in range(steps):
             eng.rerun_last_batch()
         ev1.record(ext)
         eng.synchronize()
+        clocks.active = False
         barrier()
         mine = ev0.elapsed_time(ev1) * 1e-3
         k_ms, k_launch = eng.kernel_time()
@@ -511,6 +521,7 @@ def main():
         for s in range(min(3, args.steps)):
             eng.commit(tree, topos[s])
         barrier()
+        clocks.active = True
         t0 = time.perf_counter()
         # what a caller that scores many trees does: tree s+1 is compiled and enqueued (lvb_gpu_commit_batch_submit)
         # while the device works on tree s; every length is read back (lvb_gpu_batch_wait)
@@ -521,6 +532,7 @@ def main():
                 lens.append(int(eng.batch_wait(inflight.pop(0))[0]))
         while inflight:
             lens.append(int(eng.batch_wait(inflight.pop(0))[0]))
+        clocks.active = False
         barrier()
         wall_b = max_over_ranks(time.perf_counter() - t0)
         # the same, one tree at a time (submit, wait, next): the latency of a single call

@@ -18,6 +18,7 @@
  */
 #include "fitch_kernels.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -191,19 +192,24 @@ __device__ __forceinline__ unsigned piece_start_ticket(const ExecParams &p)
     __syncthreads();
     return s_vb;
 }
-/* The wait is bounded: after spin_limit polls (or as soon as another CTA gave up) the CTA records
+/* A piece of level L > 0 waits, per column block, until every piece of level L - 1 of this launch
+ * has stored its rows (the levels below that were complete before the first piece of level L - 1
+ * went on).  dep[L][cb] only ever counts up: the host hands every launch the value it will have
+ * reached (p.dep_target), so nothing has to be reset between launches.
+ * The wait is bounded: after spin_limit polls (or as soon as another CTA gave up) the CTA records
  * 1 + its piece in the mapped host word p.err and leaves; the host turns that into an error
  * instead of a hung launch.  Returns false when the wait was abandoned. */
-__device__ __forceinline__ bool piece_wait_children(const ExecParams &p, int prog_id, int cb, int n_wait)
+__device__ __forceinline__ bool piece_wait_children(const ExecParams &p, int prog_id, int cb, int level)
 {
     __shared__ unsigned s_abort;
     if (threadIdx.x == 0)
     {
-        volatile unsigned *f = p.dep + (size_t)prog_id * p.n_colblocks + cb;
+        volatile unsigned *f = p.dep + (size_t)(level - 1) * p.n_colblocks + cb;
+        const unsigned target = p.dep_target[level - 1];
         unsigned spins = 0, ab = 0;
-        while (*f < (unsigned)n_wait)
+        while ((int)(*f - target) < 0)
         {
-            __nanosleep(100);
+            __nanosleep(64);
             if ((++spins & 1023u) == 0u && (spins >= p.spin_limit || *(volatile unsigned *)p.err != 0u))
             {
                 ab = 1u;
@@ -213,16 +219,13 @@ __device__ __forceinline__ bool piece_wait_children(const ExecParams &p, int pro
         if (ab)
             atomicCAS(p.err, 0u, 1u + (unsigned)prog_id);
         else
-        {
-            *f = 0u;
             __threadfence();
-        }
         s_abort = ab;
     }
     __syncthreads();
     return s_abort == 0u;
 }
-/* after the CTA's last row store: let the piece that reads this piece's top row go on */
+/* after the CTA's last row store: one more piece of this level is complete for the column block */
 __device__ __forceinline__ void piece_release_parent(const ExecParams &p, const FitchProgram &prog, int cb)
 {
     if (prog.parent < 0)
@@ -332,7 +335,7 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
     const int prog_id = piece_major ? vb / p.n_colblocks : vb % p.n_prog;
     const int cb = piece_major ? vb % p.n_colblocks : vb / p.n_prog;
     const FitchProgram prog = progs[prog_id];
-    if (PER_NODE && p.dep && prog.n_wait > 0 && !piece_wait_children(p, prog_id, cb, prog.n_wait))
+    if (PER_NODE && p.dep && prog.flags > 0 && !piece_wait_children(p, prog_id, cb, prog.flags))
         return;
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
@@ -617,8 +620,6 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     const int prog_id = piece_major ? vb / p.n_colblocks : vb % p.n_prog;
     const int cb = piece_major ? vb % p.n_colblocks : vb / p.n_prog;
     const FitchProgram prog = progs[prog_id];
-    if (piece_major && prog.n_wait > 0 && !piece_wait_children(p, prog_id, cb, prog.n_wait))
-        return;
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
@@ -683,6 +684,9 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
             s_instr[i] = d;
         }
         __syncthreads();
+        /* dependent piece: its instructions are staged, now wait for the rows of the level below */
+        if (piece_major && base == 0 && prog.flags > 0 && !piece_wait_children(p, prog_id, cb, prog.flags))
+            return;
 
 #define LVB_ISSUE(J, S)                                                                                               \
     {                                                                                                                 \
@@ -887,12 +891,448 @@ static cudaError_t want_smem(K kernel, size_t smem)
     return cudaSuccess;
 }
 
+/* ---- store mode, streaming kernel: TMA bulk loads + mbarrier ring, warp-specialised, persistent ----
+ * The store launches that matter for bandwidth (a first pass, a re-root of a big tree, many commits at
+ * once) are streams of rows: every HBM operand is a whole row segment of the CTA's column block,
+ * contiguous in memory (a CTA of NT consumer threads owns NT x 16 bytes of every row), and none of
+ * the addresses depends on a result.  So one PRODUCER warp per CTA walks the program ahead of the
+ * arithmetic and moves each operand segment with ONE bulk asynchronous copy (cp.async.bulk, the TMA
+ * engine) into a ring of LVB_SR segments in shared memory, completion counted in bytes on an mbarrier
+ * per ring slot; the NT CONSUMER threads wait for a slot, take their 16 bytes, hand the slot back
+ * (one mbarrier arrive per warp) and do the Fitch step.  Against the per-thread cp.async ring of
+ * fitch_score_body this removes the per-thread address arithmetic, LDGSTS issue and group
+ * bookkeeping from the inner loop, and the ring only holds REAL loads (half of the operands of a
+ * post-order program are the previous result or a stack slot), so the same look-ahead costs half the
+ * shared memory and twice as many CTAs fit an SM.
+ * The CTAs are persistent: the producer takes the next (piece, column block) ticket, stages and
+ * decodes its instructions into the other instruction buffer and starts its loads while the
+ * consumers still work on the current piece — no start-up or drain bubble between pieces.
+ * Dependent pieces: the PRODUCER waits for the level below (piece_wait_children) before it
+ * publishes a piece, the consumers never wait for anything but their operands. */
+#define LVB_SR 8       /* ring slots (power of two) */
+#define LVB_SCHUNK 128 /* instructions per staged chunk */
+
+struct StreamWork
+{
+    int32_t n;     /* instructions in this chunk; 0 = no more work */
+    int32_t base;  /* index of the chunk's first instruction in its program */
+    int32_t last;  /* last chunk of its program */
+    int32_t prog_id;
+    int32_t cb;
+    int32_t pad[3];
+    FitchProgram prog;
+};
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
+{
+    /* labels inside a { } block are local to it */
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "LVB_WAIT:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@p bra LVB_DONE;\n\t"
+                 "bra LVB_WAIT;\n\t"
+                 "LVB_DONE:\n\t}"
+                 :
+                 : "r"(bar), "r"(parity)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_load(unsigned dst, unsigned long long src, unsigned bytes, unsigned bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :
+                 : "r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void consumer_barrier(int nt)
+{
+    asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");
+}
+
+/* piece_finalize for the consumer threads of the streaming kernel (tid < nt; barrier 1) */
+__device__ __forceinline__ void stream_finalize(const ExecParams &p, const FitchInstr *instrs, const FitchProgram &prog,
+                                                int prog_id, int tid, int nt, unsigned *s_last, long long *s_acc)
+{
+    consumer_barrier(nt); /* this CTA's count atomics are issued */
+    if (tid == 0)
+    {
+        __threadfence();
+        const unsigned last = atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u ? 1u : 0u;
+        if (last)
+            p.done[prog_id] = 0u;
+        *s_last = last;
+        s_acc[0] = 0;
+        s_acc[1] = 0;
+    }
+    consumer_barrier(nt);
+    if (!*s_last)
+        return;
+    __threadfence();
+    int32_t *tchg = p.chg_rw + (int64_t)prog.tree * p.n_internal;
+    long long delta = 0, rootc = 0;
+    for (int i = tid; i < prog.n_instr; i += nt)
+    {
+        const int node = instrs[prog.instr_begin + i].node;
+        const int c = __ldcg(&p.cnts[prog.instr_begin + i]);
+        p.cnts[prog.instr_begin + i] = 0; /* ready for the next store batch */
+        if (node >= 0)
+        {
+            delta += (long long)c - tchg[node - p.n];
+            tchg[node - p.n] = c;
+        }
+        else
+            rootc += c; /* root step: never cached (TreeEvaluation.c:238-264) */
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        delta += __shfl_xor_sync(0xffffffffu, delta, o);
+        rootc += __shfl_xor_sync(0xffffffffu, rootc, o);
+    }
+    if ((tid & 31) == 0)
+    {
+        if (delta)
+            atomicAdd((unsigned long long *)&s_acc[0], (unsigned long long)delta);
+        if (rootc)
+            atomicAdd((unsigned long long *)&s_acc[1], (unsigned long long)rootc);
+    }
+    consumer_barrier(nt);
+    if (tid == 0)
+    {
+        const int k = prog.pad1;
+        const int ctree = p.cand[k].tree;
+        const unsigned n_pieces = (unsigned)p.cand[k].n_wait;
+        if (s_acc[0])
+            atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], (unsigned long long)s_acc[0]);
+        if (s_acc[1])
+            atomicAdd(&p.totals[k], (unsigned long long)s_acc[1]);
+        __threadfence();
+        if (atomicAdd(&p.done[p.n_prog + k], 1u) == n_pieces - 1u)
+        {
+            __threadfence();
+            p.done[p.n_prog + k] = 0u;
+            const long long sum = (long long)atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], 0ull);
+            p.out[k] = sum + (long long)atomicExch(&p.totals[k], 0ull);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
+{
+    extern __shared__ uint4 smem_u4[];
+    __shared__ __align__(8) unsigned long long s_bar[2 * LVB_SR + 4]; /* full[SR], empty[SR], ifull[2], iempty[2] */
+    __shared__ StreamWork s_work[2];
+    __shared__ unsigned s_last;
+    __shared__ long long s_acc[2];
+
+    const int nt = (int)blockDim.x - 32; /* consumer threads */
+    const int nwarps = nt >> 5;
+    const int tid = threadIdx.x;
+    uint4 *s_instr = smem_u4;                                              /* [2][LVB_SCHUNK] decoded instructions */
+    int *s_cnt = reinterpret_cast<int *>(smem_u4 + 2 * LVB_SCHUNK);         /* [2][LVB_SCHUNK][nwarps] */
+    uint4 *s_ring = smem_u4 + 2 * LVB_SCHUNK + (2 * LVB_SCHUNK * nwarps + 3) / 4; /* [LVB_SR][nt] */
+    uint4 *s_stack = s_ring + LVB_SR * nt;                                  /* [n_slots][nt] */
+
+    /* made opaque to the compiler, which otherwise re-derives the shared window base at every use */
+    unsigned bar0;
+    asm volatile("mov.u32 %0, %1;" : "=r"(bar0) : "r"((unsigned)__cvta_generic_to_shared(s_bar)));
+    auto full_bar = [&](unsigned s) { return bar0 + 8u * s; };
+    auto empty_bar = [&](unsigned s) { return bar0 + 8u * (LVB_SR + s); };
+    auto ifull_bar = [&](unsigned b) { return bar0 + 8u * (2 * LVB_SR + b); };
+    auto iempty_bar = [&](unsigned b) { return bar0 + 8u * (2 * LVB_SR + 2 + b); };
+    if (tid == 0)
+    {
+        for (unsigned s = 0; s < LVB_SR; s++)
+        {
+            mbar_init(full_bar(s), 1u);
+            mbar_init(empty_bar(s), (unsigned)nwarps);
+        }
+        for (unsigned b = 0; b < 2; b++)
+        {
+            mbar_init(ifull_bar(b), 1u);
+            mbar_init(iempty_bar(b), (unsigned)nwarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
+    const unsigned slot_bytes = (unsigned)nt * 16u;
+    const unsigned total = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
+    const bool piece_major = p.dep != nullptr;
+
+    if (tid >= nt)
+    { /* ---------------- producer warp ---------------- */
+        const int lane = tid - nt;
+        const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring);
+        unsigned jl = 0; /* loads issued */
+        unsigned q = 0;  /* chunks published */
+        for (;;)
+        {
+            unsigned vb = 0;
+            if (lane == 0)
+                vb = atomicAdd(p.ticket, 1u);
+            vb = __shfl_sync(0xffffffffu, vb, 0);
+            bool stop = vb >= total;
+            if (stop && lane == 0 && vb == total + gridDim.x - 1u)
+                *p.ticket = 0u; /* every CTA has drawn its last ticket: ready for the next launch */
+            int prog_id = 0, cb = 0;
+            FitchProgram prog = {};
+            if (!stop)
+            {
+                prog_id = piece_major ? (int)(vb / (unsigned)p.n_colblocks) : (int)(vb % (unsigned)p.n_prog);
+                cb = piece_major ? (int)(vb % (unsigned)p.n_colblocks) : (int)(vb / (unsigned)p.n_prog);
+                prog = p.prog[prog_id];
+            }
+            const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
+            const unsigned src_off = prog.src_tree1 > 0 ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
+            const FitchInstr *gi = p.instr + prog.instr_begin;
+            const unsigned bytes = (unsigned)min(nt, p.ncols - cb * nt) * 16u;
+            const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + (size_t)cb * nt);
+            bool waited = false;
+            for (int base = 0; base < (stop ? 1 : prog.n_instr); base += LVB_SCHUNK)
+            {
+                const unsigned buf = q & 1u;
+                mbar_wait(iempty_bar(buf), ((q >> 1) & 1u) ^ 1u); /* the consumers are done with this buffer */
+                const int m = stop ? 0 : min(LVB_SCHUNK, prog.n_instr - base);
+                uint4 *dst = s_instr + buf * LVB_SCHUNK;
+                for (int i = lane; i < m; i += 32)
+                {
+                    const FitchInstr in = gi[base + i];
+                    int a = in.a, b = in.b;
+                    if (LVB_OPER_IS_SLOT(a) || b == LVB_OPER_PREV)
+                    {
+                        const int t = a;
+                        a = b;
+                        b = t;
+                    }
+                    unsigned w = (in.ctl & LVB_CTL_STORE) ? D_STORE : 0u;
+                    const unsigned push = (in.ctl & LVB_CTL_PUSH_MASK) >> LVB_CTL_PUSH_SHIFT;
+                    if (push)
+                        w |= D_PUSH | ((push - 1u) * slot_bytes);
+                    if (a < 0)
+                    {
+                        w |= D_APREV;
+                        a = 0;
+                    }
+                    else if (a >= p.n)
+                        a = a >= p.n + p.n_internal ? a - p.n_internal + (int)tree_off : a + (int)src_off;
+                    if (b < 0)
+                    {
+                        w |= D_BSLOT;
+                        b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
+                    }
+                    else if (b >= p.n)
+                        b = b >= p.n + p.n_internal ? b - p.n_internal + (int)tree_off : b + (int)src_off;
+                    dst[i] = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
+                }
+                /* a dependent piece is published only when the rows of the level below are there */
+                unsigned ok = 1u;
+                if (!stop && !waited && piece_major && prog.flags > 0)
+                {
+                    if (lane == 0)
+                    {
+                        volatile unsigned *f = p.dep + (size_t)(prog.flags - 1) * p.n_colblocks + cb;
+                        const unsigned target = p.dep_target[prog.flags - 1];
+                        unsigned spins = 0;
+                        while ((int)(*f - target) < 0)
+                        {
+                            __nanosleep(64);
+                            if ((++spins & 1023u) == 0u && (spins >= p.spin_limit || *(volatile unsigned *)p.err != 0u))
+                            {
+                                ok = 0u;
+                                break;
+                            }
+                        }
+                        if (!ok)
+                            atomicCAS(p.err, 0u, 1u + (unsigned)prog_id);
+                        __threadfence();
+                        /* rows written by other CTAs (generic proxy) are read by the bulk copies (async proxy) */
+                        asm volatile("fence.proxy.async;" ::: "memory");
+                    }
+                    ok = __shfl_sync(0xffffffffu, ok, 0);
+                    waited = true;
+                }
+                if (lane == 0)
+                {
+                    StreamWork &wk = s_work[buf];
+                    wk.n = ok ? m : 0;
+                    wk.base = base;
+                    wk.last = base + LVB_SCHUNK >= prog.n_instr ? 1 : 0;
+                    wk.prog_id = prog_id;
+                    wk.cb = cb;
+                    wk.prog = prog;
+                }
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(ifull_bar(buf));
+                q++;
+                if (!ok)
+                    stop = true;
+                if (stop)
+                    break;
+                if (lane == 0)
+                { /* the loads of this chunk, in the order the consumers take them */
+                    for (int i = 0; i < m; i++)
+                    {
+                        const uint4 ci = dst[i];
+                        if (!(ci.w & D_APREV))
+                        {
+                            const unsigned s = jl & (LVB_SR - 1u);
+                            mbar_wait(empty_bar(s), ((jl / LVB_SR) & 1u) ^ 1u);
+                            mbar_expect_tx(full_bar(s), bytes);
+                            bulk_load(sa_ring + s * slot_bytes, row_addr(ci.x, stride_b, colbase), bytes, full_bar(s));
+                            jl++;
+                        }
+                        if (!(ci.w & D_BSLOT))
+                        {
+                            const unsigned s = jl & (LVB_SR - 1u);
+                            mbar_wait(empty_bar(s), ((jl / LVB_SR) & 1u) ^ 1u);
+                            mbar_expect_tx(full_bar(s), bytes);
+                            bulk_load(sa_ring + s * slot_bytes, row_addr(ci.y, stride_b, colbase), bytes, full_bar(s));
+                            jl++;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            if (stop)
+                break;
+        }
+        return;
+    }
+
+    /* ---------------- consumer threads ---------------- */
+    const unsigned sa_instr = (unsigned)__cvta_generic_to_shared(s_instr);
+    const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
+    const unsigned sa_stack = (unsigned)__cvta_generic_to_shared(s_stack + tid);
+    const unsigned lane0 = (tid & 31) == 0 ? 1u : 0u;
+    const unsigned cnt_step = (unsigned)nwarps * 4u;
+    uint4 acc = make_uint4(~0u, ~0u, ~0u, ~0u);
+    unsigned jc = 0; /* loads taken */
+    for (unsigned q = 0;; q++)
+    {
+        const unsigned buf = q & 1u;
+        mbar_wait(ifull_bar(buf), (q >> 1) & 1u);
+        const int m = s_work[buf].n;
+        if (m == 0)
+            break;
+        const int cb = s_work[buf].cb;
+        const int col = cb * nt + tid;
+        const unsigned active = col < p.ncols ? 1u : 0u;
+        const unsigned amask = active ? ~0u : 0u;
+        const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
+        const unsigned ia0 = sa_instr + buf * (LVB_SCHUNK * 16u);
+        int *cnt = s_cnt + buf * (LVB_SCHUNK * nwarps);
+        const unsigned sa_cnt = (unsigned)__cvta_generic_to_shared(cnt + (tid >> 5));
+        for (int i = 0; i < m; i++)
+        {
+            const uint4 ci = lds128(ia0 + (unsigned)i * 16u);
+            uint4 y;
+            if (!(ci.w & D_APREV))
+            {
+                const unsigned s = jc & (LVB_SR - 1u);
+                mbar_wait(bar0 + 8u * s, (jc / LVB_SR) & 1u);
+                acc = lds128(sa_ring + s * slot_bytes);
+                __syncwarp();
+                if (lane0)
+                    mbar_arrive(bar0 + 8u * (LVB_SR + s));
+                jc++;
+            }
+            if (ci.w & D_BSLOT)
+                y = lds128(sa_stack + ci.y);
+            else
+            {
+                const unsigned s = jc & (LVB_SR - 1u);
+                mbar_wait(bar0 + 8u * s, (jc / LVB_SR) & 1u);
+                y = lds128(sa_ring + s * slot_bytes);
+                __syncwarp();
+                if (lane0)
+                    mbar_arrive(bar0 + 8u * (LVB_SR + s));
+                jc++;
+            }
+            const unsigned f = fitch_step(acc, y, acc) & amask;
+            sts32_if(sa_cnt + (unsigned)i * cnt_step, __reduce_add_sync(0xffffffffu, __popc(f)), lane0);
+            stg_if(row_addr(ci.z, stride_b, colbase), acc, (ci.w & D_STORE) & active);
+            sts128_if(sa_stack + (ci.w & 0x0ffffff0u), acc, ci.w & D_PUSH);
+        }
+        /* chunk end: per-instruction counts of the CTA -> global; then the piece's bookkeeping */
+        const FitchProgram prog = s_work[buf].prog;
+        const int base = s_work[buf].base, last = s_work[buf].last, prog_id = s_work[buf].prog_id;
+        consumer_barrier(nt); /* counts and row stores of every consumer are issued */
+        for (int k = tid; k < m; k += nt)
+        {
+            int sum = 0;
+            for (int w = 0; w < nwarps; w++)
+                sum += cnt[k * nwarps + w];
+            if (sum)
+                atomicAdd(&p.cnts[prog.instr_begin + base + k], sum);
+        }
+        __syncwarp();
+        if (lane0)
+            mbar_arrive(iempty_bar(buf)); /* the producer may stage the chunk after next here */
+        if (last)
+        {
+            if (piece_major && prog.parent >= 0 && tid == 0)
+            {
+                __threadfence();
+                atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
+            }
+            if (p.fused_finalize)
+                stream_finalize(p, p.instr, prog, prog_id, tid, nt, &s_last, s_acc);
+        }
+    }
+}
+
+static size_t stream_smem_bytes(int n_slots, int nt)
+{
+    const int nwarps = nt / 32;
+    return (size_t)(2 * LVB_SCHUNK + (2 * LVB_SCHUNK * nwarps + 3) / 4 + (size_t)(LVB_SR + n_slots) * nt) * sizeof(uint4);
+}
+
+cudaError_t launch_fitch_stream(const ExecParams &p, int nt, cudaStream_t stream)
+{
+    static int sms[LVB_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return e;
+    if (dev < 0 || dev >= LVB_MAX_DEVICES)
+        return cudaErrorInvalidDevice;
+    if (!sms[dev] && (e = cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess)
+        return e;
+    const size_t smem = stream_smem_bytes(p.n_slots, nt);
+    if ((e = want_smem(fitch_stream_kernel, smem)) != cudaSuccess)
+        return e;
+    int per_sm = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fitch_stream_kernel, nt + 32, smem)) != cudaSuccess)
+        return e;
+    if (per_sm < 1)
+        return cudaErrorLaunchOutOfResources;
+    const long long total = (long long)p.n_prog * p.n_colblocks;
+    const unsigned grid = (unsigned)std::min<long long>(total, (long long)sms[dev] * per_sm);
+    fitch_stream_kernel<<<grid, nt + 32, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cudaStream_t stream)
 {
     const size_t smem = exec_smem_bytes(per_node, p.n_slots, block);
     const unsigned grid = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
     const bool deep = deep_enabled() && small_grid(grid);
     cudaError_t e;
+    if (per_node && p.stream_nt > 0)
+        return launch_fitch_stream(p, p.stream_nt, stream);
     if (per_node && p.dep && p.pipe_pf > 0)
     {
         const int pf = p.pipe_pf >= 7 ? 7 : p.pipe_pf >= 5 ? 5 : p.pipe_pf >= 3 ? 3 : 2;

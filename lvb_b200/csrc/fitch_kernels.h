@@ -11,6 +11,8 @@ namespace lvbgpu
 {
 
 /* Everything a batch launch needs; lives in kernel parameter space. */
+#define LVB_DEP_LEVELS 8 /* piece levels of one launch (schedule.cpp cuts at most 7) */
+
 struct ExecParams
 {
     uint4 *pool;                 /* row pool: rows [0,n) leaves, then I rows per tree */
@@ -31,8 +33,11 @@ struct ExecParams
     int32_t *cnts;               /* [n_instr of batch] per-instruction counts (store mode); zeroed by finalize */
     unsigned *ticket;            /* store mode, dependent pieces: ticket[0] CTA start-order counter (left zero by the
                                   * kernel) */
-    unsigned *dep;               /* store mode: [n_prog][n_colblocks] finished child pieces per column block
-                                  * (left zero by the kernel); NULL: pieces of the launch are independent */
+    unsigned *dep;               /* store mode: [LVB_DEP_LEVELS][n_colblocks] pieces of a level finished per column
+                                  * block, counted over all launches (never reset while the geometry stays); NULL:
+                                  * the pieces of the launch are independent */
+    unsigned dep_target[LVB_DEP_LEVELS]; /* value dep[L][cb] has when every piece of level L of THIS launch has
+                                  * stored its rows for column block cb: a piece of level L + 1 waits for it */
     int32_t fused_finalize;      /* store mode: the finalize step (chg_rw / sum_chg_rw / out) runs inside the Fitch
                                   * kernel instead of a second launch.  Single-level batch: by the last column block
                                   * of a program.  Dependent pieces: the last column block of a PIECE folds that
@@ -43,6 +48,10 @@ struct ExecParams
     int32_t n_cand;
     int32_t pipe_pf;             /* store mode, dependent pieces: 0 = register-pipelined kernel (fitch_exec_kernel),
                                   * 2/3/5/7 = cp.async ring with that many instructions of look-ahead */
+    int32_t stream_nt;           /* store mode: > 0 = the streaming kernel (TMA bulk loads, persistent CTAs) with this many
+                                  * consumer threads per CTA; `block` of launch_fitch_exec is then ignored and
+                                  * n_colblocks must have been computed with stream_nt columns per block; ticket must
+                                  * be set (dep may be NULL: independent programs) */
     unsigned *err;               /* mapped host word: 1 + piece whose dependency wait was abandoned (0 = none) */
     unsigned spin_limit;         /* polls of a dependency counter after which the wait is abandoned */
     int32_t *chg_rw;             /* = chg, writable (fused finalize) */

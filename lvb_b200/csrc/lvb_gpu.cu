@@ -144,13 +144,16 @@ struct lvb_gpu_ctx
     std::vector<std::string> c_err;
     std::vector<FitchProgram> prog;                    /* pieces, sorted by level */
     std::vector<std::pair<int32_t, int32_t>> levels;   /* (first piece, count) per launch */
-    int64_t target_warps = 148 * 384;                  /* resident warps wanted per launch */
+    int64_t target_warps = 148 * 192;                  /* resident warps wanted per launch */
     unsigned long long *d_totals = nullptr;            /* [cap_tot] per-program sums; zero between batches */
     unsigned *d_done = nullptr;                        /* [cap_tot] CTAs finished per program; zero between batches */
     long long *d_lengths = nullptr;                    /* [cap_tot] lengths on the device (site-block mode: all-reduced here) */
     size_t cap_tot = 0;
     unsigned *d_dep = nullptr;                         /* [cap_dep] + 1 ticket: dependency counters of one store launch; zero between */
     size_t cap_dep = 0;
+    size_t dep_ncb = 0;                                /* column blocks the counters in d_dep are laid out for */
+    unsigned dep_total[LVB_DEP_LEVELS] = {};           /* value of d_dep[L][*] once every launch so far is complete */
+    unsigned last_level_count[LVB_DEP_LEVELS] = {};    /* pieces per level of the resident batch */
     long long *d_nni = nullptr, *h_nni = nullptr;      /* [cap_nni] length differences of an NNI neighbourhood */
     size_t cap_nni = 0;
     int compile_par_min = 8;  /* host compile: batches of >= min candidates are spread over
@@ -161,7 +164,10 @@ struct lvb_gpu_ctx
     bool fuse_ok = true;     /* single-level store batches finalize inside the Fitch kernel (LVB_GPU_FUSE=0: own launch) */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
-    int store_pf = 0;                                  /* dependent-piece store launches: 0 = register-pipelined kernel,
+    int stream_nt = 128;                               /* dependent-piece store launches: consumer threads per CTA of the
+                                                        * streaming kernel (TMA bulk loads); 0 = the cp.async / register
+                                                        * pipelined kernels below (LVB_GPU_STORE_STREAM) */
+    int store_pf = 7;                                  /* dependent-piece store launches: 0 = register-pipelined kernel,
                                                         * 2/3/5/7 = cp.async ring with that look-ahead (LVB_GPU_STORE_PF) */
     unsigned spin_limit = 1u << 26;                    /* polls (>= 100 ns each) before a dependency wait is abandoned */
     unsigned *h_err = nullptr, *d_err = nullptr;       /* mapped host word the kernels report an abandoned wait in */
@@ -305,6 +311,12 @@ static int pick_block(const lvb_gpu_ctx *c)
     return 64;
 }
 
+/* column-block width of a store launch of dependent pieces: the streaming kernel has its own */
+static int dep_block(const lvb_gpu_ctx *c)
+{
+    return c->stream_nt > 0 ? c->stream_nt : pick_block(c);
+}
+
 /* fold finished event pairs into the running kernel-time total */
 static int drain_kernel_events(lvb_gpu_ctx *c)
 {
@@ -337,6 +349,8 @@ static int check_device_error(lvb_gpu_ctx *c)
     *c->h_err = 0u;
     if (c->d_dep)
         cudaMemsetAsync(c->d_dep, 0, (c->cap_dep + 1) * sizeof(unsigned), c->stream);
+    for (int L = 0; L < LVB_DEP_LEVELS; L++)
+        c->dep_total[L] = 0u;
     if (c->d_totals)
         cudaMemsetAsync(c->d_totals, 0, c->cap_tot * sizeof(unsigned long long), c->stream);
     if (c->d_done)
@@ -410,7 +424,9 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     p.ncols = (int32_t)c->stride_u4;
     p.n = (int32_t)c->n;
     p.n_internal = (int32_t)c->I;
-    const int block = pick_block(c);
+    const bool stream = store && c->last_dep && c->stream_nt > 0;
+    const int block = stream ? c->stream_nt : pick_block(c);
+    p.stream_nt = stream ? c->stream_nt : 0;
     p.n_colblocks = (int32_t)((c->stride_u4 + block - 1) / block);
     p.n_slots = c->last_slots;
     p.score_v1 = c->score_v1 ? 1 : 0;
@@ -434,6 +450,17 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     p.pipe_pf = c->store_pf;
     p.err = c->d_err;
     p.spin_limit = c->spin_limit;
+    for (int L = 0; L < LVB_DEP_LEVELS; L++)
+    {
+        if (c->last_dep)
+            c->dep_total[L] += c->last_level_count[L];
+        p.dep_target[L] = c->dep_total[L];
+    }
+    if (c->last_dep && c->fault_dep)
+    { /* test hook: the pieces above level 0 wait for a piece that does not exist */
+        p.dep_target[0]++;
+        c->fault_dep = 0;
+    }
 
     const double ts0 = c->profile ? wall_now() : 0;
     int slot = -1;
@@ -674,68 +701,41 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         }
         else
         {
-            /* who stores which row: (tree, node) -> piece; then every internal-row operand that a
-             * piece of this batch stores is a dependency of the piece that reads it */
-            const size_t slots = (size_t)c->max_trees * (size_t)c->I;
-            if (c->owner_stamp.size() != slots)
+            /* every piece of level L > 0 waits, per column block, for all pieces of level L - 1
+             * (schedule.cpp: a level only reads leaf rows and rows stored by the levels below, and the
+             * levels are contiguous); a piece below the top level counts itself in when its rows are
+             * stored.  The counters run on from launch to launch (launch_resident hands out targets). */
+            int top = 0;
+            for (const FitchProgram &pg : c->prog)
+                top = std::max(top, pg.flags);
+            if (top >= LVB_DEP_LEVELS)
+                return fail("internal error: %d piece levels", top + 1);
+            for (int L = 0; L < LVB_DEP_LEVELS; L++)
+                c->last_level_count[L] = 0;
+            for (FitchProgram &pg : c->prog)
             {
-                c->owner_stamp.assign(slots, 0);
-                c->owner_piece.assign(slots, 0);
-                c->owner_cur = 0;
+                c->last_level_count[pg.flags]++;
+                pg.parent = pg.flags < top ? pg.flags : -1;
+                pg.n_wait = 0;
             }
-            if (++c->owner_cur == INT32_MAX)
+            c->last_level_count[top] = 0; /* nobody waits for the top level: its pieces do not count themselves in */
+            const size_t n_cb = (size_t)((c->stride_u4 + dep_block(c) - 1) / dep_block(c));
+            const size_t need = (size_t)LVB_DEP_LEVELS * n_cb;
+            if (need > c->cap_dep || n_cb != c->dep_ncb)
             {
-                std::fill(c->owner_stamp.begin(), c->owner_stamp.end(), 0);
-                c->owner_cur = 1;
-            }
-            for (size_t q = 0; q < c->prog.size(); q++)
-            {
-                const FitchProgram &pg = c->prog[q];
-                const size_t tb = (size_t)pg.tree * (size_t)c->I;
-                for (int32_t i = 0; i < pg.n_instr; i++)
-                {
-                    const FitchInstr &in = h_instr[pg.instr_begin + i];
-                    if (in.node >= 0 && (in.ctl & LVB_CTL_STORE))
-                    {
-                        c->owner_stamp[tb + (in.node - c->n)] = c->owner_cur;
-                        c->owner_piece[tb + (in.node - c->n)] = (int32_t)q;
-                    }
-                }
-            }
-            for (size_t q = 0; q < c->prog.size(); q++)
-            {
-                FitchProgram &pg = c->prog[q];
-                const size_t tb = (size_t)pg.tree * (size_t)c->I;
-                for (int32_t i = 0; i < pg.n_instr; i++)
-                {
-                    const FitchInstr &in = h_instr[pg.instr_begin + i];
-                    const int32_t ops[2] = {in.a, in.b};
-                    for (int32_t v : ops)
-                        if (v >= c->n && c->owner_stamp[tb + (v - c->n)] == c->owner_cur)
-                        {
-                            const int32_t child = c->owner_piece[tb + (v - c->n)];
-                            if ((size_t)child >= q)
-                                return fail("internal error: piece %zu reads a row stored by piece %d", q, child);
-                            c->prog[child].parent = (int32_t)q;
-                            pg.n_wait++;
-                        }
-                }
-            }
-            const size_t n_cb = (size_t)((c->stride_u4 + pick_block(c) - 1) / pick_block(c));
-            const size_t need = c->prog.size() * n_cb;
-            if (need > c->cap_dep)
-            {
-                const size_t cap = grow(c->cap_dep, need, 1 << 16);
                 CU(cudaStreamSynchronize(c->stream));
-                cudaFree(c->d_dep);
-                CU(cudaMalloc(&c->d_dep, (cap + 1) * sizeof(unsigned)));
-                CU(cudaMemsetAsync(c->d_dep, 0, (cap + 1) * sizeof(unsigned), c->stream));
-                c->cap_dep = cap;
-            }
-            if (c->fault_dep)
-            { /* test hook: the top piece waits for a child that does not exist */
-                c->prog.back().n_wait++;
-                c->fault_dep = 0;
+                if (need > c->cap_dep)
+                {
+                    const size_t cap = grow(c->cap_dep, need, 1 << 12);
+                    cudaFree(c->d_dep);
+                    c->d_dep = nullptr;
+                    CU(cudaMalloc(&c->d_dep, (cap + 1) * sizeof(unsigned)));
+                    c->cap_dep = cap;
+                }
+                CU(cudaMemsetAsync(c->d_dep, 0, (c->cap_dep + 1) * sizeof(unsigned), c->stream));
+                for (int L = 0; L < LVB_DEP_LEVELS; L++)
+                    c->dep_total[L] = 0u;
+                c->dep_ncb = n_cb;
             }
             c->last_dep = true;
             c->levels.push_back({0, (int32_t)c->prog.size()});
@@ -921,6 +921,12 @@ extern "C"
             c->timing = true;
         const char *ll = getenv("LVB_GPU_LEVEL_LAUNCHES");
         c->level_launches = ll && atoi(ll) != 0;
+        const char *sst = getenv("LVB_GPU_STORE_STREAM");
+        if (sst)
+        {
+            const int v = atoi(sst);
+            c->stream_nt = v <= 0 ? 0 : std::min(256, std::max(32, v / 32 * 32));
+        }
         const char *spf = getenv("LVB_GPU_STORE_PF");
         if (spf)
             c->store_pf = atoi(spf);
@@ -1385,6 +1391,7 @@ extern "C"
             p.cand = nullptr;
             p.n_cand = 0;
             p.pipe_pf = 0;
+            p.stream_nt = 0;
             p.err = c->d_err;
             p.spin_limit = c->spin_limit;
             const size_t level_first[2] = {0, n_level0}, level_count[2] = {n_level0, n_pcs - n_level0};

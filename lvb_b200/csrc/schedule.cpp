@@ -202,73 +202,153 @@ bool ScheduleCompiler::compile_impl(const lvb_gpu_topology &topo, bool store, st
             return false;
         }
     }
-    /* bottom-up over the dirty forest: piece cuts, piece levels, stack need.
-     * size: nodes of the current piece under v; a node whose piece reaches piece_size becomes
-     * the root of a piece of its own (its row is stored, the parent reads it from HBM).
-     * need: stack slots in use at the peak while v's part of the piece is evaluated. */
-    for (size_t k = no; k-- > 0;)
-    {
+    /* bottom-up over the dirty forest: subtree sizes and stack need of the uncut program.
+     * size: nodes of the node's own piece at and below it; need: stack slots in use at the peak while
+     * that part is evaluated. */
+    auto size_and_need = [&](size_t k) {
         const int32_t c[2] = {k0_[k], k1_[k]};
-        int32_t sz = 1, lvl = 0, nd[2] = {-1, -1};
+        int32_t sz = 1, nd[2] = {-1, -1};
         for (int j = 0; j < 2; j++)
-        {
-            if (c[j] < 0)
-                continue;
-            if (kcut_[c[j]])
-                lvl = std::max(lvl, klevel_[c[j]] + 1);
-            else
+            if (c[j] >= 0 && !kcut_[c[j]])
             {
                 sz += ksize_[c[j]];
-                lvl = std::max(lvl, klevel_[c[j]]);
                 nd[j] = kneed_[c[j]];
             }
-        }
         if (nd[0] >= 0 && nd[1] >= 0)
             kneed_[k] = std::max(std::max(nd[0], nd[1]), std::min(nd[0], nd[1]) + 1);
         else
             kneed_[k] = std::max(0, std::max(nd[0], nd[1]));
         ksize_[k] = sz;
-        klevel_[k] = lvl;
-        kcut_[k] = (piece_size > 0 && sz >= piece_size) ? 1 : 0;
+    };
+    for (size_t k = no; k-- > 0;)
+    {
+        kcut_[k] = 0;
+        klevel_[k] = 0;
+        size_and_need(k);
     }
 
-    /* emission.  A piece is the post-order of its nodes: a node comes right after the subtrees of
-     * its dirty children, the child that needs more stack slots first (its result is parked in a
-     * slot while the other is evaluated).  So the place of every instruction follows from the
-     * subtree sizes, and the stream is written in ONE top-down sweep over the discovery order —
-     * no recursion, no explicit stack:
-     *   start(v) = first index of v's subtree, its own instruction sits at start(v) + size(v) - 1;
-     *   depth(v) = slots in use while v's subtree is evaluated. */
+    /* Pieces.  Level 0: every MAXIMAL subtree of at most piece_size dirty nodes, packed into bins of
+     * about piece_size instructions — a piece is a forest, so the bins are balanced whatever the
+     * shape of the tree.  What is left (the "crown": nodes with more than piece_size nodes below
+     * them, about 2 d / piece_size of them in a random tree) is cut the same way with a limit of
+     * sqrt(2 W) while more than kCrownTop nodes are left, and the rest runs as the top piece with
+     * the root step.  Pieces of level L read, as ordinary HBM rows, rows stored by levels < L.
+     * The dependent chain of a launch is therefore one bin per level plus a small top piece,
+     * instead of one piece_size..2*piece_size subtree per level of a greedy bottom-up cut. */
     const uint32_t node_ctl = store ? LVB_CTL_STORE : 0u;
     int peak = 0;
     size_t cursor = out.size();
-    if (piece_size > 0)
-    { /* pieces cut off below: each is a complete post-order program of its own */
-        for (size_t k = no; k-- > 0;)
+    int top_level = 0;
+    tops_.clear();
+    if (piece_size > 0 && no > (size_t)piece_size) /* what fits one piece stays one piece */
+    {
+        constexpr size_t kCrownTop = 32; /* a crown this small is not worth another dependency hop */
+        constexpr int kMaxLevels = 6;
+        /* positions that have no dirty parent: the root's children and, in the general route,
+         * detached dirty subtrees */
+        if (dirtyp(rl))
+            tops_.push_back(pos_[rl]);
+        if (dirtyp(rr))
+            tops_.push_back(pos_[rr]);
+        for (size_t i = 0; !whole && i < dirty_.size(); i++)
+            if (const int32_t v = dirty_[i]; child_[v] != cur_ && v != rl && v != rr)
+                tops_.push_back(pos_[v]);
+        crown_.clear();
+        int64_t S = piece_size;
+        bool first = true;
+        while (top_level < kMaxLevels)
         {
-            if (!kcut_[k])
-                continue;
-            kstart_[k] = (int32_t)cursor;
-            kdepth_[k] = 0;
-            kpush_[k] = 0;
-            if (pieces)
-                pieces->push_back(Piece{(int32_t)cursor, ksize_[k], klevel_[k]});
-            cursor += (size_t)ksize_[k];
+            items_.clear();
+            next_.clear();
+            auto visit = [&](size_t k) {
+                if (ksize_[k] <= S)
+                    return;
+                next_.push_back((int32_t)k);
+                const int32_t c[2] = {k0_[k], k1_[k]};
+                for (int j = 0; j < 2; j++)
+                    if (c[j] >= 0 && !kcut_[c[j]] && ksize_[c[j]] <= S)
+                    {
+                        kcut_[c[j]] = 1;
+                        items_.push_back(c[j]);
+                    }
+            };
+            if (first)
+                for (size_t k = 0; k < no; k++)
+                    visit(k);
+            else
+                for (int32_t k : crown_)
+                    visit((size_t)k);
+            for (int32_t t : tops_)
+                if (!kcut_[t] && ksize_[t] <= S)
+                {
+                    kcut_[t] = 1;
+                    items_.push_back(t);
+                }
+            first = false;
+            crown_.swap(next_);
+            if (!items_.empty())
+            {
+                /* pack the subtrees of this level into bins: largest first, each into the emptiest bin */
+                int64_t total = 0;
+                for (int32_t k : items_)
+                    total += ksize_[k];
+                const size_t n_bins = (size_t)std::max<int64_t>(1, (total + S - 1) / S);
+                std::sort(items_.begin(), items_.end(), [&](int32_t a, int32_t b) {
+                    return ksize_[a] != ksize_[b] ? ksize_[a] > ksize_[b] : a < b;
+                });
+                bins_.assign(n_bins, std::pair<int64_t, int32_t>(0, 0));
+                for (size_t b = 0; b < n_bins; b++)
+                    bins_[b].second = (int32_t)b;
+                auto heavier = [](const std::pair<int64_t, int32_t> &a, const std::pair<int64_t, int32_t> &b) {
+                    return a.first != b.first ? a.first > b.first : a.second > b.second;
+                };
+                for (int32_t k : items_)
+                { /* bins_ is a min-heap on the load */
+                    std::pop_heap(bins_.begin(), bins_.end(), heavier);
+                    klevel_[k] = bins_.back().second; /* for now: the bin */
+                    bins_.back().first += ksize_[k];
+                    std::push_heap(bins_.begin(), bins_.end(), heavier);
+                }
+                /* lay the bins out one after the other */
+                bin_at_.assign(n_bins + 1, 0);
+                for (int32_t k : items_)
+                    bin_at_[(size_t)klevel_[k] + 1] += ksize_[k];
+                for (size_t b = 0; b < n_bins; b++)
+                {
+                    if (pieces && bin_at_[b + 1] > 0)
+                        pieces->push_back(Piece{(int32_t)(cursor + (size_t)bin_at_[b]), bin_at_[b + 1], top_level});
+                    bin_at_[b + 1] += bin_at_[b];
+                }
+                for (int32_t k : items_)
+                {
+                    const size_t b = (size_t)klevel_[k];
+                    kstart_[k] = (int32_t)(cursor + (size_t)bin_at_[b]);
+                    bin_at_[b] += ksize_[k];
+                    kdepth_[k] = 0;
+                    kpush_[k] = 0;
+                    klevel_[k] = top_level;
+                }
+                cursor += (size_t)total;
+                top_level++;
+                /* sizes and stack need of what is left, without the subtrees just cut */
+                for (size_t i = crown_.size(); i-- > 0;)
+                    size_and_need((size_t)crown_[i]);
+            }
+            if (crown_.size() <= kCrownTop || items_.empty())
+                break;
+            int64_t s2 = 6;
+            while (s2 * s2 < 2 * (int64_t)crown_.size())
+                s2++;
+            S = s2;
         }
     }
     const size_t last_begin = cursor;
-    int top_level = 0;
-    auto level_above = [&](int64_t v) {
-        if (dirtyp(v))
-            top_level = std::max(top_level, klevel_[pos_[v]] + (int)kcut_[pos_[v]]);
-    };
     /* dirty subtrees that do not hang under the root's children (only for dirty sets that are
      * not closed towards the root; LVB's operators never produce them, getplen would still
      * recompute them) */
     for (size_t i = 0; !whole && i < dirty_.size(); i++)
         if (const int32_t v = dirty_[i]; child_[v] != cur_ && v != rl && v != rr)
         {
-            level_above(v);
             const int32_t k = pos_[v];
             if (!kcut_[k])
             {
@@ -280,8 +360,6 @@ bool ScheduleCompiler::compile_impl(const lvb_gpu_topology &topo, bool store, st
         }
     /* root step, TreeEvaluation.c:238-264: fitch(root.left, root.right), never stored, then the
      * count against the root's own row */
-    level_above(rl);
-    level_above(rr);
     const int32_t krl = dirtyp(rl) ? pos_[rl] : ~(int32_t)rl, krr = dirtyp(rr) ? pos_[rr] : ~(int32_t)rr;
     auto inside = [&](int32_t c) { return c >= 0 && !kcut_[c]; }; /* evaluated inside the piece being emitted */
     auto row_of = [&](int32_t c) { return c >= 0 ? korder_[c] : ~c; };

@@ -10,6 +10,7 @@
 
 #include <cstdint>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/lvb_gpu.h"
@@ -37,9 +38,11 @@ class ScheduleCompiler
     /* Appends the program for `topo` to `out`.  store: set LVB_CTL_STORE on every node
      * instruction.  Returns false and sets err on a malformed topology.  n_slots receives the
      * number of stack slots the program uses.
-     * piece_size > 0 (store programs only): cut the dirty forest into subtrees of about
-     * piece_size..2*piece_size nodes; `pieces` receives them (the last one holds the root
-     * step).  piece_size == 0: one piece. */
+     * piece_size > 0 (store programs only): cut the dirty forest into pieces; `pieces` receives
+     * them in level order (the last one holds the root step).  Level 0 holds every maximal subtree of
+     * at most piece_size nodes, packed into bins (a piece is a FOREST of such subtrees) of about
+     * piece_size instructions; the nodes above them are cut again with a smaller limit while there
+     * are many, and the rest is the top piece.  piece_size == 0: one piece. */
     bool compile(const lvb_gpu_topology &topo, bool store, std::vector<FitchInstr> &out, int &n_slots,
                  std::string &err, int piece_size = 0, std::vector<Piece> *pieces = nullptr);
 
@@ -95,6 +98,10 @@ class ScheduleCompiler
     std::vector<uint8_t> kcut_;     /* the node is the root of a piece of its own */
     std::vector<int32_t> order_;    /* scratch (up-pass): discovery order */
     std::vector<int32_t> dirty_;    /* scratch: de-duplicated dirty list */
+    /* scratch of the piece cut: positions without a dirty parent, the crown (what is not cut yet),
+     * the subtrees cut at the current level and their bins (load, bin) */
+    std::vector<int32_t> tops_, crown_, next_, items_, bin_at_;
+    std::vector<std::pair<int64_t, int32_t>> bins_;
     std::vector<Frame> frames_;
 };
 

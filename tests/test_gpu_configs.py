@@ -104,7 +104,7 @@ def test_proposals_at_config_shapes(n, m, structured):
 @pytest.mark.skipif(not os.path.exists(oracles.REF_BIN), reason="oracle/_ref/lvb_ref not on this box")
 def test_config3_trajectory_prefix_vs_reference_binary():
     """BASELINE.json configs[2] shape, one chain: the reference (`lvb -v -p 1`) for 45 s of wall
-    clock, then lvb_gpu cut off after the same number of rearrangements (-x): the first K lines of
+    clock, then lvb_gpu cut off just after the same number of rearrangements (-x stops before the line of its last one): the first K lines of
     changeAccepted.tsv (operator, accepted, length, temperature, stack size per proposal) agree."""
     with tempfile.TemporaryDirectory() as td:
         os.makedirs(os.path.join(td, "ref"))
@@ -119,7 +119,7 @@ def test_config3_trajectory_prefix_vs_reference_binary():
         ref_lines = open(os.path.join(td, "ref", "changeAccepted.tsv"), "rb").read().split(b"\n")[:-1]  # complete lines
         k = len(ref_lines) - 1  # without the header
         assert k >= 500, k
-        p = subprocess.run([H.CLI, "-s", "12345", "-a", "1", "-v", "-x", str(k)], cwd=os.path.join(td, "gpu"),
+        p = subprocess.run([H.CLI, "-s", "12345", "-a", "1", "-v", "-x", str(k + 2)], cwd=os.path.join(td, "gpu"),
                            capture_output=True, text=True, timeout=600)
         assert p.returncode == 0, p.stdout[-800:]
         gpu_lines = open(os.path.join(td, "gpu", "changeAccepted.tsv"), "rb").read().split(b"\n")

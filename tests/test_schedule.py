@@ -214,9 +214,13 @@ def test_pieces_cover_the_program_and_respect_levels(golden_dir, piece_size):
     assert sorted(nodes[nodes >= 0].tolist()) == list(range(n, 2 * n - 3))
     if piece_size >= n:
         assert len(pieces) == 1
-    elif piece_size > 1:
-        sizes = pieces[:-1, 1]
-        assert (sizes >= piece_size).all() and (sizes <= 2 * piece_size - 1).all()
+    else:
+        # level 0: forests of maximal subtrees of at most piece_size nodes, packed largest-first into the
+        # emptiest bin: no bin holds more than piece_size + (the largest subtree) - 1 instructions
+        lvl0 = pieces[pieces[:, 2] == 0, 1]
+        assert (lvl0 <= 2 * piece_size - 1).all()
+        assert pieces[-1, 2] == pieces[:, 2].max() and (np.diff(pieces[:, 2]) >= 0).all()
+        assert set(pieces[:, 2].tolist()) == set(range(pieces[-1, 2] + 1))  # levels are contiguous
     # run level by level; within a level, pieces may only read leaves and rows of lower levels
     rows = fresh_rows(enc)
     stored_level = {}
