@@ -21,6 +21,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 
 namespace lvbgpu
@@ -883,11 +884,36 @@ static bool small_grid(unsigned grid)
     return grid <= limit;
 }
 
+/* Dynamic shared memory above 48 KB must be allowed per kernel (and device) first.  The limit only
+ * ever goes UP: several host threads (driver groups of one GPU) launch the same kernels with
+ * different sizes, and a thread that lowered the limit between another thread's call here and its
+ * launch would make that launch fail. */
 template <class K>
 static cudaError_t want_smem(K kernel, size_t smem)
 {
-    if (smem > 48 * 1024)
-        return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem <= 48 * 1024)
+        return cudaSuccess;
+    struct Key
+    {
+        const void *f;
+        int dev;
+        bool operator<(const Key &o) const { return f != o.f ? f < o.f : dev < o.dev; }
+    };
+    static std::mutex mu;
+    static std::map<Key, size_t> allowed;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return e;
+    std::lock_guard<std::mutex> lock(mu);
+    size_t &cur = allowed[Key{reinterpret_cast<const void *>(kernel), dev}];
+    if (cur >= smem)
+        return cudaSuccess;
+    /* in steps of 16 KB so that a slowly growing stack does not come back here every time */
+    const size_t want = std::min<size_t>((smem + 16383) / 16384 * 16384, 227 * 1024);
+    if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(want, smem))) != cudaSuccess)
+        return e;
+    cur = std::max(want, smem);
     return cudaSuccess;
 }
 
@@ -960,28 +986,27 @@ __device__ __forceinline__ void consumer_barrier(int nt)
     asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");
 }
 
-/* piece_finalize for the consumer threads of the streaming kernel (tid < nt; barrier 1) */
-__device__ __forceinline__ void stream_finalize(const ExecParams &p, const FitchInstr *instrs, const FitchProgram &prog,
-                                                int prog_id, int tid, int nt, unsigned *s_last, long long *s_acc)
+/* piece_finalize done by ONE warp (warp 0 of the consumers) while the other warps go on with the next
+ * piece: the column block of a piece that finishes last folds that piece's counts into chg / sum_chg,
+ * the piece of a candidate that is folded last publishes the candidate's length. */
+__device__ __forceinline__ void stream_finalize_warp(const ExecParams &p, const FitchInstr *instrs, const FitchProgram &prog,
+                                                     int prog_id, int lane)
 {
-    consumer_barrier(nt); /* this CTA's count atomics are issued */
-    if (tid == 0)
+    unsigned last = 0u;
+    if (lane == 0)
     {
-        __threadfence();
-        const unsigned last = atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u ? 1u : 0u;
+        __threadfence(); /* the count atomics of this CTA (issued by this warp, ordered by __syncwarp) first */
+        last = atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u ? 1u : 0u;
         if (last)
             p.done[prog_id] = 0u;
-        *s_last = last;
-        s_acc[0] = 0;
-        s_acc[1] = 0;
     }
-    consumer_barrier(nt);
-    if (!*s_last)
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last)
         return;
     __threadfence();
     int32_t *tchg = p.chg_rw + (int64_t)prog.tree * p.n_internal;
     long long delta = 0, rootc = 0;
-    for (int i = tid; i < prog.n_instr; i += nt)
+    for (int i = lane; i < prog.n_instr; i += 32)
     {
         const int node = instrs[prog.instr_begin + i].node;
         const int c = __ldcg(&p.cnts[prog.instr_begin + i]);
@@ -999,23 +1024,15 @@ __device__ __forceinline__ void stream_finalize(const ExecParams &p, const Fitch
         delta += __shfl_xor_sync(0xffffffffu, delta, o);
         rootc += __shfl_xor_sync(0xffffffffu, rootc, o);
     }
-    if ((tid & 31) == 0)
-    {
-        if (delta)
-            atomicAdd((unsigned long long *)&s_acc[0], (unsigned long long)delta);
-        if (rootc)
-            atomicAdd((unsigned long long *)&s_acc[1], (unsigned long long)rootc);
-    }
-    consumer_barrier(nt);
-    if (tid == 0)
+    if (lane == 0)
     {
         const int k = prog.pad1;
         const int ctree = p.cand[k].tree;
         const unsigned n_pieces = (unsigned)p.cand[k].n_wait;
-        if (s_acc[0])
-            atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], (unsigned long long)s_acc[0]);
-        if (s_acc[1])
-            atomicAdd(&p.totals[k], (unsigned long long)s_acc[1]);
+        if (delta)
+            atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], (unsigned long long)delta);
+        if (rootc)
+            atomicAdd(&p.totals[k], (unsigned long long)rootc);
         __threadfence();
         if (atomicAdd(&p.done[p.n_prog + k], 1u) == n_pieces - 1u)
         {
@@ -1032,8 +1049,6 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
     extern __shared__ uint4 smem_u4[];
     __shared__ __align__(8) unsigned long long s_bar[2 * LVB_SR + 4]; /* full[SR], empty[SR], ifull[2], iempty[2] */
     __shared__ StreamWork s_work[2];
-    __shared__ unsigned s_last;
-    __shared__ long long s_acc[2];
 
     const int nt = (int)blockDim.x - 32; /* consumer threads */
     const int nwarps = nt >> 5;
@@ -1090,8 +1105,50 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
             FitchProgram prog = {};
             if (!stop)
             {
-                prog_id = piece_major ? (int)(vb / (unsigned)p.n_colblocks) : (int)(vb % (unsigned)p.n_prog);
-                cb = piece_major ? (int)(vb % (unsigned)p.n_colblocks) : (int)(vb / (unsigned)p.n_prog);
+                if (piece_major && p.lag < 0)
+                { /* level by level, piece by piece (the level-0 bins get smaller towards the end), all column blocks */
+                    prog_id = (int)(vb / (unsigned)p.n_colblocks);
+                    cb = (int)(vb % (unsigned)p.n_colblocks);
+                }
+                else if (piece_major)
+                { /* ticket -> (piece, column block) in key order, key = cb + level * lag (ExecParams::lag) */
+                    const int ncb = p.n_colblocks, nl = p.n_levels, lag = p.lag;
+                    auto upto = [&](int k) { /* items with key <= k */
+                        unsigned c = 0;
+                        for (int L = 0; L < nl; L++)
+                            c += (unsigned)(p.level_off[L + 1] - p.level_off[L]) * (unsigned)min(max(k - L * lag + 1, 0), ncb);
+                        return c;
+                    };
+                    int lo = 0, hi = ncb - 1 + (nl - 1) * lag; /* smallest k with upto(k) > vb */
+                    while (lo < hi)
+                    {
+                        const int mid = (lo + hi) >> 1;
+                        if (upto(mid) > vb)
+                            hi = mid;
+                        else
+                            lo = mid + 1;
+                    }
+                    unsigned r = vb - (lo > 0 ? upto(lo - 1) : 0u);
+                    for (int L = 0; L < nl; L++)
+                    {
+                        const int c = lo - L * lag;
+                        if (c < 0 || c >= ncb)
+                            continue;
+                        const unsigned pl = (unsigned)(p.level_off[L + 1] - p.level_off[L]);
+                        if (r < pl)
+                        {
+                            prog_id = p.level_off[L] + (int)r;
+                            cb = c;
+                            break;
+                        }
+                        r -= pl;
+                    }
+                }
+                else
+                {
+                    prog_id = (int)(vb % (unsigned)p.n_prog);
+                    cb = (int)(vb / (unsigned)p.n_prog);
+                }
                 prog = p.prog[prog_id];
             }
             const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
@@ -1270,7 +1327,13 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
         const FitchProgram prog = s_work[buf].prog;
         const int base = s_work[buf].base, last = s_work[buf].last, prog_id = s_work[buf].prog_id;
         consumer_barrier(nt); /* counts and row stores of every consumer are issued */
-        for (int k = tid; k < m; k += nt)
+        if (tid >= 32)
+        { /* the other warps go on with the next chunk; warp 0 keeps the books of this one */
+            if (lane0)
+                mbar_arrive(iempty_bar(buf));
+            continue;
+        }
+        for (int k = tid; k < m; k += 32)
         {
             int sum = 0;
             for (int w = 0; w < nwarps; w++)
@@ -1289,7 +1352,7 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                 atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
             }
             if (p.fused_finalize)
-                stream_finalize(p, p.instr, prog, prog_id, tid, nt, &s_last, s_acc);
+                stream_finalize_warp(p, p.instr, prog, prog_id, tid);
         }
     }
 }

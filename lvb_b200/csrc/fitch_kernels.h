@@ -48,6 +48,15 @@ struct ExecParams
     int32_t n_cand;
     int32_t pipe_pf;             /* store mode, dependent pieces: 0 = register-pipelined kernel (fitch_exec_kernel),
                                   * 2/3/5/7 = cp.async ring with that many instructions of look-ahead */
+    int32_t level_off[LVB_DEP_LEVELS + 1]; /* streaming kernel, dependent pieces: pieces of level L are prog[level_off[L]
+                                  * .. level_off[L + 1]) (the pieces are sorted by level) */
+    int32_t n_levels;
+    int32_t lag;                 /* streaming kernel: work order.  < 0 (default): level by level, piece by piece, all column
+                                  * blocks of a piece together.  >= 0 (LVB_GPU_STREAM_LAG, measured: no gain): item (piece of level L, column block cb) has the key
+                                  * cb + L * lag; items are handed out by ascending key, so the upper levels of a column
+                                  * block follow `lag` column blocks behind its level below instead of after ALL column
+                                  * blocks of that level: by the time they are drawn their operands are normally there,
+                                  * and the end of the launch has only the last column blocks' small upper pieces left */
     int32_t stream_nt;           /* store mode: > 0 = the streaming kernel (TMA bulk loads, persistent CTAs) with this many
                                   * consumer threads per CTA; `block` of launch_fitch_exec is then ignored and
                                   * n_colblocks must have been computed with stream_nt columns per block; ticket must

@@ -144,7 +144,8 @@ struct lvb_gpu_ctx
     std::vector<std::string> c_err;
     std::vector<FitchProgram> prog;                    /* pieces, sorted by level */
     std::vector<std::pair<int32_t, int32_t>> levels;   /* (first piece, count) per launch */
-    int64_t target_warps = 148 * 192;                  /* resident warps wanted per launch */
+    int piece_min = 64;                                /* smallest piece size asked of the compiler (LVB_GPU_PIECE_MIN) */
+    int64_t target_warps = 148 * 128;                  /* resident warps wanted per launch */
     unsigned long long *d_totals = nullptr;            /* [cap_tot] per-program sums; zero between batches */
     unsigned *d_done = nullptr;                        /* [cap_tot] CTAs finished per program; zero between batches */
     long long *d_lengths = nullptr;                    /* [cap_tot] lengths on the device (site-block mode: all-reduced here) */
@@ -153,7 +154,11 @@ struct lvb_gpu_ctx
     size_t cap_dep = 0;
     size_t dep_ncb = 0;                                /* column blocks the counters in d_dep are laid out for */
     unsigned dep_total[LVB_DEP_LEVELS] = {};           /* value of d_dep[L][*] once every launch so far is complete */
-    unsigned last_level_count[LVB_DEP_LEVELS] = {};    /* pieces per level of the resident batch */
+    unsigned last_level_count[LVB_DEP_LEVELS] = {};    /* pieces per level of the resident batch that count themselves in */
+    unsigned last_level_pieces[LVB_DEP_LEVELS] = {};   /* pieces per level of the resident batch */
+    int sm_count = 148;
+    bool taper = true;                                 /* level-0 bins get smaller towards the end (LVB_GPU_TAPER=0: equal bins) */
+    int stream_lag = -1;                               /* LVB_GPU_STREAM_LAG: column-block lag between levels (-1 = automatic) */
     long long *d_nni = nullptr, *h_nni = nullptr;      /* [cap_nni] length differences of an NNI neighbourhood */
     size_t cap_nni = 0;
     int compile_par_min = 8;  /* host compile: batches of >= min candidates are spread over
@@ -164,7 +169,7 @@ struct lvb_gpu_ctx
     bool fuse_ok = true;     /* single-level store batches finalize inside the Fitch kernel (LVB_GPU_FUSE=0: own launch) */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
-    int stream_nt = 128;                               /* dependent-piece store launches: consumer threads per CTA of the
+    int stream_nt = 256;                               /* dependent-piece store launches: consumer threads per CTA of the
                                                         * streaming kernel (TMA bulk loads); 0 = the cp.async / register
                                                         * pipelined kernels below (LVB_GPU_STORE_STREAM) */
     int store_pf = 7;                                  /* dependent-piece store launches: 0 = register-pipelined kernel,
@@ -456,6 +461,22 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
             c->dep_total[L] += c->last_level_count[L];
         p.dep_target[L] = c->dep_total[L];
     }
+    p.n_levels = 1;
+    p.lag = -1;
+    p.level_off[0] = 0;
+    p.level_off[1] = (int32_t)c->last_n_prog;
+    if (c->last_dep)
+    { /* the pieces are sorted by level; last_level_pieces[] counts them (the top level included) */
+        int nl = 0;
+        for (int L = 0; L < LVB_DEP_LEVELS; L++)
+        {
+            p.level_off[L + 1] = p.level_off[L] + (int32_t)c->last_level_pieces[L];
+            if (c->last_level_pieces[L])
+                nl = L + 1;
+        }
+        p.n_levels = nl;
+        p.lag = c->stream_lag < 0 ? -1 : (int32_t)std::min<int64_t>(c->stream_lag, p.n_colblocks);
+    }
     if (c->last_dep && c->fault_dep)
     { /* test hook: the pieces above level 0 wait for a piece that does not exist */
         p.dep_target[0]++;
@@ -614,8 +635,12 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         if (want_pieces > 1)
         {
             const int64_t d = topos[k].n_dirty < 0 ? c->I : topos[k].n_dirty;
-            if (d >= 64) /* not worth a second launch for short programs */
-                piece_size = (int)std::max<int64_t>(4, (d + want_pieces - 1) / want_pieces);
+            /* not worth dependent pieces for short programs; and a piece costs its CTA a start-up and a drain
+             * (ticket, decode, refill of the operand ring, bookkeeping), which pieces under piece_min
+             * instructions do not earn back even when that leaves fewer CTAs than the device can hold
+             * (measured on the word blocks of an 8-GPU run, profiles/r02*_sweep*) */
+            if (d >= 64)
+                piece_size = (int)std::max<int64_t>(c->piece_min, (d + want_pieces - 1) / want_pieces);
         }
         c->c_instr[k].clear();
         c->c_pieces[k].clear();
@@ -712,9 +737,12 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
                 return fail("internal error: %d piece levels", top + 1);
             for (int L = 0; L < LVB_DEP_LEVELS; L++)
                 c->last_level_count[L] = 0;
+            for (int L = 0; L < LVB_DEP_LEVELS; L++)
+                c->last_level_pieces[L] = 0;
             for (FitchProgram &pg : c->prog)
             {
                 c->last_level_count[pg.flags]++;
+                c->last_level_pieces[pg.flags]++;
                 pg.parent = pg.flags < top ? pg.flags : -1;
                 pg.n_wait = 0;
             }
@@ -831,7 +859,10 @@ static int alloc_matrix(lvb_gpu_ctx *c, int64_t n, int64_t nwords, int64_t word_
     nsc = std::max(1, std::min(16, omp_get_max_threads()));
 #endif
     for (int i = 0; i < nsc; i++)
+    {
         c->sc.push_back(new ScheduleCompiler(n));
+        c->sc.back()->set_taper(c->taper);
+    }
     return 0;
 }
 
@@ -927,6 +958,15 @@ extern "C"
             const int v = atoi(sst);
             c->stream_nt = v <= 0 ? 0 : std::min(256, std::max(32, v / 32 * 32));
         }
+        const char *pm = getenv("LVB_GPU_PIECE_MIN");
+        if (pm && atoi(pm) >= 1)
+            c->piece_min = atoi(pm);
+        const char *tp = getenv("LVB_GPU_TAPER");
+        c->taper = !(tp && atoi(tp) == 0);
+        const char *slg = getenv("LVB_GPU_STREAM_LAG");
+        if (slg)
+            c->stream_lag = atoi(slg);
+        cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
         const char *spf = getenv("LVB_GPU_STORE_PF");
         if (spf)
             c->store_pf = atoi(spf);

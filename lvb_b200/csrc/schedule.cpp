@@ -288,26 +288,53 @@ bool ScheduleCompiler::compile_impl(const lvb_gpu_topology &topo, bool store, st
             crown_.swap(next_);
             if (!items_.empty())
             {
-                /* pack the subtrees of this level into bins: largest first, each into the emptiest bin */
+                /* pack the subtrees of this level into bins, largest first.  Level 0 is handed out piece by piece
+                 * (all column blocks of a bin, then the next bin), so its bins get SMALLER towards the end —
+                 * full size for the first 3/4 of the work, then half, a quarter, an eighth of it (guided
+                 * self-scheduling): the launch runs dry on small items instead of on whole bins.  Upper levels:
+                 * equal bins, each subtree into the emptiest one. */
                 int64_t total = 0;
                 for (int32_t k : items_)
                     total += ksize_[k];
-                const size_t n_bins = (size_t)std::max<int64_t>(1, (total + S - 1) / S);
                 std::sort(items_.begin(), items_.end(), [&](int32_t a, int32_t b) {
                     return ksize_[a] != ksize_[b] ? ksize_[a] > ksize_[b] : a < b;
                 });
-                bins_.assign(n_bins, std::pair<int64_t, int32_t>(0, 0));
-                for (size_t b = 0; b < n_bins; b++)
-                    bins_[b].second = (int32_t)b;
-                auto heavier = [](const std::pair<int64_t, int32_t> &a, const std::pair<int64_t, int32_t> &b) {
-                    return a.first != b.first ? a.first > b.first : a.second > b.second;
-                };
-                for (int32_t k : items_)
-                { /* bins_ is a min-heap on the load */
-                    std::pop_heap(bins_.begin(), bins_.end(), heavier);
-                    klevel_[k] = bins_.back().second; /* for now: the bin */
-                    bins_.back().first += ksize_[k];
-                    std::push_heap(bins_.begin(), bins_.end(), heavier);
+                size_t n_bins = 0;
+                if (top_level == 0 && taper_ && S >= 48)
+                {
+                    int64_t filled = 0, load = 0, cap = S;
+                    for (int32_t k : items_)
+                    {
+                        if (load > 0 && load + ksize_[k] > cap + cap / 4)
+                        { /* next bin */
+                            n_bins++;
+                            load = 0;
+                            const int64_t left = total - filled;
+                            cap = left * 4 > total ? S : left * 8 > total ? S / 2 : left * 16 > total ? S / 4 : S / 8;
+                            cap = std::max<int64_t>(cap, 4);
+                        }
+                        klevel_[k] = (int32_t)n_bins; /* for now: the bin */
+                        load += ksize_[k];
+                        filled += ksize_[k];
+                    }
+                    n_bins++;
+                }
+                else
+                {
+                    n_bins = (size_t)std::max<int64_t>(1, (total + S - 1) / S);
+                    bins_.assign(n_bins, std::pair<int64_t, int32_t>(0, 0));
+                    for (size_t b = 0; b < n_bins; b++)
+                        bins_[b].second = (int32_t)b;
+                    auto heavier = [](const std::pair<int64_t, int32_t> &a, const std::pair<int64_t, int32_t> &b) {
+                        return a.first != b.first ? a.first > b.first : a.second > b.second;
+                    };
+                    for (int32_t k : items_)
+                    { /* bins_ is a min-heap on the load */
+                        std::pop_heap(bins_.begin(), bins_.end(), heavier);
+                        klevel_[k] = bins_.back().second; /* for now: the bin */
+                        bins_.back().first += ksize_[k];
+                        std::push_heap(bins_.begin(), bins_.end(), heavier);
+                    }
                 }
                 /* lay the bins out one after the other */
                 bin_at_.assign(n_bins + 1, 0);

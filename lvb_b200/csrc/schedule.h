@@ -48,6 +48,9 @@ class ScheduleCompiler
 
     int64_t n() const { return n_; }
 
+    /* level-0 bins of equal size instead of bins that get smaller towards the end (A/B switch) */
+    void set_taper(bool on) { taper_ = on; }
+
     /* The up-pass of a whole tree: one store instruction per internal node v computing
      * up(v) = the Fitch set of everything that is NOT below v (the tree seen from v's parent
      * branch): up(v) = fitch(up(parent), low(sister)), and fitch(row(root), low(sister)) for
@@ -75,6 +78,7 @@ class ScheduleCompiler
     };
     bool is_dirty(int64_t v) const { return v >= n_ && v < B_ && stamp_[v] == cur_; }
     int64_t n_, B_;
+    bool taper_ = true;
     uint32_t cur_;
     /* indexed by node */
     std::vector<uint32_t> stamp_;   /* dirty marks */

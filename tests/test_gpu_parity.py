@@ -474,3 +474,40 @@ def test_nni_neighbourhood_2000x1M(engine):
     assert np.array_equal(got[idx], want)
     engine.tree_destroy(t)
     engine.tree_destroy(s)
+
+
+@pytest.mark.parametrize("env", [
+    {},                                                        # default: streaming kernel, tapered bins
+    {"LVB_GPU_PIECE_MIN": "4", "LVB_GPU_TARGET_WARPS": str(148 * 4096)},  # many small pieces: every level of the cut
+    {"LVB_GPU_PIECE_MIN": "4", "LVB_GPU_STORE_STREAM": "64", "LVB_GPU_STREAM_LAG": "3"},  # lagged work order
+    {"LVB_GPU_TAPER": "0", "LVB_GPU_STORE_STREAM": "128"},
+    {"LVB_GPU_STORE_STREAM": "0", "LVB_GPU_STORE_PF": "7", "LVB_GPU_PIECE_MIN": "8"},  # cp.async ring kernel
+    {"LVB_GPU_STORE_STREAM": "0", "LVB_GPU_STORE_PF": "0", "LVB_GPU_PIECE_MIN": "8"},  # register-pipelined kernel
+    {"LVB_GPU_STORE_STREAM": "0", "LVB_GPU_LEVEL_LAUNCHES": "1", "LVB_GPU_PIECE_MIN": "8"},  # one launch per level
+])
+def test_dependent_piece_store_routes(monkeypatch, env):
+    """a whole-tree evaluation is cut into dependent pieces (forests in level-0 bins, the crown above
+    them) and run in ONE launch: every kernel route and every setting of the cut gives the oracle's
+    length, per-node counts and rows — three passes in a row (the level counters run on from launch to
+    launch), for two topologies on the same device tree"""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    n, m = 700, 40_000
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=11, p=0.1))
+    eng = Engine(0)
+    try:
+        eng.upload(enc, max_trees=2)
+        t = eng.tree_create()
+        for seed in (21, 22):
+            left, right, root = synthetic.random_topology(n, seed=seed)
+            want, rows, chg = oracles.oracle_getplen(enc, left, right, root)
+            assert eng.commit(t, Topology(left, right, root)) == want
+            eng.rerun_last_batch()
+            eng.rerun_last_batch()
+            eng.synchronize()
+            assert eng.commit(t, Topology(left, right, root)) == want, (env, seed)
+            assert np.array_equal(eng.changes(t)[n:], chg[n:]), (env, seed)
+            for v in list(range(n, 2 * n - 3, 37)) + [2 * n - 4]:
+                assert np.array_equal(eng.download_row(t, v), rows[v]), (env, seed, v)
+    finally:
+        eng.close()

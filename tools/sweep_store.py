@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--warps", default="96,192,384,768,1536")
     ap.add_argument("--block", default="256,128")
     ap.add_argument("--shards", default="1,8")
+    ap.add_argument("--taper", default="1", help="LVB_GPU_TAPER values")
+    ap.add_argument("--lag", default="-1", help="LVB_GPU_STREAM_LAG values (-1 = automatic)")
     ap.add_argument("--stream", default="0", help="LVB_GPU_STORE_STREAM values (consumer threads of the TMA streaming kernel; 0 = the other kernels)")
     args = ap.parse_args()
 
@@ -48,12 +50,15 @@ def main():
         grid = []
         for st in args.stream.split(","):
             if int(st) > 0:
-                grid += [(st, "0", tw, "256") for tw in args.warps.split(",")]
+                grid += [(st, lg, tw, "256") for lg in args.lag.split(",") for tw in args.warps.split(",")]
             else:
                 grid += [(st, pf, tw, blk) for pf, tw, blk in itertools.product(args.pf.split(","), args.warps.split(","), args.block.split(","))]
-        for st, pf, tw, blk in grid:
+        grid = [(st, pf, tw, blk, tp) for tp in args.taper.split(",") for st, pf, tw, blk in grid]
+        for st, pf, tw, blk, tp in grid:
+            os.environ["LVB_GPU_TAPER"] = tp
             os.environ["LVB_GPU_STORE_STREAM"] = st
-            os.environ["LVB_GPU_STORE_PF"] = pf
+            os.environ["LVB_GPU_STORE_PF"] = pf if int(st) == 0 else "0"
+            os.environ["LVB_GPU_STREAM_LAG"] = pf if int(st) > 0 else "-1"
             os.environ["LVB_GPU_TARGET_WARPS"] = str(148 * int(tw))
             os.environ["LVB_GPU_BLOCK"] = blk
             eng = Engine(0)
@@ -76,13 +81,13 @@ def main():
                 k_ms, k_n = eng.kernel_time()
                 key = shards
                 want.setdefault(key, length)
-                print(json.dumps({"shards": shards, "words": wc, "stream": int(st), "pf": int(pf), "target_warps_per_sm": int(tw),
+                print(json.dumps({"shards": shards, "words": wc, "stream": int(st), "taper": int(tp), "pf_or_lag": int(pf), "target_warps_per_sm": int(tw),
                                   "block": int(blk), "kernel_ms": round(k_ms / max(1, k_n), 4),
                                   "stream_ms": round(e0.elapsed_time(e1) / args.reps, 4),
                                   "launches_per_pass": (eng.launches - l0) / args.reps, "length": int(length),
                                   "length_ok": bool(length == want[key])}), flush=True)
             except Exception as exc:
-                print(json.dumps({"shards": shards, "stream": int(st), "pf": int(pf), "target_warps_per_sm": int(tw), "block": int(blk),
+                print(json.dumps({"shards": shards, "stream": int(st), "pf_or_lag": int(pf), "target_warps_per_sm": int(tw), "block": int(blk),
                                   "error": str(exc)[:200]}), flush=True)
             finally:
                 eng.close()
