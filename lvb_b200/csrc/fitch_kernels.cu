@@ -176,6 +176,46 @@ __device__ __forceinline__ void fitch_commit_finalize_body(const FitchInstr *ins
 }
 
 
+/* one value of the peer-memory all-reduce (see P2PParams): this rank's partial sum `v` of entry k goes into
+ * its row of every rank's slab, then the rows of all ranks that arrived in the own slab are added, in rank
+ * order.  Returns the sum; on a wait that was abandoned sets *q.err and returns the partial value. */
+__device__ __forceinline__ long long p2p_exchange_one(const P2PParams &q, int64_t k, long long pv)
+{
+    const unsigned long long v = (unsigned long long)pv;
+    const unsigned long long tag = (unsigned long long)q.seq << 32;
+    const unsigned long long w0 = tag | (v & 0xffffffffull), w1 = tag | (v >> 32);
+    const size_t mine = 2 * (((size_t)q.slot * q.nranks + q.rank) * (size_t)q.kmax + (size_t)k);
+    for (int r = 0; r < q.nranks; r++)
+    {
+        /* start with the next rank so that the ranks do not all write to rank 0 first */
+        const int d = (q.rank + 1 + r) % q.nranks;
+        volatile unsigned long long *dst = q.peer[d] + mine;
+        dst[0] = w0;
+        dst[1] = w1;
+    }
+    long long sum = 0;
+    for (int r = 0; r < q.nranks; r++)
+    {
+        const volatile unsigned long long *e =
+            q.peer[q.rank] + 2 * (((size_t)q.slot * q.nranks + r) * (size_t)q.kmax + (size_t)k);
+        unsigned long long a = e[0], b = e[1];
+        unsigned spins = 0;
+        while ((a >> 32) != q.seq || (b >> 32) != q.seq)
+        {
+            __nanosleep(50);
+            if ((++spins & 1023u) == 0u && (spins >= q.spin_limit || *(volatile unsigned *)q.err != 0u))
+            {
+                atomicCAS(q.err, 0u, 0x80000000u | (unsigned)r);
+                return pv;
+            }
+            a = e[0];
+            b = e[1];
+        }
+        sum += (long long)(((b & 0xffffffffull) << 32) | (a & 0xffffffffull));
+    }
+    return sum;
+}
+
 /* ---- dependent pieces in one launch (store mode) -------------------------------------------
  * A piece waits, per column block, for the pieces whose stored rows it reads.  CTAs are numbered
  * in the order they START (pieces are sorted by level, children before parents), so a waiting CTA
@@ -308,7 +348,14 @@ __device__ __forceinline__ void piece_finalize(const ExecParams &p, const FitchI
             __threadfence();
             p.done[p.n_prog + k] = 0u;
             const long long sum = (long long)atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], 0ull);
-            p.out[k] = sum + (long long)atomicExch(&p.totals[k], 0ull);
+            long long len = sum + (long long)atomicExch(&p.totals[k], 0ull);
+            if (p.fuse_p2p)
+            { /* site blocks: this rank's partial length -> every rank, their partial lengths -> the sum */
+                len = p2p_exchange_one(p.x, k, len);
+                if (p.x.out2)
+                    p.x.out2[k] = len;
+            }
+            p.out[k] = len;
         }
     }
 }
@@ -1039,7 +1086,14 @@ __device__ __forceinline__ void stream_finalize_warp(const ExecParams &p, const 
             __threadfence();
             p.done[p.n_prog + k] = 0u;
             const long long sum = (long long)atomicAdd((unsigned long long *)&p.sum_chg_rw[ctree], 0ull);
-            p.out[k] = sum + (long long)atomicExch(&p.totals[k], 0ull);
+            long long len = sum + (long long)atomicExch(&p.totals[k], 0ull);
+            if (p.fuse_p2p)
+            { /* site blocks: this rank's partial length -> every rank, their partial lengths -> the sum */
+                len = p2p_exchange_one(p.x, k, len);
+                if (p.x.out2)
+                    p.x.out2[k] = len;
+            }
+            p.out[k] = len;
         }
     }
 }
@@ -1398,12 +1452,11 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
         return launch_fitch_stream(p, p.stream_nt, stream);
     if (per_node && p.dep && p.pipe_pf > 0)
     {
-        const int pf = p.pipe_pf >= 7 ? 7 : p.pipe_pf >= 5 ? 5 : p.pipe_pf >= 3 ? 3 : 2;
+        const int pf = p.pipe_pf >= 7 ? 7 : p.pipe_pf >= 5 ? 5 : 3;
         const size_t sm = pipe_smem_bytes(true, pf, p.n_slots, block);
         void (*k)(const ExecParams) = pf == 7   ? fitch_store_pipe_kernel<7>
                                       : pf == 5 ? fitch_store_pipe_kernel<5>
-                                      : pf == 3 ? fitch_store_pipe_kernel<3>
-                                                : fitch_store_pipe_kernel<2>;
+                                                : fitch_store_pipe_kernel<3>;
         if ((e = want_smem(k, sm)) != cudaSuccess)
             return e;
         k<<<grid, block, sm, stream>>>(p);
@@ -1790,38 +1843,9 @@ __global__ void __launch_bounds__(256) p2p_allreduce_kernel(const __grid_constan
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= q.K)
         return;
-    const unsigned long long v = (unsigned long long)q.in[k];
-    const unsigned long long tag = (unsigned long long)q.seq << 32;
-    const unsigned long long w0 = tag | (v & 0xffffffffull), w1 = tag | (v >> 32);
-    const size_t mine = 2 * (((size_t)q.slot * q.nranks + q.rank) * (size_t)q.kmax + (size_t)k);
-    for (int r = 0; r < q.nranks; r++)
-    {
-        /* start with the next rank so that the ranks do not all write to rank 0 first */
-        const int d = (q.rank + 1 + r) % q.nranks;
-        volatile unsigned long long *dst = q.peer[d] + mine;
-        dst[0] = w0;
-        dst[1] = w1;
-    }
-    long long sum = 0;
-    for (int r = 0; r < q.nranks; r++)
-    {
-        const volatile unsigned long long *e =
-            q.peer[q.rank] + 2 * (((size_t)q.slot * q.nranks + r) * (size_t)q.kmax + (size_t)k);
-        unsigned long long a = e[0], b = e[1];
-        unsigned spins = 0;
-        while ((a >> 32) != q.seq || (b >> 32) != q.seq)
-        {
-            __nanosleep(50);
-            if ((++spins & 1023u) == 0u && (spins >= q.spin_limit || *(volatile unsigned *)q.err != 0u))
-            {
-                atomicCAS(q.err, 0u, 0x80000000u | (unsigned)r);
-                return;
-            }
-            a = e[0];
-            b = e[1];
-        }
-        sum += (long long)(((b & 0xffffffffull) << 32) | (a & 0xffffffffull));
-    }
+    const long long sum = p2p_exchange_one(q, k, q.in[k]);
+    if (*(volatile unsigned *)q.err != 0u)
+        return;
     q.out[k] = sum;
     if (q.out2)
         q.out2[k] = sum;

@@ -11,6 +11,31 @@ namespace lvbgpu
 {
 
 /* Everything a batch launch needs; lives in kernel parameter space. */
+/* Sum of K int64 over the ranks of a site-block run through PEER MEMORY (NVLink / NVSwitch loads and
+ * stores between the GPUs of one box) instead of a collective library call: every rank owns a slab
+ * that all ranks have mapped (CUDA IPC); rank r writes its K partial values into its own row of slot
+ * (seq mod slots) of EVERY rank's slab, then sums the nranks rows that arrived in its own slab.
+ * An entry is two 8-byte words {low half | seq << 32}, {high half | seq << 32}: an 8-byte store is
+ * atomic, so the sequence number doubles as the arrival flag (no separate flag, no fence between
+ * data and flag).  Every rank adds the rows in the same order.  A rank can run at most one call
+ * ahead of the slowest one, so two slots would do; there are four. */
+#define LVB_P2P_MAX_RANKS 16
+#define LVB_P2P_SLOTS 4
+struct P2PParams
+{
+    unsigned long long *peer[LVB_P2P_MAX_RANKS]; /* peer[r]: rank r's slab as mapped on this rank (peer[rank] = own) */
+    int32_t nranks, rank;
+    int32_t slot;               /* seq % LVB_P2P_SLOTS */
+    uint32_t seq;               /* call number, never 0 */
+    int64_t kmax;               /* entries per row */
+    int64_t K;
+    const long long *in;        /* [K] this rank's partial values */
+    long long *out;             /* [K] the sums (may alias in) */
+    long long *out2;            /* optional second destination (mapped host memory), or NULL */
+    unsigned *err;              /* mapped host word: set to 0x80000000 | rank that did not arrive */
+    unsigned spin_limit;
+};
+
 #define LVB_DEP_LEVELS 8 /* piece levels of one launch (schedule.cpp cuts at most 7) */
 
 struct ExecParams
@@ -57,6 +82,11 @@ struct ExecParams
                                   * block follow `lag` column blocks behind its level below instead of after ALL column
                                   * blocks of that level: by the time they are drawn their operands are normally there,
                                   * and the end of the launch has only the last column blocks' small upper pieces left */
+    int32_t fuse_p2p;            /* streaming kernel, fused finalize, site-block mode: the thread that completes a
+                                  * candidate's partial length exchanges it with the other ranks through peer memory
+                                  * right there (x: in/out/K unused; the candidate number is the entry) — the launch
+                                  * IS the all-reduce, no second kernel.  out[k] and x.out2[k] receive the sum */
+    P2PParams x;
     int32_t stream_nt;           /* store mode: > 0 = the streaming kernel (TMA bulk loads, persistent CTAs) with this many
                                   * consumer threads per CTA; `block` of launch_fitch_exec is then ignored and
                                   * n_colblocks must have been computed with stream_nt columns per block; ticket must
@@ -122,30 +152,6 @@ cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int
 cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *sums,
                                 cudaStream_t stream);
 
-/* Sum of K int64 over the ranks of a site-block run through PEER MEMORY (NVLink / NVSwitch loads and
- * stores between the GPUs of one box) instead of a collective library call: every rank owns a slab
- * that all ranks have mapped (CUDA IPC); rank r writes its K partial values into its own row of slot
- * (seq mod slots) of EVERY rank's slab, then sums the nranks rows that arrived in its own slab.
- * An entry is two 8-byte words {low half | seq << 32}, {high half | seq << 32}: an 8-byte store is
- * atomic, so the sequence number doubles as the arrival flag (no separate flag, no fence between
- * data and flag).  Every rank adds the rows in the same order.  A rank can run at most one call
- * ahead of the slowest one, so two slots would do; there are four. */
-#define LVB_P2P_MAX_RANKS 16
-#define LVB_P2P_SLOTS 4
-struct P2PParams
-{
-    unsigned long long *peer[LVB_P2P_MAX_RANKS]; /* peer[r]: rank r's slab as mapped on this rank (peer[rank] = own) */
-    int32_t nranks, rank;
-    int32_t slot;               /* seq % LVB_P2P_SLOTS */
-    uint32_t seq;               /* call number, never 0 */
-    int64_t kmax;               /* entries per row */
-    int64_t K;
-    const long long *in;        /* [K] this rank's partial values */
-    long long *out;             /* [K] the sums (may alias in) */
-    long long *out2;            /* optional second destination (mapped host memory), or NULL */
-    unsigned *err;              /* mapped host word: set to 0x80000000 | rank that did not arrive */
-    unsigned spin_limit;
-};
 cudaError_t launch_p2p_allreduce(const P2PParams &p, cudaStream_t stream);
 
 } // namespace lvbgpu

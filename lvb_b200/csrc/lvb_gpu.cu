@@ -214,6 +214,7 @@ struct lvb_gpu_ctx
     unsigned long long *p2p_peer[LVB_P2P_MAX_RANKS] = {};
     int64_t p2p_kmax = 8192;
     uint32_t p2p_seq = 0;
+    bool p2p_fuse = true;                              /* LVB_GPU_P2P_FUSE=0: always the separate all-reduce kernel */
 
     /* LVB_GPU_PROFILE=1: host seconds per stage of commit/score calls, printed at shutdown */
     bool profile = false;
@@ -461,6 +462,29 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
             c->dep_total[L] += c->last_level_count[L];
         p.dep_target[L] = c->dep_total[L];
     }
+    /* site blocks, dependent pieces with the finalize inside the kernel: the kernel also exchanges the partial
+     * lengths over peer memory (no all-reduce launch behind it) */
+    const bool want_reduce = c->comm && (lengths || !store || reduce_always || defer);
+    const bool fuse_p2p = want_reduce && fused && c->last_dep && c->p2p && c->p2p_fuse && K <= c->p2p_kmax;
+    p.fuse_p2p = fuse_p2p ? 1 : 0;
+    if (fuse_p2p)
+    {
+        for (int r = 0; r < LVB_P2P_MAX_RANKS; r++)
+            p.x.peer[r] = c->p2p_peer[r];
+        p.x.nranks = c->nranks;
+        p.x.rank = c->rank;
+        if (++c->p2p_seq == 0u)
+            c->p2p_seq = 1u;
+        p.x.seq = c->p2p_seq;
+        p.x.slot = (int32_t)(c->p2p_seq % LVB_P2P_SLOTS);
+        p.x.kmax = c->p2p_kmax;
+        p.x.K = K;
+        p.x.in = nullptr;
+        p.x.out = nullptr;
+        p.x.out2 = (lengths || defer) ? st.d_len : nullptr;
+        p.x.err = c->d_err;
+        p.x.spin_limit = c->spin_limit;
+    }
     p.n_levels = 1;
     p.lag = -1;
     p.level_off[0] = 0;
@@ -532,7 +556,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
                                   c->last_max_instr, c->stream));
         c->launches++;
     }
-    if (c->comm && (lengths || !store || reduce_always || defer))
+    if (want_reduce && !fuse_p2p)
     {
         bool wrote = false;
         if (allreduce_i64(c, c->d_lengths, K, (lengths || defer) ? st.d_len : nullptr, &wrote))
@@ -1075,23 +1099,18 @@ extern "C"
         const int64_t site0 = word_begin * 16;
         const int64_t site1 = std::min<int64_t>(m, (word_begin + word_count) * 16);
         const int64_t mloc = site1 - site0;
-        unsigned char *d_text = nullptr, *h_text = nullptr;
+        unsigned char *d_text = nullptr;
         int *d_bad = nullptr;
         CU(cudaMalloc(&d_text, (size_t)n * mloc));
         CU(cudaMalloc(&d_bad, sizeof(int)));
         CU(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
-        const size_t chunk_rows = std::max<size_t>(1, std::min<size_t>((size_t)n, (64u << 20) / (size_t)mloc));
-        CU(cudaMallocHost(&h_text, chunk_rows * mloc));
+        /* row by row straight from the caller's (pageable) memory: the driver stages each copy itself;
+         * a pinned staging buffer of our own costs more to allocate than it saves (measured) */
         int rc = 0;
-        for (int64_t r0 = 0; r0 < n && !rc; r0 += (int64_t)chunk_rows)
+        for (int64_t r = 0; r < n && !rc; r++)
         {
-            const int64_t nr = std::min<int64_t>((int64_t)chunk_rows, n - r0);
-            for (int64_t r = 0; r < nr; r++)
-                memcpy(h_text + r * mloc, rows[r0 + r] + site0, (size_t)mloc);
-            cudaError_t e = cudaMemcpyAsync(d_text + r0 * mloc, h_text, (size_t)nr * mloc, cudaMemcpyHostToDevice,
-                                            c->stream);
-            if (e == cudaSuccess)
-                e = cudaStreamSynchronize(c->stream);
+            const cudaError_t e = cudaMemcpyAsync(d_text + r * mloc, rows[r] + site0, (size_t)mloc, cudaMemcpyHostToDevice,
+                                                  c->stream);
             if (e != cudaSuccess)
                 rc = fail("text upload failed: %s", cudaGetErrorString(e));
         }
@@ -1110,7 +1129,6 @@ extern "C"
         }
         cudaFree(d_text);
         cudaFree(d_bad);
-        cudaFreeHost(h_text);
         if (!rc && bad)
             rc = fail("bad base symbol in data MSA: %c (cannot read data MSA)", (char)(bad - 1));
         return rc;
@@ -1432,6 +1450,7 @@ extern "C"
             p.n_cand = 0;
             p.pipe_pf = 0;
             p.stream_nt = 0;
+            p.fuse_p2p = 0;
             p.err = c->d_err;
             p.spin_limit = c->spin_limit;
             const size_t level_first[2] = {0, n_level0}, level_count[2] = {n_level0, n_pcs - n_level0};
@@ -1578,6 +1597,8 @@ extern "C"
         /* peer-memory all-reduce: one slab per rank, mapped by every rank through CUDA IPC; the 64-byte
          * handles travel through the communicator that was just made */
         const char *pp = getenv("LVB_GPU_P2P");
+        const char *pfz = getenv("LVB_GPU_P2P_FUSE");
+        c->p2p_fuse = !(pfz && atoi(pfz) == 0);
         c->p2p = false;
         if (!(pp && atoi(pp) == 0) && nranks <= LVB_P2P_MAX_RANKS && g_nccl.AllGather)
         {

@@ -2,6 +2,9 @@
  * same functions the `lvb` binary uses.  Thin call-throughs only. */
 #include <cstring>
 
+#include <chrono>
+#include <cstdlib>
+
 #include "lvb_host.h"
 
 using namespace lvbhost;
@@ -279,7 +282,11 @@ int lvbh_search(void *hv, int device, int seed, int algorithm, int cooling, int 
         rc.groups = groups < 0 ? 0 : groups;
         rc.device = device;
         Device dev;
+        const auto t_open = std::chrono::steady_clock::now();
         device_open(dev, device, &h->msa, replicates);
+        if (getenv("LVB_GPU_PROFILE"))
+            fprintf(stderr, "[lvbh_search] device_open (alignment packed and on the device, %d trees allocated): %.3f s\n", replicates,
+                    std::chrono::duration<double>(std::chrono::steady_clock::now() - t_open).count());
         FILE *tsv = tsv_path ? fopen(tsv_path, "w") : nullptr;
         std::vector<TREESTACK> stacks;
         std::vector<SearchResult> results;
