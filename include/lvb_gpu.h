@@ -159,6 +159,31 @@ int lvb_gpu_commit_batch_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees,
 int lvb_gpu_score_batch_submit_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
                                    const lvb_gpu_program_view *pre, int *ticket);
 
+/* ---- score AND keep: Solve.c:300-323, 366-370 without the second evaluation.  The reference scores a
+ * proposal with getplen on a copy of the tree (treecopy + mutate, :288-300) and, if it is accepted,
+ * SwapTrees makes the copy the tree (:323, :370) — the rows getplen wrote are kept.  The plain calls above
+ * score read-only and pay a commit (the same rows again, now stored) for an accepted proposal.  Here a
+ * candidate with keep[k] != 0 is scored with its rows STORED — into spare rows of its tree, which nothing
+ * else reads — and lvb_gpu_accept_kept() afterwards makes it the tree by switching the tree's nodes over to
+ * those rows and installing the candidate's per-node counts: no second pass over the rows.  A candidate that
+ * is not accepted costs nothing more; the tree is as it was.  Worth it when a proposal is more likely
+ * accepted than not (the early, hot phase of the annealing): a kept candidate writes a row per node it
+ * reads.  At most ONE kept candidate per tree and batch; candidates with keep[k] == 0 are scored read-only
+ * as by lvb_gpu_score_batch.  The lengths are the ones lvb_gpu_score_batch returns.
+ *   lvb_gpu_score_keep_submit_pre  asynchronous, programs from the caller (pre[k] compiled with store = 0;
+ *                                  pre may be NULL or pre[k].instr NULL: compiled here); lengths through
+ *                                  lvb_gpu_batch_wait(ticket)
+ *   lvb_gpu_score_keep             the same, synchronous, compiled here
+ *   lvb_gpu_accept_kept            cands[i] = index of a kept candidate in the batch named by `ticket`; the
+ *                                  batch must still be held: at most 7 device calls after its submit, and
+ *                                  after its lengths were fetched.  Returns without waiting for the device;
+ *                                  the trees count as changed for every later call. */
+int lvb_gpu_score_keep_submit_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                  const lvb_gpu_program_view *pre, const uint8_t *keep, int *ticket);
+int lvb_gpu_score_keep(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                       const uint8_t *keep, int64_t *lengths, int *ticket);
+int lvb_gpu_accept_kept(lvb_gpu_ctx *ctx, int ticket, int64_t n_accept, const int64_t *cands);
+
 /* ---- the exhaustive NNI neighbourhood of one evaluated tree, in one call: what the loop of
  * deterministic_hillclimb (Solve.c:100-111) computes with 2(n-3) x (mutate_deterministic,
  * TreeOperations.c:105-158, + getplen).  lengths[2*(u-n) + j] is the length getplen would return

@@ -18,7 +18,9 @@
  *   v >= 0        state row of LVB node v (leaf: the alignment row; internal: the row the
  *                 program's tree currently holds for v) — read from HBM.  Store programs that
  *                 read one tree and write another (FitchProgram::src_tree1) name a row of the
- *                 tree they write as (2n-3) + (v - n)
+ *                 tree they write as (2n-3) + (v - n).  This is what the COMPILER emits; before a
+ *                 batch goes to the device the device layer replaces every operand >= n by the
+ *                 absolute row of the pool (tree, bank of the node: see lvb_gpu.cu)
  *   OPER_PREV     the result of the previous instruction (still in registers)
  *   OPER_SLOT(s)  on-chip stack slot s (shared memory), written by an earlier push
  */
@@ -30,6 +32,8 @@
 /* FitchInstr::ctl bits */
 #define LVB_CTL_STORE 0x1u      /* write the result to the row of `node` in the program's tree */
 #define LVB_CTL_COUNT_ONLY 0x2u /* only the change count is needed (2nd root-step application) */
+#define LVB_CTL_BANK1 0x4u      /* (set by the device layer, not by the compiler) the result row is the node's row in
+                                 * the SECOND bank of the program's tree */
 #define LVB_CTL_PUSH_SHIFT 8    /* bits 8..15: 1 + stack slot to push the result to; 0 = no push */
 #define LVB_CTL_PUSH_MASK 0xff00u
 

@@ -131,7 +131,8 @@ __device__ __forceinline__ unsigned fitch_step(const uint4 &x, const uint4 &y, u
  * and publishes the length (its own launch, or the last column block of a single-level batch) */
 __device__ __forceinline__ void fitch_commit_finalize_body(const FitchInstr *instr, const FitchProgram *progs,
                                                            int32_t *cnts, int32_t *chg, long long *sum_chg, int n,
-                                                           int n_internal, long long *lengths, int pi)
+                                                           int n_internal, long long *lengths, int pi,
+                                                           int32_t *kept = nullptr, long long *newsum = nullptr)
 {
     __shared__ long long s_delta, s_root;
     const FitchProgram prog = progs[pi];
@@ -151,7 +152,10 @@ __device__ __forceinline__ void fitch_commit_finalize_body(const FitchInstr *ins
         if (node >= 0)
         {
             delta += (long long)c - tchg[node - n];
-            tchg[node - n] = c;
+            if (kept) /* peek: the tree keeps its counts, the candidate's are put aside */
+                kept[prog.instr_begin + i] = c;
+            else
+                tchg[node - n] = c;
         }
         else
             rootc += c; /* root step: never cached (TreeEvaluation.c:238-264) */
@@ -170,11 +174,13 @@ __device__ __forceinline__ void fitch_commit_finalize_body(const FitchInstr *ins
     if (threadIdx.x == 0)
     {
         const long long s = sum_chg[prog.tree] + s_delta;
-        sum_chg[prog.tree] = s;
+        if (kept)
+            newsum[pi] = s;
+        else
+            sum_chg[prog.tree] = s;
         lengths[pi] = s + s_root;
     }
 }
-
 
 /* one value of the peer-memory all-reduce (see P2PParams): this rank's partial sum `v` of entry k goes into
  * its row of every rank's slab, then the rows of all ranks that arrived in the own slab are added, in rank
@@ -388,9 +394,9 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
-    const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal; /* internal node v lives in row v + tree_off */
-    /* rows the operands are read from: the program's own tree unless it names another one */
-    const unsigned src_off = prog.src_tree1 > 0 ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
+    /* operand rows are absolute pool rows (the host resolved tree and bank); node v of the program's tree is stored
+     * to row v + tree_off (+ I for the tree's second bank, LVB_CTL_BANK1) */
+    const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.tree_stride;
     const FitchInstr *gi = instrs + prog.instr_begin;
     /* threads past the end of the row (last column block only) redo the last column; their
      * counts are masked and their stores suppressed */
@@ -435,16 +441,12 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
                     w |= D_APREV;
                     a = 0;
                 }
-                else if (a >= p.n) /* rows >= n + I: the program's own (store) tree, see compile_up_pass */
-                    a = a >= p.n + p.n_internal ? a - p.n_internal + (int)tree_off : a + (int)src_off;
                 if (b < 0)
                 {
                     w |= D_BSLOT;
                     b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
                 }
-                else if (b >= p.n)
-                    b = b >= p.n + p.n_internal ? b - p.n_internal + (int)tree_off : b + (int)src_off;
-                d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
+                d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off + ((in.ctl & LVB_CTL_BANK1) ? (unsigned)p.n_internal : 0u) : 0u, w);
             }
             s_instr[i] = d;
         }
@@ -531,7 +533,8 @@ __device__ __forceinline__ void fitch_exec_body(const ExecParams &p, const Fitch
             if (s_last)
             {
                 __threadfence();
-                fitch_commit_finalize_body(instrs, progs, p.cnts, p.chg_rw, p.sum_chg_rw, p.n, p.n_internal, p.out, prog_id);
+                fitch_commit_finalize_body(instrs, progs, p.cnts, p.chg_rw, p.sum_chg_rw, p.n, p.n_internal, p.out, prog_id,
+                                           p.peek ? p.kept : nullptr, p.newsum);
             }
         }
         return;
@@ -671,9 +674,7 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     const int col = cb * nthr + tid;
     const unsigned active = col < p.ncols ? 1u : 0u;
     const unsigned amask = active ? ~0u : 0u;
-    const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
-    /* store programs may read one tree and write another (up-pass), see fitch_exec_body */
-    const unsigned src_off = (STORE && prog.src_tree1 > 0) ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
+    const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.tree_stride; /* see fitch_exec_body */
     const FitchInstr *gi = instrs + prog.instr_begin;
     const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
     const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
@@ -718,16 +719,12 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
                     w |= D_APREV;
                     a = 0;
                 }
-                else if (a >= p.n)
-                    a = a >= p.n + p.n_internal ? a - p.n_internal + (int)tree_off : a + (int)src_off;
                 if (b < 0)
                 {
                     w |= D_BSLOT;
                     b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
                 }
-                else if (b >= p.n)
-                    b = b >= p.n + p.n_internal ? b - p.n_internal + (int)tree_off : b + (int)src_off;
-                d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
+                d = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off + ((in.ctl & LVB_CTL_BANK1) ? (unsigned)p.n_internal : 0u) : 0u, w);
             }
             s_instr[i] = d;
         }
@@ -818,7 +815,8 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
         if (s_last)
         {
             __threadfence();
-            fitch_commit_finalize_body(instrs, progs, p.cnts, p.chg_rw, p.sum_chg_rw, p.n, p.n_internal, p.out, prog_id);
+            fitch_commit_finalize_body(instrs, progs, p.cnts, p.chg_rw, p.sum_chg_rw, p.n, p.n_internal, p.out, prog_id,
+                                           p.peek ? p.kept : nullptr, p.newsum);
         }
         return;
     }
@@ -1205,8 +1203,7 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                 }
                 prog = p.prog[prog_id];
             }
-            const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.n_internal;
-            const unsigned src_off = prog.src_tree1 > 0 ? (unsigned)(prog.src_tree1 - 1) * (unsigned)p.n_internal : tree_off;
+            const unsigned tree_off = (unsigned)prog.tree * (unsigned)p.tree_stride;
             const FitchInstr *gi = p.instr + prog.instr_begin;
             const unsigned bytes = (unsigned)min(nt, p.ncols - cb * nt) * 16u;
             const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + (size_t)cb * nt);
@@ -1236,16 +1233,12 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                         w |= D_APREV;
                         a = 0;
                     }
-                    else if (a >= p.n)
-                        a = a >= p.n + p.n_internal ? a - p.n_internal + (int)tree_off : a + (int)src_off;
                     if (b < 0)
                     {
                         w |= D_BSLOT;
                         b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
                     }
-                    else if (b >= p.n)
-                        b = b >= p.n + p.n_internal ? b - p.n_internal + (int)tree_off : b + (int)src_off;
-                    dst[i] = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off : 0u, w);
+                    dst[i] = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off + ((in.ctl & LVB_CTL_BANK1) ? (unsigned)p.n_internal : 0u) : 0u, w);
                 }
                 /* a dependent piece is published only when the rows of the level below are there */
                 unsigned ok = 1u;
@@ -1500,16 +1493,86 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
 __global__ void __launch_bounds__(1024) fitch_commit_finalize_kernel(const FitchInstr *instr, const FitchProgram *progs,
                                                                     int32_t *cnts, int32_t *chg,
                                                                     long long *sum_chg, int n, int n_internal,
-                                                                    long long *lengths)
+                                                                    long long *lengths, int32_t *kept, long long *newsum)
 {
-    fitch_commit_finalize_body(instr, progs, cnts, chg, sum_chg, n, n_internal, lengths, blockIdx.x);
+    fitch_commit_finalize_body(instr, progs, cnts, chg, sum_chg, n, n_internal, lengths, blockIdx.x, kept, newsum);
+}
+
+/* a kept candidate becomes its tree: its counts and its sum replace the tree's */
+__global__ void __launch_bounds__(256) fitch_apply_kept_kernel(const FitchInstr *instr, const FitchProgram *cand,
+                                                               const int32_t *which, const int32_t *kept,
+                                                               const long long *newsum, int32_t *chg, long long *sum_chg,
+                                                               int n, int n_internal)
+{
+    const int k = which[blockIdx.x];
+    const FitchProgram prog = cand[k];
+    int32_t *tchg = chg + (int64_t)prog.tree * n_internal;
+    for (int i = threadIdx.x; i < prog.n_instr; i += blockDim.x)
+    {
+        const int node = instr[prog.instr_begin + i].node;
+        if (node >= 0)
+            tchg[node - n] = kept[prog.instr_begin + i];
+    }
+    if (threadIdx.x == 0)
+        sum_chg[prog.tree] = newsum[k];
 }
 template <int NP, int NI>
 __global__ void __launch_bounds__(1024)
     fitch_commit_finalize_kernel_inl(const __grid_constant__ InlineBatch<NP, NI> b, int32_t *cnts, int32_t *chg,
-                                     long long *sum_chg, int n, int n_internal, long long *lengths)
+                                     long long *sum_chg, int n, int n_internal, long long *lengths, int32_t *kept,
+                                     long long *newsum)
 {
-    fitch_commit_finalize_body(b.instr, b.cand, cnts, chg, sum_chg, n, n_internal, lengths, blockIdx.x);
+    fitch_commit_finalize_body(b.instr, b.cand, cnts, chg, sum_chg, n, n_internal, lengths, blockIdx.x, kept, newsum);
+}
+
+/* the same with the batch and the list of candidates inside the kernel parameters */
+struct WhichList
+{
+    int32_t k[LVB_INL_LARGE_P];
+};
+template <int NP, int NI>
+__global__ void __launch_bounds__(128)
+    fitch_apply_kept_kernel_inl(const __grid_constant__ InlineBatch<NP, NI> b, const __grid_constant__ WhichList w,
+                                const int32_t *kept, const long long *newsum, int32_t *chg, long long *sum_chg, int n,
+                                int n_internal)
+{
+    const int k = w.k[blockIdx.x];
+    const FitchProgram prog = b.cand[k];
+    int32_t *tchg = chg + (int64_t)prog.tree * n_internal;
+    for (int i = threadIdx.x; i < prog.n_instr; i += blockDim.x)
+    {
+        const int node = b.instr[prog.instr_begin + i].node;
+        if (node >= 0)
+            tchg[node - n] = kept[prog.instr_begin + i];
+    }
+    if (threadIdx.x == 0)
+        sum_chg[prog.tree] = newsum[k];
+}
+
+template <int NP, int NI>
+static cudaError_t launch_apply_kept_inline_t(const FitchProgram *cand, int n_cand, const FitchInstr *instr, size_t n_instr,
+                                              const int64_t *which, int n_which, const int32_t *kept, const long long *newsum,
+                                              int32_t *chg, long long *sum_chg, int n, int n_internal, cudaStream_t stream)
+{
+    static thread_local InlineBatch<NP, NI> tb;
+    WhichList w;
+    memcpy(tb.cand, cand, (size_t)n_cand * sizeof(FitchProgram));
+    memcpy(tb.instr, instr, n_instr * sizeof(FitchInstr));
+    for (int i = 0; i < n_which; i++)
+        w.k[i] = (int32_t)which[i];
+    fitch_apply_kept_kernel_inl<NP, NI><<<n_which, 128, 0, stream>>>(tb, w, kept, newsum, chg, sum_chg, n, n_internal);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_apply_kept_inline(const FitchProgram *cand, int n_cand, const FitchInstr *instr, size_t n_instr,
+                                     const int64_t *which, int n_which, const int32_t *kept, const long long *newsum,
+                                     int32_t *chg, long long *sum_chg, int n, int n_internal, cudaStream_t stream)
+{
+    if (n_cand <= LVB_INL_SMALL_P && n_instr <= (size_t)LVB_INL_SMALL_I)
+        return launch_apply_kept_inline_t<LVB_INL_SMALL_P, LVB_INL_SMALL_I>(cand, n_cand, instr, n_instr, which, n_which, kept,
+                                                                            newsum, chg, sum_chg, n, n_internal, stream);
+    return launch_apply_kept_inline_t<LVB_INL_LARGE_P, LVB_INL_LARGE_I>(cand, n_cand, instr, n_instr, which, n_which, kept, newsum,
+                                                                        chg, sum_chg, n, n_internal, stream);
 }
 
 /* ---- launches with the batch inside the kernel parameters ---- */
@@ -1555,7 +1618,8 @@ static cudaError_t launch_inline_t(const ExecParams &p, bool per_node, int block
             while (threads < max_instr && threads < 1024)
                 threads *= 2;
             fitch_commit_finalize_kernel_inl<NP, NI><<<n_cand, threads, 0, stream>>>(tb, p.cnts, chg, sum_chg, p.n,
-                                                                                    p.n_internal, lengths);
+                                                                                    p.n_internal, lengths,
+                                                                                    p.peek ? p.kept : nullptr, p.newsum);
         }
     }
     else if (deep)
@@ -1589,12 +1653,21 @@ cudaError_t launch_fitch_inline(const ExecParams &p, bool per_node, int block, c
 
 cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
-                                   int max_instr, cudaStream_t stream)
+                                   int max_instr, cudaStream_t stream, int32_t *kept, long long *newsum)
 {
     /* one thread per instruction of the longest program where possible: the loads are dependent
      * (instruction -> count, cached count), so width, not work, sets the duration */
     const int threads = max_instr >= 1024 ? 1024 : max_instr <= 128 ? 128 : (max_instr + 31) / 32 * 32;
-    fitch_commit_finalize_kernel<<<n_prog, threads, 0, stream>>>(instr, prog, cnts, chg, sum_chg, n, n_internal, lengths);
+    fitch_commit_finalize_kernel<<<n_prog, threads, 0, stream>>>(instr, prog, cnts, chg, sum_chg, n, n_internal, lengths,
+                                                                 kept, newsum);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_apply_kept(const FitchInstr *instr, const FitchProgram *cand, const int32_t *which, int n_which,
+                              const int32_t *kept, const long long *newsum, int32_t *chg, long long *sum_chg, int n,
+                              int n_internal, cudaStream_t stream)
+{
+    fitch_apply_kept_kernel<<<n_which, 128, 0, stream>>>(instr, cand, which, kept, newsum, chg, sum_chg, n, n_internal);
     return cudaGetLastError();
 }
 

@@ -45,6 +45,14 @@ struct ExecParams
     int32_t ncols;               /* columns to process (= stride_u4) */
     int32_t n;                   /* leaves */
     int32_t n_internal;          /* I = n - 3 */
+    int32_t tree_stride;         /* pool rows per device tree: 2 I (two banks of I rows; a node's current row is in one
+                                  * of them, the other takes the rows of a KEPT candidate, see peek) */
+    int32_t peek;                /* store-mode launch whose finalize step only LOOKS: out[k] = the length the candidate
+                                  * would have, kept[] <- its per-node counts, newsum[k] <- its sum of counts; chg and
+                                  * sum_chg stay as they are (lvb_gpu_score_keep_*: candidates scored with their rows
+                                  * stored in the spare bank; fitch_apply_kept_kernel makes one of them the tree) */
+    int32_t *kept;               /* [n_instr of batch] */
+    long long *newsum;           /* [n_cand] */
     int32_t n_prog;
     int32_t n_colblocks;
     int32_t n_slots;             /* stack slots of the deepest program in the batch */
@@ -114,11 +122,24 @@ cudaError_t launch_fitch_inline(const ExecParams &p, bool per_node, int block, c
                                 const FitchInstr *instr, size_t n_instr, int32_t *chg, long long *sum_chg,
                                 long long *lengths, int max_instr);
 
+/* A kept candidate becomes its tree: chg[tree][node] <- kept count of every node instruction, sum_chg[tree] <-
+ * newsum[k]; which[] lists the candidates (indices into cand), one CTA each */
+cudaError_t launch_apply_kept(const FitchInstr *instr, const FitchProgram *cand, const int32_t *which, int n_which,
+                              const int32_t *kept, const long long *newsum, int32_t *chg, long long *sum_chg, int n,
+                              int n_internal, cudaStream_t stream);
+
+/* the same for a batch that went out inside kernel parameters (inline_batch_fits): cand / instr are HOST pointers, the
+ * candidate list travels in the parameters too — one launch, nothing staged */
+cudaError_t launch_apply_kept_inline(const FitchProgram *cand, int n_cand, const FitchInstr *instr, size_t n_instr,
+                                     const int64_t *which, int n_which, const int32_t *kept, const long long *newsum,
+                                     int32_t *chg, long long *sum_chg, int n, int n_internal, cudaStream_t stream);
+
 /* After a store-mode batch: chg[tree][node] <- new count, sum_chg[tree] += delta,
  * lengths[p] <- sum_chg[tree] + root step counts.  Trees of the batch must be distinct. */
 cudaError_t launch_commit_finalize(const FitchInstr *instr, const FitchProgram *prog, int n_prog, int32_t *cnts,
                                    int32_t *chg, long long *sum_chg, int n, int n_internal, long long *lengths,
-                                   int max_instr, cudaStream_t stream);
+                                   int max_instr, cudaStream_t stream, int32_t *kept = nullptr,
+                                   long long *newsum = nullptr);
 
 /* Exhaustive NNI neighbourhood (Solve.c:64-142, TreeOperations.c:105-158): branch e joins the
  * pool rows rows[e] = {A, B, C, D}; delta[2e] += length(((A,C),(B,D))) - length(((A,B),(C,D))),

@@ -116,6 +116,16 @@ struct Staging
     cudaEvent_t done = nullptr; /* recorded after the last kernel that reads this slot */
     bool pending = false;
     int64_t unclaimed = 0;      /* > 0: a submitted batch whose lengths lvb_gpu_batch_wait has not fetched yet */
+    /* a batch of lvb_gpu_score_keep_*: what lvb_gpu_accept_kept needs to make a kept candidate its tree */
+    bool keep_batch = false, staged = false;
+    size_t k_prog = 0, k_instr = 0, k_cand = 0;
+    std::vector<uint8_t> kept_flag; /* per candidate: 1 = kept, 2 = accepted */
+    int32_t *d_kept = nullptr;      /* [cap_kept] per-instruction counts of the batch, put aside by the peek finalize */
+    size_t cap_kept = 0;
+    long long *d_newsum = nullptr;  /* [cap_newsum] per candidate: the sum of counts its tree would have */
+    size_t cap_newsum = 0;
+    int32_t *h_which = nullptr, *d_which = nullptr; /* pinned, mapped: the candidates of one accept call */
+    size_t cap_which = 0;
 };
 
 struct lvb_gpu_ctx
@@ -132,6 +142,11 @@ struct lvb_gpu_ctx
     int32_t *chg = nullptr;
     long long *sum_chg = nullptr;
     std::vector<uint8_t> tree_used, tree_ready;
+    /* Every device tree owns TWO banks of I rows; bank[t * I + (v - n)] says which one holds the row of node v.
+     * A commit rewrites rows in place.  A KEPT candidate (lvb_gpu_score_keep_*) is scored with its rows stored
+     * into the OTHER bank of its dirty nodes; accepting it flips those bits — the tree changes without a second
+     * pass over the rows.  Programs name nodes; the operands become absolute pool rows when a batch is laid out. */
+    std::vector<uint8_t> bank;
     std::vector<ScheduleCompiler *> sc; /* one per host thread that compiles */
 
     /* batch staging */
@@ -227,6 +242,12 @@ static inline double wall_now()
     struct timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
     return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
+
+/* the pool row that holds node v (>= n) of device tree t */
+static inline int64_t pool_row(const lvb_gpu_ctx *c, int64_t t, int64_t v)
+{
+    return c->n + t * 2 * c->I + (int64_t)c->bank[(size_t)(t * c->I + (v - c->n))] * c->I + (v - c->n);
 }
 
 static size_t grow(size_t have, size_t need, size_t start)
@@ -430,6 +451,10 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     p.ncols = (int32_t)c->stride_u4;
     p.n = (int32_t)c->n;
     p.n_internal = (int32_t)c->I;
+    p.tree_stride = (int32_t)(2 * c->I);
+    p.peek = st.keep_batch ? 1 : 0;
+    p.kept = st.d_kept;
+    p.newsum = st.d_newsum;
     const bool stream = store && c->last_dep && c->stream_nt > 0;
     const int block = stream ? c->stream_nt : pick_block(c);
     p.stream_nt = stream ? c->stream_nt : 0;
@@ -553,7 +578,7 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     if (store && !c->last_inline && !fused)
     {
         CU(launch_commit_finalize(d_instr, d_cand, (int)K, c->d_cnts, c->chg, c->sum_chg, (int)c->n, (int)c->I, out,
-                                  c->last_max_instr, c->stream));
+                                  c->last_max_instr, c->stream, st.keep_batch ? st.d_kept : nullptr, st.d_newsum));
         c->launches++;
     }
     if (want_reduce && !fuse_p2p)
@@ -587,8 +612,14 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
 
 /* compile + launch one batch; store: commit semantics, else score semantics */
 static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_topology *topos, bool store,
-                     int64_t *lengths, int *ticket = nullptr, const lvb_gpu_program_view *pre = nullptr)
+                     int64_t *lengths, int *ticket = nullptr, const lvb_gpu_program_view *pre = nullptr,
+                     const uint8_t *keep = nullptr)
 {
+    /* keep: a SCORE batch (nothing about the trees changes) that runs as a store launch: candidates with keep[k] != 0
+     * leave their rows in the spare bank of their tree and their counts aside (peek finalize) */
+    const bool keeping = keep != nullptr;
+    if (keeping)
+        store = true;
     if (!c->pool)
         return fail("no alignment on the device: call lvb_gpu_matrix_upload first");
     if (K <= 0)
@@ -599,24 +630,26 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     /* Large store programs are cut into independent subtrees so that enough warps are resident:
      * a program owns ceil(cols/32) warps per piece. */
     const int64_t warps_per_piece = (c->stride_u4 + 31) / 32;
-    const int64_t want_pieces = store ? std::max<int64_t>(1, c->target_warps / (warps_per_piece * K)) : 1;
+    const int64_t want_pieces = store && !keeping ? std::max<int64_t>(1, c->target_warps / (warps_per_piece * K)) : 1;
     for (int64_t k = 0; k < K; k++)
     {
         const int t = trees[k];
         if (t < 0 || t >= c->max_trees || !c->tree_used[t])
             return fail("candidate %lld: tree %d does not exist", (long long)k, t);
-        if (!store && !c->tree_ready[t])
+        if ((!store || keeping) && !c->tree_ready[t])
             return fail("candidate %lld: tree %d has never been evaluated (commit it first)", (long long)k, t);
-        if (store && !c->tree_ready[t] && topos[k].n_dirty >= 0)
+        if (store && !keeping && !c->tree_ready[t] && topos[k].n_dirty >= 0)
             return fail("tree %d: first commit must recompute every internal node (n_dirty < 0)", t);
     }
     if (store)
-    { /* in-place commits of one tree must not share a launch */
+    { /* in-place commits of one tree must not share a launch; nor two kept candidates of one tree the spare bank */
         std::vector<uint8_t> seen(c->max_trees, 0);
         for (int64_t k = 0; k < K; k++)
         {
+            if (keeping && !keep[k])
+                continue;
             if (seen[trees[k]])
-                return fail("commit batch names tree %d twice", trees[k]);
+                return fail(keeping ? "two kept candidates name tree %d" : "commit batch names tree %d twice", trees[k]);
             seen[trees[k]] = 1;
         }
     }
@@ -670,7 +703,7 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
         c->c_pieces[k].clear();
         c->c_err[k].clear();
         int slots = 0;
-        if (!sc->compile(topos[k], store, c->c_instr[k], slots, c->c_err[k], piece_size, &c->c_pieces[k]))
+        if (!sc->compile(topos[k], store && !keeping, c->c_instr[k], slots, c->c_err[k], piece_size, &c->c_pieces[k]))
             bad = true;
         c->c_slots[k] = slots;
     };
@@ -719,6 +752,31 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     {
         const auto &ins = c->c_instr[k];
         memcpy(h_instr + off, ins.data(), ins.size() * sizeof(FitchInstr));
+        { /* nodes -> pool rows: operands read the bank that holds the node's row; a commit stores in place, a kept
+           * candidate into the other bank (and every node of it is stored) */
+            const int64_t t = trees[k];
+            const uint8_t *bk = c->bank.data() + (size_t)(t * c->I);
+            const int32_t n32 = (int32_t)c->n, I32 = (int32_t)c->I;
+            const int32_t base = (int32_t)(c->n + t * 2 * c->I);
+            const bool kp = keeping && keep[k];
+            FitchInstr *ip = h_instr + off;
+            for (size_t i = 0; i < ins.size(); i++)
+            {
+                FitchInstr &in = ip[i];
+                if (in.a >= n32)
+                    in.a = base + (int32_t)bk[in.a - n32] * I32 + (in.a - n32);
+                if (in.b >= n32)
+                    in.b = base + (int32_t)bk[in.b - n32] * I32 + (in.b - n32);
+                if (in.node >= 0)
+                {
+                    const uint8_t b = bk[in.node - n32];
+                    if (kp)
+                        in.ctl |= LVB_CTL_STORE | (b ? 0u : LVB_CTL_BANK1);
+                    else if (b)
+                        in.ctl |= LVB_CTL_BANK1;
+                }
+            }
+        }
         for (const auto &pc : c->c_pieces[k])
         {
             c->prog.push_back(FitchProgram{(int32_t)(off + pc.instr_begin), pc.n_instr, trees[k], pc.level, -1, 0, 0, (int32_t)k});
@@ -801,9 +859,34 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
     c->last_inline = c->inline_ok && !multilevel && c->levels.size() == 1 && inline_batch_fits((int)n_prog, (int)K, n_instr);
     if (!c->last_inline)
         CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
-    if (store)
+    if (store && !keeping)
         for (int64_t k = 0; k < K; k++)
             c->tree_ready[trees[k]] = 1;
+    st.keep_batch = keeping;
+    st.staged = !c->last_inline;
+    if (keeping)
+    {
+        st.k_prog = n_prog;
+        st.k_instr = n_instr;
+        st.k_cand = (size_t)K;
+        st.kept_flag.assign(keep, keep + K);
+        if (n_instr > st.cap_kept)
+        {
+            const size_t cap = grow(st.cap_kept, n_instr, 4096);
+            cudaFree(st.d_kept);
+            st.d_kept = nullptr;
+            CU(cudaMalloc(&st.d_kept, cap * sizeof(int32_t)));
+            st.cap_kept = cap;
+        }
+        if ((size_t)K > st.cap_newsum)
+        {
+            const size_t cap = grow(st.cap_newsum, (size_t)K, 256);
+            cudaFree(st.d_newsum);
+            st.d_newsum = nullptr;
+            CU(cudaMalloc(&st.d_newsum, cap * sizeof(long long)));
+            st.cap_newsum = cap;
+        }
+    }
     c->last_K = K;
     c->last_store = store;
     c->last_slots = n_slots;
@@ -867,7 +950,7 @@ static int alloc_matrix(lvb_gpu_ctx *c, int64_t n, int64_t nwords, int64_t word_
     /* two words per 16-byte column; rows padded to 128 bytes so that every warp access is line-aligned */
     const int64_t cols = (word_count + 1) / 2;
     c->stride_u4 = (cols + 7) / 8 * 8;
-    const int64_t rows = n + max_trees * c->I;
+    const int64_t rows = n + max_trees * 2 * c->I;
     if (rows > (int64_t)INT32_MAX)
         return fail("row pool too large");
     CU(cudaMalloc(&c->pool, (size_t)rows * c->stride_u4 * sizeof(uint4)));
@@ -878,6 +961,7 @@ static int alloc_matrix(lvb_gpu_ctx *c, int64_t n, int64_t nwords, int64_t word_
     CU(cudaMemsetAsync(c->sum_chg, 0, (size_t)max_trees * sizeof(long long), c->stream));
     c->tree_used.assign(max_trees, 0);
     c->tree_ready.assign(max_trees, 0);
+    c->bank.assign((size_t)max_trees * (size_t)c->I, 0);
     int nsc = 1;
 #ifdef _OPENMP
     nsc = std::max(1, std::min(16, omp_get_max_threads()));
@@ -1050,6 +1134,10 @@ extern "C"
             cudaFreeHost(st.h);
             cudaFree(st.d);
             cudaFreeHost(st.h_len);
+            cudaFree(st.d_kept);
+            cudaFree(st.d_newsum);
+            if (st.h_which)
+                cudaFreeHost(st.h_which);
             if (st.done)
                 cudaEventDestroy(st.done);
         }
@@ -1225,6 +1313,7 @@ extern "C"
             {
                 c->tree_used[t] = 1;
                 c->tree_ready[t] = 0;
+                std::fill(c->bank.begin() + t * c->I, c->bank.begin() + (t + 1) * c->I, 0);
                 CU(cudaSetDevice(c->device));
                 CU(cudaMemsetAsync(c->chg + t * c->I, 0, (size_t)c->I * sizeof(int32_t), c->stream));
                 CU(cudaMemsetAsync(c->sum_chg + t, 0, sizeof(long long), c->stream));
@@ -1252,9 +1341,13 @@ extern "C"
         if (dst == src)
             return 0;
         CU(cudaSetDevice(c->device));
-        const size_t bytes = (size_t)c->I * c->stride_u4 * sizeof(uint4);
-        CU(cudaMemcpyAsync(c->pool + (c->n + dst * c->I) * c->stride_u4, c->pool + (c->n + src * c->I) * c->stride_u4,
-                           bytes, cudaMemcpyDeviceToDevice, c->stream));
+        /* both banks as they are, and which bank holds what */
+        const size_t bytes = (size_t)2 * c->I * c->stride_u4 * sizeof(uint4);
+        CU(cudaMemcpyAsync(c->pool + (c->n + (int64_t)dst * 2 * c->I) * c->stride_u4,
+                           c->pool + (c->n + (int64_t)src * 2 * c->I) * c->stride_u4, bytes, cudaMemcpyDeviceToDevice,
+                           c->stream));
+        std::copy(c->bank.begin() + (int64_t)src * c->I, c->bank.begin() + (int64_t)(src + 1) * c->I,
+                  c->bank.begin() + (int64_t)dst * c->I);
         CU(cudaMemcpyAsync(c->chg + dst * c->I, c->chg + src * c->I, (size_t)c->I * sizeof(int32_t),
                            cudaMemcpyDeviceToDevice, c->stream));
         CU(cudaMemcpyAsync(c->sum_chg + dst, c->sum_chg + src, sizeof(long long), cudaMemcpyDeviceToDevice,
@@ -1406,15 +1499,30 @@ extern "C"
         h_prog[n_pcs] = FitchProgram{0, (int32_t)n_instr, scratch_tree, 1, -1, 0, tree + 1, 0};
         if (n_instr)
             memcpy(h_instr, instr.data(), n_instr * sizeof(FitchInstr));
+        /* the scratch tree takes the up sets in its first bank; operands: rows of `tree` where they are now, and
+         * (numbered from B up by the compiler) rows of the scratch tree */
+        std::fill(c->bank.begin() + (int64_t)scratch_tree * c->I, c->bank.begin() + (int64_t)(scratch_tree + 1) * c->I, 0);
+        auto low_row = [&](int32_t v) { return (uint32_t)(v < c->n ? v : pool_row(c, tree, v)); };
+        auto up_row = [&](int32_t v) { return (uint32_t)(c->n + (int64_t)scratch_tree * 2 * c->I + (v - c->n)); };
+        for (size_t i = 0; i < n_instr; i++)
+        {
+            FitchInstr &in = h_instr[i];
+            int32_t *ops[2] = {&in.a, &in.b};
+            for (int32_t *op : ops)
+                if (*op >= c->B)
+                    *op = (int32_t)up_row((int32_t)(*op - c->B + c->n));
+                else if (*op >= c->n)
+                    *op = (int32_t)low_row(*op);
+        }
+        st.keep_batch = false;
         const int64_t root = topo->root;
-        auto low_row = [&](int32_t v) { return (uint32_t)(v < c->n ? v : v + (int64_t)tree * c->I); };
         for (int64_t e = 0; e < E; e++)
         {
             const int32_t u = (int32_t)(c->n + e), v = parent[u];
             const int32_t sis = left[v] == u ? right[v] : left[v];
-            const uint32_t up = v == root ? (uint32_t)root : (uint32_t)(v + (int64_t)scratch_tree * c->I);
+            const uint32_t up = v == root ? (uint32_t)root : up_row(v);
             h_rows[e] = make_uint4(low_row(left[u]), low_row(right[u]), low_row(sis), up);
-            h_rows2[e] = make_uint2(low_row(u), (uint32_t)(u + (int64_t)scratch_tree * c->I));
+            h_rows2[e] = make_uint2(low_row(u), up_row(u));
         }
         CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
         c->tree_ready[scratch_tree] = 0; /* its rows now hold up sets, not an evaluated tree */
@@ -1431,6 +1539,10 @@ extern "C"
             p.ncols = (int32_t)c->stride_u4;
             p.n = (int32_t)c->n;
             p.n_internal = (int32_t)c->I;
+            p.tree_stride = (int32_t)(2 * c->I);
+            p.peek = 0;
+            p.kept = nullptr;
+            p.newsum = nullptr;
             p.n_colblocks = n_cb;
             p.n_slots = n_slots;
             p.score_v1 = 0;
@@ -1526,7 +1638,7 @@ extern "C"
         {
             if (tree < 0 || tree >= c->max_trees || !c->tree_used[tree])
                 return fail("lvb_gpu_download_row: tree %d does not exist", tree);
-            row = node + (int64_t)tree * c->I;
+            row = pool_row(c, tree, node);
         }
         CU(cudaSetDevice(c->device));
         CU(cudaMemcpyAsync(out, c->pool + row * c->stride_u4, (size_t)c->word_count * 8, cudaMemcpyDeviceToHost,
@@ -1814,6 +1926,114 @@ extern "C"
         if (n_cand <= 0)
             return fail("lvb_gpu_score_batch_submit_pre: empty batch");
         return run_batch(c, n_cand, trees, topos, false, nullptr, ticket, pre);
+    }
+
+    int lvb_gpu_score_keep_submit_pre(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                      const lvb_gpu_program_view *pre, const uint8_t *keep, int *ticket)
+    {
+        if (!c || !trees || !topos || !keep || !ticket)
+            return fail("lvb_gpu_score_keep_submit_pre: null argument");
+        if (n_cand <= 0)
+            return fail("lvb_gpu_score_keep_submit_pre: empty batch");
+        return run_batch(c, n_cand, trees, topos, false, nullptr, ticket, pre, keep);
+    }
+
+    int lvb_gpu_score_keep(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                           const uint8_t *keep, int64_t *lengths, int *ticket)
+    {
+        if (!c || !trees || !topos || !keep || !lengths || !ticket)
+            return fail("lvb_gpu_score_keep: null argument");
+        if (n_cand <= 0)
+            return fail("lvb_gpu_score_keep: empty batch");
+        if (run_batch(c, n_cand, trees, topos, false, nullptr, ticket, nullptr, keep))
+            return 1;
+        return lvb_gpu_batch_wait(c, *ticket, lengths);
+    }
+
+    int lvb_gpu_accept_kept(lvb_gpu_ctx *c, int ticket, int64_t n_accept, const int64_t *cands)
+    {
+        if (!c || ticket < 0 || ticket >= lvb_gpu_ctx::kRing || (n_accept > 0 && !cands))
+            return fail("lvb_gpu_accept_kept: bad argument");
+        if (n_accept <= 0)
+            return 0;
+        Staging &st = c->ring[ticket];
+        if (!st.keep_batch)
+            return fail("lvb_gpu_accept_kept: ticket %d does not name a batch of lvb_gpu_score_keep_* that is still held "
+                        "(at most %d device calls may lie between the submit and the accept)", ticket, lvb_gpu_ctx::kRing - 1);
+        if (st.unclaimed)
+            return fail("lvb_gpu_accept_kept: fetch the lengths of the batch first (lvb_gpu_batch_wait)");
+        const FitchProgram *h_cand = reinterpret_cast<const FitchProgram *>(st.h) + st.k_prog;
+        const FitchInstr *h_instr = reinterpret_cast<const FitchInstr *>(h_cand + st.k_cand);
+        std::vector<uint8_t> seen(c->max_trees, 0);
+        for (int64_t i = 0; i < n_accept; i++)
+        {
+            const int64_t k = cands[i];
+            if (k < 0 || (size_t)k >= st.k_cand || st.kept_flag[(size_t)k] != 1)
+                return fail("lvb_gpu_accept_kept: candidate %lld of the batch was not kept (or was accepted already)", (long long)k);
+            if (seen[h_cand[k].tree])
+                return fail("lvb_gpu_accept_kept: two candidates of tree %d", h_cand[k].tree);
+            seen[h_cand[k].tree] = 1;
+        }
+        CU(cudaSetDevice(c->device));
+        /* a small batch went out inside kernel parameters: so does its accept — one launch, nothing staged */
+        const bool inl = !st.staged && inline_batch_fits((int)st.k_prog, (int)st.k_cand, st.k_instr) && st.k_prog == st.k_cand;
+        if (!inl)
+        {
+            if ((size_t)n_accept > st.cap_which)
+            {
+                const size_t cap = grow(st.cap_which, (size_t)n_accept, 64);
+                if (st.h_which)
+                    CU(cudaFreeHost(st.h_which));
+                st.h_which = nullptr;
+                CU(cudaHostAlloc(&st.h_which, cap * sizeof(int32_t), cudaHostAllocMapped));
+                CU(cudaHostGetDevicePointer(&st.d_which, st.h_which, 0));
+                st.cap_which = cap;
+            }
+            else if (st.pending)
+            { /* an earlier accept of this batch may still read the list */
+                CU(cudaEventSynchronize(st.done));
+                st.pending = false;
+            }
+        }
+        for (int64_t i = 0; i < n_accept; i++)
+        {
+            const int64_t k = cands[i];
+            if (!inl)
+                st.h_which[i] = (int32_t)k;
+            st.kept_flag[(size_t)k] = 2;
+            /* the rows of the candidate's nodes are in the other bank: from now on they are the tree's */
+            uint8_t *bk = c->bank.data() + (size_t)((int64_t)h_cand[k].tree * c->I);
+            for (int32_t j = 0; j < h_cand[k].n_instr; j++)
+            {
+                const int32_t node = h_instr[h_cand[k].instr_begin + j].node;
+                if (node >= 0)
+                    bk[node - c->n] ^= 1;
+            }
+        }
+        if (inl)
+        {
+            CU(launch_apply_kept_inline(h_cand, (int)st.k_cand, h_instr, st.k_instr, cands, (int)n_accept, st.d_kept, st.d_newsum,
+                                        c->chg, c->sum_chg, (int)c->n, (int)c->I, c->stream));
+            c->launches++;
+            c->last_K = 0;
+            return 0;
+        }
+        if (!st.staged)
+        { /* the batch went out inside kernel parameters: the apply kernel reads it from device memory */
+            const size_t bytes = (st.k_prog + st.k_cand) * sizeof(FitchProgram) + st.k_instr * sizeof(FitchInstr);
+            CU(cudaMemcpyAsync(st.d, st.h, bytes, cudaMemcpyHostToDevice, c->stream));
+            st.staged = true;
+        }
+        const FitchProgram *d_cand = reinterpret_cast<const FitchProgram *>(st.d) + st.k_prog;
+        const FitchInstr *d_instr = reinterpret_cast<const FitchInstr *>(d_cand + st.k_cand);
+        CU(launch_apply_kept(d_instr, d_cand, st.d_which, (int)n_accept, st.d_kept, st.d_newsum, c->chg, c->sum_chg, (int)c->n,
+                             (int)c->I, c->stream));
+        c->launches++;
+        /* the slot's host and device staging are read by what was just enqueued */
+        CU(cudaEventRecord(st.done, c->stream));
+        st.pending = true;
+        c->last_K = 0; /* the resident batch no longer describes the trees */
+        return 0;
     }
 
     int lvb_gpu_compile_up_pass(int64_t n, const lvb_gpu_topology *topo, int piece_size, int32_t *instr, int64_t cap,

@@ -67,6 +67,8 @@ def load_library() -> C.CDLL:
     lib.lvb_gpu_score_batch.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_score_batch_submit.argtypes = [vp, i64, i32p, C.POINTER(_Topo), i32p]
     lib.lvb_gpu_batch_wait.argtypes = [vp, C.c_int, C.POINTER(i64)]
+    lib.lvb_gpu_score_keep.argtypes = [vp, i64, i32p, C.POINTER(_Topo), C.POINTER(C.c_uint8), C.POINTER(i64), i32p]
+    lib.lvb_gpu_accept_kept.argtypes = [vp, C.c_int, i64, C.POINTER(i64)]
     lib.lvb_gpu_commit_batch_submit.argtypes = [vp, i64, i32p, C.POINTER(_Topo), i32p]
     lib.lvb_gpu_nni_neighbourhood.argtypes = [vp, C.c_int, C.c_int, C.POINTER(_Topo), C.POINTER(i64)]
     lib.lvb_gpu_download_row.argtypes = [vp, C.c_int, i64, vp]
@@ -284,6 +286,26 @@ class Engine:
         ticket = C.c_int(-1)
         _check(self.lib.lvb_gpu_commit_batch_submit(self.ctx, k, tarr, sarr, C.byref(ticket)))
         return ticket.value, k
+
+    def score_keep(self, trees: Sequence[int], topos: Sequence[Topology], keep: Sequence[int]):
+        """lvb_gpu_score_keep: lengths of the candidates; those with keep[k] != 0 leave their rows in the spare
+        bank of their tree.  Returns (lengths, ticket) — ticket for accept_kept"""
+        k = len(topos)
+        tarr = (C.c_int * k)(*[int(t) for t in trees])
+        sarr = (_Topo * k)()
+        for i, tp in enumerate(topos):
+            tp.fill(sarr[i])
+        karr = (C.c_uint8 * k)(*[1 if x else 0 for x in keep])
+        out = np.zeros(k, dtype=np.int64)
+        ticket = C.c_int(-1)
+        _check(self.lib.lvb_gpu_score_keep(self.ctx, k, tarr, sarr, karr, out.ctypes.data_as(C.POINTER(C.c_int64)),
+                                           C.byref(ticket)))
+        return out, ticket.value
+
+    def accept_kept(self, ticket: int, cands: Sequence[int]) -> None:
+        """lvb_gpu_accept_kept: the kept candidates `cands` of the batch become their trees"""
+        arr = (C.c_int64 * len(cands))(*[int(x) for x in cands])
+        _check(self.lib.lvb_gpu_accept_kept(self.ctx, int(ticket), len(cands), arr))
 
     def batch_wait(self, ticket) -> np.ndarray:
         out = np.zeros(ticket[1], dtype=np.int64)

@@ -155,6 +155,13 @@ struct Chain
     int n_spec = 0;
     SAState spec_end;
     CommitReq commit;
+    /* score AND keep (lvb_gpu_score_keep_*): the first proposal of the round is scored with its rows stored in the
+     * spare rows of the device tree, and if it is the one accepted the device tree switches over to them
+     * (lvb_gpu_accept_kept) instead of recomputing them in a commit.  Used while a proposal is more likely
+     * accepted than not — the hot phase, where nearly every round ends with its first proposal accepted. */
+    bool keep_ok = true;      /* LVB_GPU_KEEP=0 switches it off */
+    bool keep_first = false;  /* this round's first proposal is kept */
+    bool accept_kept = false; /* ... and was accepted: the driver tells the device */
 
     SearchResult res;
 
@@ -458,6 +465,7 @@ struct Chain
     void advance()
     {
         n_spec = 0;
+        keep_first = accept_kept = false;
         ccommit.valid = false;
         if (S.phase == PH_DONE)
             return;
@@ -573,6 +581,7 @@ struct Chain
         }
         spec_end = W;
         res.getplen_calls += n_spec;
+        keep_first = keep_ok && n_spec > 0 && (ema_taken + 0.25) / (ema_used + 0.5) >= 0.5;
         compile_round();
     }
 
@@ -636,7 +645,12 @@ struct Chain
                     S.phase = PH_AN_BEGIN;
             }
             if (go_on)
-                request_rows(cand[(size_t)k].dirty.begin(), cand[(size_t)k].dirty.end());
+            {
+                if (k == 0 && keep_first)
+                    accept_kept = true; /* its rows are on the device already */
+                else
+                    request_rows(cand[(size_t)k].dirty.begin(), cand[(size_t)k].dirty.end());
+            }
             break;
         }
         if (taken < 0)
@@ -690,8 +704,10 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
         std::vector<int> trees, owner;
         std::vector<lvb_gpu_topology> topos;
         std::vector<lvb_gpu_program_view> pre;
-        std::vector<int64_t> lens, clen;
+        std::vector<int64_t> lens, clen, accepts;
         std::vector<size_t> offsets;
+        std::vector<uint8_t> keepf;
+        bool kept_any = false;
     };
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto since = [](std::chrono::steady_clock::time_point a) {
@@ -699,6 +715,12 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
     };
     /* site-block mode keeps the ranks in lock-step through the all-reduce: one half */
     const bool whole = dev.word_count >= 0 && dev.word_count != MSA->nwords;
+    {
+        const char *ke = getenv("LVB_GPU_KEEP");
+        const bool keep_ok = !(ke && atoi(ke) == 0) && !whole;
+        for (int r = r0; r < r1; r++)
+            chains[(size_t)r].keep_ok = keep_ok;
+    }
 #ifdef _OPENMP
     /* this driver thread's team size, also seen by the library when it spreads the schedule
      * compile of a batch over threads (omp_get_max_threads there) */
@@ -796,7 +818,22 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
                 }
             }
             h.lens.resize(h.trees.size());
-            if (!h.trees.empty())
+            h.keepf.assign(h.trees.size(), 0);
+            h.kept_any = false;
+            for (int r = h.a; r < h.b && !whole; r++)
+                if (chains[(size_t)r].keep_first)
+                {
+                    h.keepf[h.offsets[(size_t)(r - h.a)]] = 1;
+                    h.kept_any = true;
+                }
+            if (h.kept_any)
+            {
+                gpu_check(lvb_gpu_score_keep_submit_pre(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
+                                                        h.pre.data(), h.keepf.data(), &h.ticket));
+                score_launches++;
+                h.inflight = true;
+            }
+            else if (!h.trees.empty())
             {
                 gpu_check(lvb_gpu_score_batch_submit_pre(dev.ctx, (int64_t)h.trees.size(), h.trees.data(), h.topos.data(),
                                                          h.pre.data(), &h.ticket));
@@ -835,6 +872,17 @@ static void run_group(Dataptr MSA, Device &dev, std::vector<Chain> &chains, int 
         }
         if (!failure.empty())
             crash("%s", failure.c_str());
+        /* kept proposals that were accepted: the device trees switch over to their rows */
+        h.accepts.clear();
+        for (int r = h.a; r < h.b; r++)
+            if (chains[(size_t)r].accept_kept)
+            {
+                lvb_assert(h.kept_any && h.keepf[h.offsets[(size_t)(r - h.a)]] == 1);
+                h.accepts.push_back((int64_t)h.offsets[(size_t)(r - h.a)]);
+                chains[(size_t)r].accept_kept = false;
+            }
+        if (!h.accepts.empty())
+            gpu_check(lvb_gpu_accept_kept(dev.ctx, h.ticket, (int64_t)h.accepts.size(), h.accepts.data()));
         prof[3] += since(tp0);
     };
     for (int x = 0; x < nh; x++)
@@ -968,7 +1016,13 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
      * in the chains' own loop (profiles/r01i_sa_config5_groups.log; before that, when every device
      * call compiled its batch itself, one group was fastest: 1.60 / 1.95 / 2.1 s).  -G overrides. */
     const int ND = std::max(1, std::min(rc.devices, R));
-    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : std::max(1, std::min(4, R / ND / 16));
+    /* measured again in round 2 (profiles/r02j_sa_probe.log, LVB_GPU_PROFILE <= 1: timing every launch with events
+     * had slowed the earlier runs): a round of a group costs its host thread two device calls and the wait for two
+     * latency-bound kernels whatever the number of chains in it, so few chains go ONE per group — 8 chains of
+     * 1000 x 200k: 0.49 / 0.29 / 0.24 s with 1 / 4 / 8 groups, 16 chains 0.35 / 0.33 s with 8 / 16 — and many
+     * chains (the device is then busy) into 8 groups: 64 chains 0.88 / 0.81 / 0.89 s with 4 / 8 / 16 */
+    const int chains_per_dev = std::max(1, R / ND);
+    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : (chains_per_dev <= 16 ? chains_per_dev : 8);
     per_dev = std::max(1, per_dev);
     int G = std::max(1, std::min(ND * per_dev, R));
     if (dev.word_count >= 0 && dev.word_count != MSA->nwords)

@@ -31,6 +31,11 @@ struct lvb_gpu_ctx
     int64_t *ticket_len[8]; /* submitted batches waiting for lvb_gpu_batch_wait */
     int64_t ticket_n[8];
     int ticket_next;
+    /* lvb_gpu_score_keep_*: the evaluated state of every kept candidate of a batch, until the ticket is reused */
+    int64_t keep_n[8];
+    int *keep_tree[8];
+    uint64_t **keep_rows[8];
+    long **keep_chg[8];
 };
 #define MOCK_TICKETS 8
 
@@ -41,6 +46,7 @@ static int fail(const char *msg)
     return 1;
 }
 
+static void drop_kept(lvb_gpu_ctx *c, int t);
 const char *lvb_gpu_last_error(void) { return g_err; }
 int lvb_gpu_device_count(int *count)
 {
@@ -71,6 +77,8 @@ int lvb_gpu_shutdown(lvb_gpu_ctx *c)
     free(c->right);
     free(c->scratch);
     free(c->scratch_chg);
+    for (int t = 0; t < MOCK_TICKETS; t++)
+        drop_kept(c, t);
     free(c);
     return 0;
 }
@@ -271,6 +279,76 @@ int lvb_gpu_batch_wait(lvb_gpu_ctx *c, int ticket, int64_t *lengths)
         return fail("no such ticket");
     memcpy(lengths, c->ticket_len[ticket], (size_t)c->ticket_n[ticket] * sizeof(int64_t));
     c->ticket_n[ticket] = 0;
+    return 0;
+}
+
+/* score and keep: a kept candidate's rows and counts are put aside; accepting it installs them */
+static void drop_kept(lvb_gpu_ctx *c, int t)
+{
+    for (int64_t k = 0; k < c->keep_n[t]; k++)
+    {
+        free(c->keep_rows[t][k]);
+        free(c->keep_chg[t][k]);
+    }
+    free(c->keep_rows[t]);
+    free(c->keep_chg[t]);
+    free(c->keep_tree[t]);
+    c->keep_rows[t] = NULL;
+    c->keep_chg[t] = NULL;
+    c->keep_tree[t] = NULL;
+    c->keep_n[t] = 0;
+}
+int lvb_gpu_score_keep_submit_pre(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                                  const lvb_gpu_program_view *pre, const uint8_t *keep, int *ticket)
+{
+    (void)pre;
+    if (lvb_gpu_score_batch_submit(c, n_cand, trees, topos, ticket))
+        return 1;
+    const int t = *ticket;
+    drop_kept(c, t);
+    c->keep_n[t] = n_cand;
+    c->keep_tree[t] = (int *)calloc((size_t)n_cand, sizeof(int));
+    c->keep_rows[t] = (uint64_t **)calloc((size_t)n_cand, sizeof(uint64_t *));
+    c->keep_chg[t] = (long **)calloc((size_t)n_cand, sizeof(long *));
+    for (int64_t k = 0; k < n_cand; k++)
+    {
+        c->keep_tree[t][k] = trees[k];
+        if (!keep[k])
+            continue;
+        c->keep_rows[t][k] = (uint64_t *)malloc((size_t)c->B * c->nwords * 8);
+        c->keep_chg[t][k] = (long *)malloc((size_t)c->B * sizeof(long));
+        memcpy(c->keep_rows[t][k], c->rows[trees[k]], (size_t)c->B * c->nwords * 8);
+        memcpy(c->keep_chg[t][k], c->changes[trees[k]], (size_t)c->B * sizeof(long));
+        if (evaluate(c, &topos[k], c->keep_rows[t][k], c->keep_chg[t][k]) != c->ticket_len[t][k])
+            return fail("kept candidate: lengths differ");
+    }
+    return 0;
+}
+int lvb_gpu_score_keep(lvb_gpu_ctx *c, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
+                       const uint8_t *keep, int64_t *lengths, int *ticket)
+{
+    if (lvb_gpu_score_keep_submit_pre(c, n_cand, trees, topos, NULL, keep, ticket))
+        return 1;
+    return lvb_gpu_batch_wait(c, *ticket, lengths);
+}
+int lvb_gpu_accept_kept(lvb_gpu_ctx *c, int ticket, int64_t n_accept, const int64_t *cands)
+{
+    if (ticket < 0 || ticket >= MOCK_TICKETS)
+        return fail("accept: no such ticket");
+    for (int64_t i = 0; i < n_accept; i++)
+    {
+        const int64_t k = cands[i];
+        if (k < 0 || k >= c->keep_n[ticket] || !c->keep_rows[ticket][k])
+            return fail("accept: candidate was not kept");
+        const int t = c->keep_tree[ticket][k];
+        memcpy(c->rows[t], c->keep_rows[ticket][k], (size_t)c->B * c->nwords * 8);
+        memcpy(c->changes[t], c->keep_chg[ticket][k], (size_t)c->B * sizeof(long));
+        free(c->keep_rows[ticket][k]);
+        free(c->keep_chg[ticket][k]);
+        c->keep_rows[ticket][k] = NULL;
+        c->keep_chg[ticket][k] = NULL;
+        c->launches++;
+    }
     return 0;
 }
 

@@ -511,3 +511,103 @@ def test_dependent_piece_store_routes(monkeypatch, env):
                 assert np.array_equal(eng.download_row(t, v), rows[v]), (env, seed, v)
     finally:
         eng.close()
+
+
+def _nni_of(left, right, root, n, u, swap_a):
+    """one NNI rearrangement around internal node u with its dirty path (plain test-input code)"""
+    B = 2 * n - 3
+    parent = np.full(B, -1, dtype=np.int64)
+    for v in list(range(n, B)) + [root]:
+        parent[left[v]] = v
+        parent[right[v]] = v
+    v = int(parent[u])
+    a, b = int(left[u]), int(right[u])
+    c = int(right[v]) if left[v] == u else int(left[v])
+    l2, r2 = left.copy(), right.copy()
+    moved = a if swap_a else b
+    if l2[v] == u:
+        r2[v] = moved
+    else:
+        l2[v] = moved
+    l2[u], r2[u] = (b, c) if swap_a else (a, c)
+    dirty, w = [], u
+    while w != root:
+        dirty.append(w)
+        w = int(parent[w])
+    return l2, r2, dirty
+
+
+@pytest.mark.parametrize("env", [{}, {"LVB_GPU_INLINE": "0"}, {"LVB_GPU_FUSE": "0", "LVB_GPU_DEEP": "0"}])
+def test_score_keep_and_accept(monkeypatch, env):
+    """lvb_gpu_score_keep / lvb_gpu_accept_kept (Solve.c:300-323 without the second evaluation): kept candidates
+    score like the read-only ones; an accepted one IS the tree afterwards — lengths of further candidates, per-node
+    counts and rows as the oracle has them after a commit; one that is not accepted leaves the tree alone.  Twelve
+    rounds on two trees, so rows move between the banks in both directions; a classic commit, a tree copy and the
+    NNI neighbourhood in between read the rows where they are."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    n, m = 150, 20_000
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=5, p=0.1))
+    rng = np.random.default_rng(17)
+    eng = Engine(0)
+    try:
+        eng.upload(enc, max_trees=4)
+        trees = [eng.tree_create(), eng.tree_create()]
+        scratch = eng.tree_create()
+        cur = []
+        for i, t in enumerate(trees):
+            left, right, root = synthetic.random_topology(n, seed=30 + i)
+            want, rows, chg = oracles.oracle_getplen(enc, left, right, root)
+            assert eng.commit(t, Topology(left, right, root)) == want
+            cur.append([left, right, root, rows, chg, want])
+        for rnd in range(12):
+            topos, which, keep, expect = [], [], [], []
+            for i, t in enumerate(trees):
+                left, right, root, rows, chg, _ = cur[i]
+                for j in range(3):
+                    u = int(rng.integers(n, 2 * n - 3))
+                    l2, r2, dirty = _nni_of(left, right, root, n, u, bool(rng.integers(0, 2)))
+                    topos.append(Topology(l2, r2, root, dirty))
+                    which.append(t)
+                    keep.append(1 if j == 1 else 0)  # the middle candidate of each tree is kept
+                    rr, cc = rows.copy(), chg.copy()
+                    rr[dirty, 0] = 0
+                    expect.append((oracles.oracle_getplen(enc, l2, r2, root, rr, cc), l2, r2, dirty))
+            lens, ticket = eng.score_keep(which, topos, keep)
+            assert lens.tolist() == [e[0][0] for e in expect], rnd
+            assert lens.tolist() == eng.score_batch(which, topos).tolist()
+            # tree 0 accepts its kept candidate in even rounds, tree 1 in rounds 1, 2 mod 3; the others stay
+            acc = [k for k in (1, 4) if (rnd % 2 == 0 if k == 1 else rnd % 3 != 0)]
+            if rnd == 5:
+                acc = []
+            eng.accept_kept(ticket, acc)
+            for k in acc:
+                i = k // 3
+                (want, rows, chg), l2, r2, dirty = expect[k]
+                cur[i] = [l2, r2, cur[i][2], rows, chg, want]
+            for i, t in enumerate(trees):
+                left, right, root, rows, chg, want = cur[i]
+                assert eng.score_batch([t], [Topology(left, right, root, [])]).tolist() == [want], (rnd, i)
+                assert np.array_equal(eng.changes(t)[n:], chg[n:]), (rnd, i)
+                for v in (n, n + 71, 2 * n - 4):
+                    assert np.array_equal(eng.download_row(t, v), rows[v]), (rnd, i, v)
+            if rnd == 3:  # a classic commit of tree 0 on top of flipped banks
+                left, right, root, rows, chg, _ = cur[0]
+                l2, r2, dirty = _nni_of(left, right, root, n, n + 40, True)
+                rr, cc = rows.copy(), chg.copy()
+                rr[dirty, 0] = 0
+                want, rr, cc = oracles.oracle_getplen(enc, l2, r2, root, rr, cc)
+                assert eng.commit(trees[0], Topology(l2, r2, root, dirty)) == want
+                cur[0] = [l2, r2, root, rr, cc, want]
+            if rnd == 7:  # the neighbourhood and a copy read the rows where they are
+                left, right, root, rows, chg, want = cur[1]
+                nn = eng.nni_neighbourhood(trees[1], scratch, Topology(left, right, root))
+                l2, r2, _ = _nni_of(left, right, root, n, n + 9, False)
+                assert nn[2 * 9 + 0] == oracles.oracle_getplen(enc, l2, r2, root)[0]
+                spare = eng.tree_create()
+                eng.tree_copy(spare, trees[1])
+                assert eng.score_batch([spare], [Topology(left, right, root, [])]).tolist() == [want]
+                assert np.array_equal(eng.download_row(spare, n + 71), rows[n + 71])
+                eng.tree_destroy(spare)
+    finally:
+        eng.close()
