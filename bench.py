@@ -576,7 +576,8 @@ def main():
             rows_read = [int((compile_schedule(n, c, store=False)[0][:, :2] >= 0).sum()) for c in cands[:64]]
             rows_read_mean = float(np.mean(rows_read))
             score_ms = c_ms / max(1, c_launch)
-            score_traffic, score_src = traffic_from_profile("score_dram_bytes_per_batch")
+            score_traffic, _ = traffic_from_profile("score_dram_bytes_per_batch")
+            prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))) if score_traffic else {}
             extras["sa_trees_scored_per_s"] = {
                 "e2e": reps_c * len(cands) / wall_c, "device": len(cands) / (score_ms * 1e-3),
                 "batch": len(cands), "mean_dirty_nodes": dirty_mean,
@@ -585,14 +586,19 @@ def main():
             }
             operand_gbs = rows_read_mean * 8 * my_words * len(cands) / (score_ms * 1e-3) / 1e9
             extras["roofline_score"] = {
-                "bound": "hbm (L2-assisted)", "unit": "GB/s", "peak": peak,
+                "bound": "integer issue (ALU pipe), not HBM: candidates of one tree share their operand rows through L2",
+                "unit": "GB/s", "peak": peak,
                 "achieved": (score_traffic / (score_ms * 1e-3) / 1e9) if score_traffic else None,
                 "frac": (score_traffic / (score_ms * 1e-3) / 1e9 / peak) if score_traffic else None,
-                "traffic": score_traffic, "traffic_source": score_src,
+                "traffic": score_traffic, "traffic_source": prof.get("score_source"),
+                "l2_hit_pct": prof.get("score_l2_hit_pct"), "alu_pipe_pct": prof.get("score_alu_pipe_pct"),
+                "issue_pct": prof.get("score_issue_pct"),
                 "operand_gbs": operand_gbs, "operand_frac": operand_gbs / peak,
                 "rows_read_per_candidate": rows_read_mean, "kernel": "fitch_score_kernel", "kernel_ms_per_batch": score_ms,
-                "note": "achieved/frac = DRAM bytes of the committed ncu capture / this run's kernel time; operand_* = "
-                        "8 B x nwords x (clean rows read) per candidate (SURVEY 8(d)), part of which L2 serves",
+                "note": "achieved/frac = DRAM bytes per batch of the committed ncu capture / this run's kernel time / HBM peak "
+                        "(low by design: 80 % of the operand sectors hit L2); what bounds the kernel is instruction issue, "
+                        "alu_pipe_pct / issue_pct of the same capture; operand_* = 8 B x nwords x (clean rows read) per "
+                        "candidate (SURVEY 8(d)), served by L2 + HBM together",
             }
             # ---- exhaustive NNI neighbourhood (deterministic_hillclimb's 2(n-3) candidates) in one call ----
             scratch = eng.tree_create()

@@ -217,6 +217,17 @@ void lvbh_tree_set(void *hv, void *tv, const long *parent, const long *left, con
     ss_init(&((Handle *)hv)->msa, t);
 }
 
+/* the same sequence of tree-stack pushes as ref_treestack_sequence of oracle/ref_shim.cpp */
+long lvbh_treestack_sequence(void *hv, long count, void *const *trees, const long *roots, int hash, long *results)
+{
+    Handle *h = (Handle *)hv;
+    TREESTACK stack = CreateNewTreestack();
+    for (long i = 0; i < count; i++)
+        results[i] = hash ? CompareHashTreeToHashstack(&h->msa, &stack, (const TREESTACK_TREE_NODES *)trees[i], roots[i])
+                          : CompareTreeToTreestack(&h->msa, &stack, (const TREESTACK_TREE_NODES *)trees[i], roots[i]);
+    return stack.next;
+}
+
 int lvbh_same_topology(void *hv, const void *t1, long r1, const void *t2, long r2)
 {
     Handle *h = (Handle *)hv;

@@ -1022,7 +1022,12 @@ void GetSolnBatched(Dataptr MSA, const Parameters &rc, Device &dev, int replicat
      * 1000 x 200k: 0.49 / 0.29 / 0.24 s with 1 / 4 / 8 groups, 16 chains 0.35 / 0.33 s with 8 / 16 — and many
      * chains (the device is then busy) into 8 groups: 64 chains 0.88 / 0.81 / 0.89 s with 4 / 8 / 16 */
     const int chains_per_dev = std::max(1, R / ND);
-    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : (chains_per_dev <= 16 ? chains_per_dev : 8);
+    /* ... but never more groups than host threads: a driver thread spins while it waits for its lengths, and on the
+     * 8-GPU box (32 cores, 4 per rank) 8 groups of one chain on 4 cores took 0.37 s where the 16-core single-GPU box
+     * needs 0.19 s (profiles/r02o_bench_n8.json, r02n_sa_probe.log); groups of two chains work as two alternating
+     * halves instead, one chain's host work under the other's kernel */
+    const int by_threads = std::max(1, host_threads / ND);
+    int per_dev = rc.groups > 0 ? std::max(1, rc.groups / ND) : std::min(by_threads, chains_per_dev <= 16 ? chains_per_dev : 8);
     per_dev = std::max(1, per_dev);
     int G = std::max(1, std::min(ND * per_dev, R));
     if (dev.word_count >= 0 && dev.word_count != MSA->nwords)

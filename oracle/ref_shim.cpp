@@ -13,6 +13,7 @@
  * treealloc -> PullRandomTree -> ss_init -> getplen / mutate_* / arbreroot.
  */
 #include "LVB.h"
+#include "Hash.h"
 #include "DataOperations.h"
 #include "MemoryOperations.h"
 #include "SearchParameters.h"
@@ -319,6 +320,22 @@ extern "C"
 			}
 		}
 		FreeTreestackMemory(h->msa, &stack);
+	}
+
+	/* A sequence of pushes into one fresh tree stack: results[i] = what CompareTreeToTreestack (hash == 0,
+	 * Treestack.c:231-306) or CompareHashTreeToHashstack (hash != 0, Hash.cpp:49-90) returns for trees[i]
+	 * (1 = pushed as new, 0 = a duplicate of a topology already there); returns the final stack size.
+	 * Used by tests/test_host_parity.py to pin the repository's own duplicate detection. */
+	long ref_treestack_sequence(void *hv, long count, void *const *trees, const long *roots, int hash, long *results)
+	{
+		RefHandle *h = (RefHandle *)hv;
+		TREESTACK stack = CreateNewTreestack();
+		for (long i = 0; i < count; i++)
+			results[i] = hash ? CompareHashTreeToHashstack(h->msa, &stack, (const TREESTACK_TREE_NODES *)trees[i], roots[i], LVB_FALSE)
+			                  : CompareTreeToTreestack(h->msa, &stack, (const TREESTACK_TREE_NODES *)trees[i], roots[i], LVB_FALSE);
+		const long size = stack.next;
+		FreeTreestackMemory(h->msa, &stack);
+		return size;
 	}
 
 	/* ---- timing legs for bench.py (cpu_baseline / --impl reference) ----

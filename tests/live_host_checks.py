@@ -72,6 +72,72 @@ def ops(n, m, seed, steps=3000):
     same(ref.tree().random(), h.tree().random(), "PullRandomTree again")
 
 
+def stack(n, m, seed, count=400):
+    """duplicate detection of the tree stack.  One sequence of trees — proposals, the same tree
+    again, the same topology re-rooted, trees pushed long before — goes into a fresh stack on both sides:
+    CompareTreeToTreestack (Treestack.c:231-306) and CompareHashTreeToHashstack (Hash.cpp:49-90) of the reference
+    against lvb_b200/host/treestack.cpp; every push must give the same answer (1 = new, 0 = duplicate)."""
+    import ctypes as C
+
+    rng = np.random.default_rng(seed)
+    mat = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=(n, m))]
+    rows = [bytes(r) for r in mat]
+    ref = oracles.RefMSA.from_rows(rows)
+    h = host.HostMSA.from_rows(rows)
+    L = oracles.ref()
+    L.ref_rinit(seed + 9)
+    h.rinit(seed + 9)
+    rc, hc = ref.tree().random(), h.tree().random()
+    rc.getplen()
+    hc.mark_clean()
+    rts, hts, kinds = [], [], []
+
+    def keep(what):
+        rts.append(ref.tree().copy_from(rc))
+        hts.append(h.tree().copy_from(hc))
+        kinds.append(what)
+
+    keep("start")
+    for i in range(count):
+        r = int(rng.integers(0, 10))
+        if r < 5:  # a rearrangement becomes the current tree
+            kind = ("nni", "spr", "tbr")[i % 3]
+            rp, hp = ref.tree().mutate(kind, rc), h.tree().mutate(kind, hc)
+            rp.getplen()
+            hp.mark_clean()
+            rc, hc = rp, hp
+            keep(kind)
+        elif r < 7:  # the same unrooted topology seen from another root
+            rc.arbreroot()
+            hc.arbreroot()
+            assert rc.root == hc.root
+            keep("reroot")
+        elif r < 8:  # exactly the same tree again
+            keep("again")
+        else:  # a tree that went in earlier
+            j = int(rng.integers(0, len(rts)))
+            rts.append(rts[j]); hts.append(hts[j]); kinds.append(("old", j))
+    k = len(rts)
+    roots_r = (C.c_long * k)(*[t.root for t in rts])
+    roots_h = (C.c_long * k)(*[t.root for t in hts])
+    assert list(roots_r) == list(roots_h)
+    ptr_r = (C.c_void_p * k)(*[t.t for t in rts])
+    ptr_h = (C.c_void_p * k)(*[t.t for t in hts])
+    L.ref_treestack_sequence.restype = C.c_long
+    L.ref_treestack_sequence.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    HL = host.load_host_library()
+    HL.lvbh_treestack_sequence.restype = C.c_long
+    HL.lvbh_treestack_sequence.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    for use_hash in (0, 1):
+        res_r, res_h = (C.c_long * k)(), (C.c_long * k)()
+        size_r = L.ref_treestack_sequence(ref.h, k, ptr_r, roots_r, use_hash, res_r)
+        size_h = HL.lvbh_treestack_sequence(h.h, k, ptr_h, roots_h, use_hash, res_h)
+        bad = [(i, kinds[i], res_r[i], res_h[i]) for i in range(k) if res_r[i] != res_h[i]]
+        assert not bad, (use_hash, bad[:5])
+        assert size_r == size_h and 1 < size_r < k, (use_hash, size_r, size_h, k)
+        assert any(res_r[i] == 0 for i in range(k) if kinds[i] == "reroot")  # a re-rooted tree IS a duplicate
+
+
 if __name__ == "__main__":
     globals()[sys.argv[1]](*[int(a) for a in sys.argv[2:]])
     print("ok")

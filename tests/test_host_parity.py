@@ -153,6 +153,14 @@ def test_topology_key_is_root_and_order_invariant(golden_dir):
     assert a.same_topology(d)
 
 
+@needs_ref
+@pytest.mark.parametrize("n,m,seed", [(6, 40, 1), (12, 40, 2), (60, 120, 3), (200, 64, 4)])
+def test_tree_stack_duplicates_match_reference_live(n, m, seed):
+    """tree-stack pushes (CompareTreeToTreestack / CompareHashTreeToHashstack): the same answer as the reference
+    for every tree of a sequence with rearrangements, repeats, re-rooted copies and old trees"""
+    run_isolated("stack", n, m, seed)
+
+
 def test_newick_text(tmp_path):
     rows = [b"AAAAA", b"AAACC", b"CCAAC", b"CCGGT", b"GGTTT", b"GTTTA"]
     h = host.HostMSA.from_rows(rows)
