@@ -178,6 +178,11 @@ int lvb_gpu_score_batch_submit_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *
  *                                  batch must still be held: at most 7 device calls after its submit, and
  *                                  after its lengths were fetched.  Returns without waiting for the device;
  *                                  the trees count as changed for every later call. */
+/* measuring aid (LVB_GPU_TRACE=1 when the context is made): six device time stamps in ns per work item — (piece,
+ * column block), in hand-out order — of the last whole-tree store launch: ticket drawn, instructions decoded,
+ * published, first operand taken, last step done, books kept.  out == NULL: only the counts. */
+int lvb_gpu_trace_download(lvb_gpu_ctx *ctx, uint64_t *out, int64_t cap_items, int64_t *n_items, int64_t *n_colblocks);
+
 int lvb_gpu_score_keep_submit_pre(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,
                                   const lvb_gpu_program_view *pre, const uint8_t *keep, int *ticket);
 int lvb_gpu_score_keep(lvb_gpu_ctx *ctx, int64_t n_cand, const int *trees, const lvb_gpu_topology *topos,

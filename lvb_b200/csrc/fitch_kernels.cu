@@ -96,6 +96,14 @@ __device__ __forceinline__ void sts128_if(unsigned addr, const uint4 &v, unsigne
                  : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(addr), "r"(pred)
                  : "memory");
 }
+__device__ __forceinline__ void sts16_if(unsigned addr, unsigned v, unsigned pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b16 h;\n\tsetp.ne.b32 p, %2, 0;\n\tcvt.u16.u32 h, %0;\n\t"
+                 "@p st.shared.u16 [%1], h;\n\t}"
+                 :
+                 : "r"(v), "r"(addr), "r"(pred)
+                 : "memory");
+}
 __device__ __forceinline__ void sts32_if(unsigned addr, unsigned v, unsigned pred)
 {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t"
@@ -974,7 +982,8 @@ static cudaError_t want_smem(K kernel, size_t smem)
  * fitch_score_body this removes the per-thread address arithmetic, LDGSTS issue and group
  * bookkeeping from the inner loop, and the ring only holds REAL loads (half of the operands of a
  * post-order program are the previous result or a stack slot), so the same look-ahead costs half the
- * shared memory and twice as many CTAs fit an SM.
+ * shared memory and twice as many CTAs fit an SM.  A third role, the BOOKKEEPER warp, does what follows the
+ * last step of a piece (counts to global memory, the piece counted in for the level above, the finalize).
  * The CTAs are persistent: the producer takes the next (piece, column block) ticket, stages and
  * decodes its instructions into the other instruction buffer and starts its loads while the
  * consumers still work on the current piece — no start-up or drain bubble between pieces.
@@ -1026,11 +1035,12 @@ __device__ __forceinline__ void bulk_load(unsigned dst, unsigned long long src, 
                  : "r"(dst), "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ void consumer_barrier(int nt)
+__device__ __forceinline__ unsigned long long global_ns()
 {
-    asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
-
 /* piece_finalize done by ONE warp (warp 0 of the consumers) while the other warps go on with the next
  * piece: the column block of a piece that finishes last folds that piece's counts into chg / sum_chg,
  * the piece of a candidate that is folded last publishes the candidate's length. */
@@ -1096,18 +1106,20 @@ __device__ __forceinline__ void stream_finalize_warp(const ExecParams &p, const 
     }
 }
 
-__global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
+__global__ void __launch_bounds__(320) fitch_stream_kernel(const ExecParams p)
 {
     extern __shared__ uint4 smem_u4[];
-    __shared__ __align__(8) unsigned long long s_bar[2 * LVB_SR + 4]; /* full[SR], empty[SR], ifull[2], iempty[2] */
+    /* full[SR], empty[SR], ifull[2], iempty[2], cdone[2] */
+    __shared__ __align__(8) unsigned long long s_bar[2 * LVB_SR + 6];
     __shared__ StreamWork s_work[2];
 
-    const int nt = (int)blockDim.x - 32; /* consumer threads */
+    const int nt = (int)blockDim.x - 64; /* consumer threads; then the producer warp, then the bookkeeper warp */
     const int nwarps = nt >> 5;
     const int tid = threadIdx.x;
     uint4 *s_instr = smem_u4;                                              /* [2][LVB_SCHUNK] decoded instructions */
-    int *s_cnt = reinterpret_cast<int *>(smem_u4 + 2 * LVB_SCHUNK);         /* [2][LVB_SCHUNK][nwarps] */
-    uint4 *s_ring = smem_u4 + 2 * LVB_SCHUNK + (2 * LVB_SCHUNK * nwarps + 3) / 4; /* [LVB_SR][nt] */
+    /* [2][LVB_SCHUNK][nwarps] 16-bit: a warp's count of one step is at most 32 x 32 sites */
+    unsigned short *s_cnt = reinterpret_cast<unsigned short *>(smem_u4 + 2 * LVB_SCHUNK);
+    uint4 *s_ring = smem_u4 + 2 * LVB_SCHUNK + (2 * LVB_SCHUNK * nwarps + 7) / 8; /* [LVB_SR][nt] */
     uint4 *s_stack = s_ring + LVB_SR * nt;                                  /* [n_slots][nt] */
 
     /* made opaque to the compiler, which otherwise re-derives the shared window base at every use */
@@ -1117,6 +1129,7 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
     auto empty_bar = [&](unsigned s) { return bar0 + 8u * (LVB_SR + s); };
     auto ifull_bar = [&](unsigned b) { return bar0 + 8u * (2 * LVB_SR + b); };
     auto iempty_bar = [&](unsigned b) { return bar0 + 8u * (2 * LVB_SR + 2 + b); };
+    auto cdone_bar = [&](unsigned b) { return bar0 + 8u * (2 * LVB_SR + 4 + b); };
     if (tid == 0)
     {
         for (unsigned s = 0; s < LVB_SR; s++)
@@ -1127,7 +1140,8 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
         for (unsigned b = 0; b < 2; b++)
         {
             mbar_init(ifull_bar(b), 1u);
-            mbar_init(iempty_bar(b), (unsigned)nwarps);
+            mbar_init(iempty_bar(b), 1u);               /* the bookkeeper hands the buffer back */
+            mbar_init(cdone_bar(b), (unsigned)nwarps);  /* every consumer warp is through with the chunk */
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -1138,6 +1152,53 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
     const unsigned total = (unsigned)p.n_prog * (unsigned)p.n_colblocks;
     const bool piece_major = p.dep != nullptr;
 
+    if (tid >= nt + 32)
+    { /* ---------------- bookkeeper warp ----------------
+       * What has to happen after the last step of a chunk — the per-instruction counts of the CTA into global
+       * memory, the piece counted in for the level above (after a fence behind every row store of the CTA), the
+       * fused finalize — is a chain of fences and atomic round trips (~10 us under load, measured with
+       * LVB_GPU_TRACE).  Done by a consumer warp it stalls the whole CTA through the operand ring; here the
+       * consumers only arrive on an mbarrier and go on with the next piece. */
+        const int lane = tid - nt - 32;
+        for (unsigned q = 0;; q++)
+        {
+            const unsigned buf = q & 1u;
+            mbar_wait(ifull_bar(buf), (q >> 1) & 1u);
+            const int m = s_work[buf].n;
+            if (m == 0)
+                break;
+            const FitchProgram prog = s_work[buf].prog;
+            const int base = s_work[buf].base, last = s_work[buf].last, prog_id = s_work[buf].prog_id, cb = s_work[buf].cb;
+            const unsigned item = (unsigned)s_work[buf].pad[0];
+            mbar_wait(cdone_bar(buf), (q >> 1) & 1u); /* counts and row stores of every consumer warp are issued */
+            /* first of all the piece is counted in: pieces of the level above wait for nothing but this */
+            if (last && piece_major && prog.parent >= 0 && lane == 0)
+            {
+                __threadfence();
+                atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
+            }
+            const unsigned short *cnt = s_cnt + buf * (LVB_SCHUNK * nwarps);
+            for (int k = lane; k < m; k += 32)
+            {
+                int sum = 0;
+                for (int w = 0; w < nwarps; w++)
+                    sum += cnt[k * nwarps + w];
+                if (sum)
+                    atomicAdd(&p.cnts[prog.instr_begin + base + k], sum);
+            }
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(iempty_bar(buf)); /* the producer may stage the chunk after next here */
+            if (last)
+            {
+                if (p.fused_finalize)
+                    stream_finalize_warp(p, p.instr, prog, prog_id, lane);
+                if (p.trace && lane == 0)
+                    p.trace[6 * (size_t)item + 5] = global_ns();
+            }
+        }
+        return;
+    }
     if (tid >= nt)
     { /* ---------------- producer warp ---------------- */
         const int lane = tid - nt;
@@ -1151,6 +1212,8 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                 vb = atomicAdd(p.ticket, 1u);
             vb = __shfl_sync(0xffffffffu, vb, 0);
             bool stop = vb >= total;
+            if (p.trace && lane == 0 && !stop)
+                p.trace[6 * (size_t)vb + 0] = global_ns();
             if (stop && lane == 0 && vb == total + gridDim.x - 1u)
                 *p.ticket = 0u; /* every CTA has drawn its last ticket: ready for the next launch */
             int prog_id = 0, cb = 0;
@@ -1240,6 +1303,8 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                     }
                     dst[i] = make_uint4((unsigned)a, (unsigned)b, in.node >= 0 ? (unsigned)in.node + tree_off + ((in.ctl & LVB_CTL_BANK1) ? (unsigned)p.n_internal : 0u) : 0u, w);
                 }
+                if (p.trace && lane == 0 && !stop && base == 0)
+                    p.trace[6 * (size_t)vb + 1] = global_ns();
                 /* a dependent piece is published only when the rows of the level below are there */
                 unsigned ok = 1u;
                 if (!stop && !waited && piece_major && prog.flags > 0)
@@ -1267,9 +1332,12 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                     ok = __shfl_sync(0xffffffffu, ok, 0);
                     waited = true;
                 }
+                if (p.trace && lane == 0 && !stop && base == 0)
+                    p.trace[6 * (size_t)vb + 2] = global_ns();
                 if (lane == 0)
                 {
                     StreamWork &wk = s_work[buf];
+                    wk.pad[0] = (int32_t)vb;
                     wk.n = ok ? m : 0;
                     wk.base = base;
                     wk.last = base + LVB_SCHUNK >= prog.n_instr ? 1 : 0;
@@ -1321,7 +1389,7 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
     const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
     const unsigned sa_stack = (unsigned)__cvta_generic_to_shared(s_stack + tid);
     const unsigned lane0 = (tid & 31) == 0 ? 1u : 0u;
-    const unsigned cnt_step = (unsigned)nwarps * 4u;
+    const unsigned cnt_step = (unsigned)nwarps * 2u;
     uint4 acc = make_uint4(~0u, ~0u, ~0u, ~0u);
     unsigned jc = 0; /* loads taken */
     for (unsigned q = 0;; q++)
@@ -1337,8 +1405,8 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
         const unsigned amask = active ? ~0u : 0u;
         const unsigned long long colbase = reinterpret_cast<unsigned long long>(p.pool + min(col, p.ncols - 1));
         const unsigned ia0 = sa_instr + buf * (LVB_SCHUNK * 16u);
-        int *cnt = s_cnt + buf * (LVB_SCHUNK * nwarps);
-        const unsigned sa_cnt = (unsigned)__cvta_generic_to_shared(cnt + (tid >> 5));
+        const unsigned sa_cnt = (unsigned)__cvta_generic_to_shared(s_cnt + buf * (LVB_SCHUNK * nwarps) + (tid >> 5));
+        const unsigned item = (unsigned)s_work[buf].pad[0];
         for (int i = 0; i < m; i++)
         {
             const uint4 ci = lds128(ia0 + (unsigned)i * 16u);
@@ -1365,49 +1433,27 @@ __global__ void __launch_bounds__(288) fitch_stream_kernel(const ExecParams p)
                     mbar_arrive(bar0 + 8u * (LVB_SR + s));
                 jc++;
             }
+            if (p.trace && tid == 0 && i == 0 && s_work[buf].base == 0)
+                p.trace[6 * (size_t)item + 3] = global_ns();
             const unsigned f = fitch_step(acc, y, acc) & amask;
-            sts32_if(sa_cnt + (unsigned)i * cnt_step, __reduce_add_sync(0xffffffffu, __popc(f)), lane0);
+            sts16_if(sa_cnt + (unsigned)i * cnt_step, __reduce_add_sync(0xffffffffu, __popc(f)), lane0);
             stg_if(row_addr(ci.z, stride_b, colbase), acc, (ci.w & D_STORE) & active);
             sts128_if(sa_stack + (ci.w & 0x0ffffff0u), acc, ci.w & D_PUSH);
         }
-        /* chunk end: per-instruction counts of the CTA -> global; then the piece's bookkeeping */
-        const FitchProgram prog = s_work[buf].prog;
-        const int base = s_work[buf].base, last = s_work[buf].last, prog_id = s_work[buf].prog_id;
-        consumer_barrier(nt); /* counts and row stores of every consumer are issued */
-        if (tid >= 32)
-        { /* the other warps go on with the next chunk; warp 0 keeps the books of this one */
-            if (lane0)
-                mbar_arrive(iempty_bar(buf));
-            continue;
-        }
-        for (int k = tid; k < m; k += 32)
-        {
-            int sum = 0;
-            for (int w = 0; w < nwarps; w++)
-                sum += cnt[k * nwarps + w];
-            if (sum)
-                atomicAdd(&p.cnts[prog.instr_begin + base + k], sum);
-        }
+        if (p.trace && tid == 0 && s_work[buf].last)
+            p.trace[6 * (size_t)item + 4] = global_ns();
+        /* chunk end: this warp's counts and row stores are issued (the arrive releases them to the bookkeeper) */
         __syncwarp();
         if (lane0)
-            mbar_arrive(iempty_bar(buf)); /* the producer may stage the chunk after next here */
-        if (last)
-        {
-            if (piece_major && prog.parent >= 0 && tid == 0)
-            {
-                __threadfence();
-                atomicAdd(p.dep + (size_t)prog.parent * p.n_colblocks + cb, 1u);
-            }
-            if (p.fused_finalize)
-                stream_finalize_warp(p, p.instr, prog, prog_id, tid);
-        }
+            mbar_arrive(cdone_bar(buf));
     }
 }
+
 
 static size_t stream_smem_bytes(int n_slots, int nt)
 {
     const int nwarps = nt / 32;
-    return (size_t)(2 * LVB_SCHUNK + (2 * LVB_SCHUNK * nwarps + 3) / 4 + (size_t)(LVB_SR + n_slots) * nt) * sizeof(uint4);
+    return (size_t)(2 * LVB_SCHUNK + (2 * LVB_SCHUNK * nwarps + 7) / 8 + (size_t)(LVB_SR + n_slots) * nt) * sizeof(uint4);
 }
 
 cudaError_t launch_fitch_stream(const ExecParams &p, int nt, cudaStream_t stream)
@@ -1425,13 +1471,13 @@ cudaError_t launch_fitch_stream(const ExecParams &p, int nt, cudaStream_t stream
     if ((e = want_smem(fitch_stream_kernel, smem)) != cudaSuccess)
         return e;
     int per_sm = 0;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fitch_stream_kernel, nt + 32, smem)) != cudaSuccess)
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fitch_stream_kernel, nt + 64, smem)) != cudaSuccess)
         return e;
     if (per_sm < 1)
         return cudaErrorLaunchOutOfResources;
     const long long total = (long long)p.n_prog * p.n_colblocks;
     const unsigned grid = (unsigned)std::min<long long>(total, (long long)sms[dev] * per_sm);
-    fitch_stream_kernel<<<grid, nt + 32, smem, stream>>>(p);
+    fitch_stream_kernel<<<grid, nt + 64, smem, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -1683,26 +1729,52 @@ cudaError_t launch_apply_kept(const FitchInstr *instr, const FitchProgram *cand,
  * branch) and returns both length differences: 6 rows of traffic per PAIR of candidates, whatever
  * the depth of u.  The kernel is bound by integer issue, not by HBM (ncu: ALU pipe 86 %), so
  * reading low(u)/up(u) instead of recomputing fitch(A,B)/fitch(C,D) is a net gain. */
-__device__ __forceinline__ unsigned fitch_lane_flags(unsigned x, unsigned y)
+/* The neighbourhood kernel is bound by the ALU pipe (LOP3 / SHF / IADD: 82 % busy, the FMA pipe a third of that), so
+ * its additions go to the FMA pipe as multiply-adds: t * one + 0x7777... with `one` = 1 from the kernel parameters
+ * (an immediate 1 would be folded back into an IADD). */
+__device__ __forceinline__ unsigned add7_fma(unsigned t, unsigned one)
+{
+    unsigned a;
+    asm("mad.lo.u32 %0, %1, %2, 0x77777777;" : "=r"(a) : "r"(t & 0x77777777u), "r"(one));
+    return a;
+}
+__device__ __forceinline__ unsigned fitch_lane_flags(unsigned x, unsigned y, unsigned one)
 {
     const unsigned t = x & y;
-    const unsigned a = (t & 0x77777777u) + 0x77777777u;
+    const unsigned a = add7_fma(t, one);
     return ~(a | t) & 0x88888888u;
 }
-/* number of sites of the column whose intersection is empty (no result row wanted) */
-__device__ __forceinline__ int fitch_count(const uint4 &x, const uint4 &y)
+__device__ __forceinline__ unsigned fitch_lane_fma(unsigned x, unsigned y, unsigned &out, unsigned one)
 {
-    const unsigned f = (fitch_lane_flags(x.x, y.x) >> 3) | (fitch_lane_flags(x.y, y.y) >> 2) |
-                       (fitch_lane_flags(x.z, y.z) >> 1) | fitch_lane_flags(x.w, y.w);
+    const unsigned t = x & y;
+    const unsigned a = add7_fma(t, one);
+    const unsigned e8 = ~(a | t) & 0x88888888u;
+    const unsigned s = e8 >> 3; /* 1 per site whose intersection is empty */
+    out = t | ((x | y) & (s * 15u));
+    return s;
+}
+__device__ __forceinline__ unsigned fitch_step_fma(const uint4 &x, const uint4 &y, uint4 &out, unsigned one)
+{
+    const unsigned s0 = fitch_lane_fma(x.x, y.x, out.x, one);
+    const unsigned s1 = fitch_lane_fma(x.y, y.y, out.y, one);
+    const unsigned s2 = fitch_lane_fma(x.z, y.z, out.z, one);
+    const unsigned s3 = fitch_lane_fma(x.w, y.w, out.w, one);
+    return s0 + 2u * s1 + 4u * s2 + 8u * s3;
+}
+/* number of sites of the column whose intersection is empty (no result row wanted) */
+__device__ __forceinline__ int fitch_count(const uint4 &x, const uint4 &y, unsigned one)
+{
+    const unsigned f = (fitch_lane_flags(x.x, y.x, one) >> 3) | (fitch_lane_flags(x.y, y.y, one) >> 2) |
+                       (fitch_lane_flags(x.z, y.z, one) >> 1) | fitch_lane_flags(x.w, y.w, one);
     return __popc(f);
 }
-__device__ __forceinline__ int join_cost(const uint4 &p, const uint4 &q, const uint4 &r, const uint4 &s)
+__device__ __forceinline__ int join_cost(const uint4 &p, const uint4 &q, const uint4 &r, const uint4 &s, unsigned one)
 {
     /* ((p,q),(r,s)) evaluated on its middle branch */
     uint4 pq, rs;
-    int c = __popc(fitch_step(p, q, pq));
-    c += __popc(fitch_step(r, s, rs));
-    return c + fitch_count(pq, rs);
+    int c = __popc(fitch_step_fma(p, q, pq, one));
+    c += __popc(fitch_step_fma(r, s, rs, one));
+    return c + fitch_count(pq, rs, one);
 }
 
 __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams p)
@@ -1732,9 +1804,9 @@ __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams 
         /* the current tree on this branch costs changes(A,B) + changes(C,D) + changes(low(u), up(u)):
          * the first two are the cached counts of u in the two trees (subtracted once per branch
          * below), both sets are rows already — only the third term is computed here */
-        const int cur = fitch_count(LU, UU);
-        d0 = join_cost(A, C, B, D) - cur;
-        d1 = join_cost(B, C, A, D) - cur;
+        const int cur = fitch_count(LU, UU, p.one);
+        d0 = join_cost(A, C, B, D, p.one) - cur;
+        d1 = join_cost(B, C, A, D, p.one) - cur;
     }
     d0 = __reduce_add_sync(0xffffffffu, d0);
     d1 = __reduce_add_sync(0xffffffffu, d1);

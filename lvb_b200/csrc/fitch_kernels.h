@@ -90,6 +90,9 @@ struct ExecParams
                                   * block follow `lag` column blocks behind its level below instead of after ALL column
                                   * blocks of that level: by the time they are drawn their operands are normally there,
                                   * and the end of the launch has only the last column blocks' small upper pieces left */
+    unsigned long long *trace;   /* streaming kernel, LVB_GPU_TRACE=1 (a measuring aid, NULL otherwise): per work item
+                                  * (ticket) six %globaltimer stamps: ticket drawn, instructions decoded, published (after
+                                  * the wait for the level below), first operand in registers, last step done, books kept */
     int32_t fuse_p2p;            /* streaming kernel, fused finalize, site-block mode: the thread that completes a
                                   * candidate's partial length exchanges it with the other ranks through peer memory
                                   * right there (x: in/out/K unused; the candidate number is the entry) — the launch
@@ -158,6 +161,7 @@ struct NniParams
     const int32_t *chg_low; /* [n_edges] cached counts of u in the evaluated tree = changes(A,B) over all columns */
     const int32_t *chg_up;  /* [n_edges] the same in the scratch tree (left by the up-pass) = changes(C,D) */
     long long *delta;       /* [2 * n_edges] */
+    unsigned one;           /* = 1: a multiplier the compiler cannot fold (additions as IMAD on the FMA pipe) */
 };
 cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t stream);
 

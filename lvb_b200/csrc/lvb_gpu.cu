@@ -160,7 +160,7 @@ struct lvb_gpu_ctx
     std::vector<FitchProgram> prog;                    /* pieces, sorted by level */
     std::vector<std::pair<int32_t, int32_t>> levels;   /* (first piece, count) per launch */
     int piece_min = 64;                                /* smallest piece size asked of the compiler (LVB_GPU_PIECE_MIN) */
-    int64_t target_warps = 148 * 128;                  /* resident warps wanted per launch */
+    int64_t target_warps = 148 * 96;                   /* resident warps wanted per launch */
     unsigned long long *d_totals = nullptr;            /* [cap_tot] per-program sums; zero between batches */
     unsigned *d_done = nullptr;                        /* [cap_tot] CTAs finished per program; zero between batches */
     long long *d_lengths = nullptr;                    /* [cap_tot] lengths on the device (site-block mode: all-reduced here) */
@@ -184,9 +184,10 @@ struct lvb_gpu_ctx
     bool fuse_ok = true;     /* single-level store batches finalize inside the Fitch kernel (LVB_GPU_FUSE=0: own launch) */
     bool score_v1 = false;
     bool level_launches = false;                       /* one launch per level instead of dependent pieces in one launch */
-    int stream_nt = 256;                               /* dependent-piece store launches: consumer threads per CTA of the
+    int stream_nt = -1;                                /* dependent-piece store launches: consumer threads per CTA of the
                                                         * streaming kernel (TMA bulk loads); 0 = the cp.async / register
-                                                        * pipelined kernels below (LVB_GPU_STORE_STREAM) */
+                                                        * pipelined kernels below (LVB_GPU_STORE_STREAM); -1 = by the row
+                                                        * width, see stream_threads() */
     int store_pf = 7;                                  /* dependent-piece store launches: 0 = register-pipelined kernel,
                                                         * 2/3/5/7 = cp.async ring with that look-ahead (LVB_GPU_STORE_PF) */
     unsigned spin_limit = 1u << 26;                    /* polls (>= 100 ns each) before a dependency wait is abandoned */
@@ -229,6 +230,10 @@ struct lvb_gpu_ctx
     unsigned long long *p2p_peer[LVB_P2P_MAX_RANKS] = {};
     int64_t p2p_kmax = 8192;
     uint32_t p2p_seq = 0;
+    /* LVB_GPU_TRACE=1: time stamps of every work item of the last streaming store launch (lvb_gpu_trace_download) */
+    bool trace = false;
+    unsigned long long *d_trace = nullptr;
+    size_t cap_trace = 0, n_trace = 0;
     bool p2p_fuse = true;                              /* LVB_GPU_P2P_FUSE=0: always the separate all-reduce kernel */
 
     /* LVB_GPU_PROFILE=1: host seconds per stage of commit/score calls, printed at shutdown */
@@ -338,10 +343,19 @@ static int pick_block(const lvb_gpu_ctx *c)
     return 64;
 }
 
+/* consumer threads per CTA of the streaming kernel: 256 (4 KB operand segments) for wide rows, 128 when that would
+ * leave under 32 column blocks — the word blocks of an 8-GPU run of 2000 x 1M: 0.0705 ms against 0.0733 per pass */
+static int stream_threads(const lvb_gpu_ctx *c)
+{
+    if (c->stream_nt >= 0)
+        return c->stream_nt;
+    return c->stride_u4 >= 8192 ? 256 : 128;
+}
+
 /* column-block width of a store launch of dependent pieces: the streaming kernel has its own */
 static int dep_block(const lvb_gpu_ctx *c)
 {
-    return c->stream_nt > 0 ? c->stream_nt : pick_block(c);
+    return stream_threads(c) > 0 ? stream_threads(c) : pick_block(c);
 }
 
 /* fold finished event pairs into the running kernel-time total */
@@ -455,9 +469,9 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
     p.peek = st.keep_batch ? 1 : 0;
     p.kept = st.d_kept;
     p.newsum = st.d_newsum;
-    const bool stream = store && c->last_dep && c->stream_nt > 0;
-    const int block = stream ? c->stream_nt : pick_block(c);
-    p.stream_nt = stream ? c->stream_nt : 0;
+    const bool stream = store && c->last_dep && stream_threads(c) > 0;
+    const int block = stream ? stream_threads(c) : pick_block(c);
+    p.stream_nt = stream ? stream_threads(c) : 0;
     p.n_colblocks = (int32_t)((c->stride_u4 + block - 1) / block);
     p.n_slots = c->last_slots;
     p.score_v1 = c->score_v1 ? 1 : 0;
@@ -509,6 +523,22 @@ static int launch_resident(lvb_gpu_ctx *c, int64_t *lengths, bool reduce_always 
         p.x.out2 = (lengths || defer) ? st.d_len : nullptr;
         p.x.err = c->d_err;
         p.x.spin_limit = c->spin_limit;
+    }
+    p.trace = nullptr;
+    if (c->trace && stream)
+    {
+        const size_t items = (size_t)c->last_n_prog * (size_t)p.n_colblocks;
+        if (items > c->cap_trace)
+        {
+            CU(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_trace);
+            c->d_trace = nullptr;
+            CU(cudaMalloc(&c->d_trace, items * 6 * sizeof(unsigned long long)));
+            c->cap_trace = items;
+        }
+        CU(cudaMemsetAsync(c->d_trace, 0, items * 6 * sizeof(unsigned long long), c->stream));
+        c->n_trace = items;
+        p.trace = c->d_trace;
     }
     p.n_levels = 1;
     p.lag = -1;
@@ -1069,6 +1099,8 @@ extern "C"
         const char *pm = getenv("LVB_GPU_PIECE_MIN");
         if (pm && atoi(pm) >= 1)
             c->piece_min = atoi(pm);
+        const char *tr = getenv("LVB_GPU_TRACE");
+        c->trace = tr && atoi(tr) != 0;
         const char *tp = getenv("LVB_GPU_TAPER");
         c->taper = !(tp && atoi(tp) == 0);
         const char *slg = getenv("LVB_GPU_STREAM_LAG");
@@ -1125,6 +1157,7 @@ extern "C"
         cudaFree(c->d_done);
         cudaFree(c->d_lengths);
         cudaFree(c->d_nni);
+        cudaFree(c->d_trace);
         if (c->h_nni)
             cudaFreeHost(c->h_nni);
         if (c->h_err)
@@ -1563,6 +1596,7 @@ extern "C"
             p.pipe_pf = 0;
             p.stream_nt = 0;
             p.fuse_p2p = 0;
+            p.trace = nullptr;
             p.err = c->d_err;
             p.spin_limit = c->spin_limit;
             const size_t level_first[2] = {0, n_level0}, level_count[2] = {n_level0, n_pcs - n_level0};
@@ -1593,6 +1627,7 @@ extern "C"
         q.chg_low = c->chg + (int64_t)tree * c->I;
         q.chg_up = c->chg + (int64_t)scratch_tree * c->I;
         q.delta = c->d_nni;
+        q.one = 1u;
         if ((int64_t)E * n_cb > (int64_t)INT32_MAX)
             return fail("lvb_gpu_nni_neighbourhood: %lld CTAs", (long long)E * n_cb);
         int ev = -1;
@@ -1785,6 +1820,23 @@ extern "C"
     }
 
     int64_t lvb_gpu_launch_count(lvb_gpu_ctx *c) { return c ? c->launches : 0; }
+
+    int lvb_gpu_trace_download(lvb_gpu_ctx *c, uint64_t *out, int64_t cap_items, int64_t *n_items, int64_t *n_colblocks)
+    {
+        if (!c || !n_items)
+            return fail("lvb_gpu_trace_download: null argument");
+        *n_items = (int64_t)c->n_trace;
+        if (n_colblocks)
+            *n_colblocks = c->n_trace && c->last_n_prog ? (int64_t)(c->n_trace / c->last_n_prog) : 0;
+        if (!out || !c->n_trace)
+            return 0;
+        if (cap_items < (int64_t)c->n_trace)
+            return fail("lvb_gpu_trace_download: room for %lld items, have %zu", (long long)cap_items, c->n_trace);
+        CU(cudaSetDevice(c->device));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaMemcpy(out, c->d_trace, c->n_trace * 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        return 0;
+    }
 
     int lvb_gpu_set_timing(lvb_gpu_ctx *c, int on)
     {

@@ -264,6 +264,22 @@ class Engine:
     def score_batch(self, trees: Sequence[int], topos: Sequence[Topology]) -> np.ndarray:
         return self._batch(self.lib.lvb_gpu_score_batch, trees, topos)
 
+    def prepare_batch(self, trees: Sequence[int], topos: Sequence[Topology]):
+        """the C arrays of a batch (device tree numbers, lvb_gpu_topology records pointing into the arrays of
+        `topos`, which must stay alive): what a C caller holds anyway; score_prepared then times the C-ABI call
+        itself, not this binding"""
+        k = len(topos)
+        tarr = (C.c_int * k)(*[int(t) for t in trees])
+        sarr = (_Topo * k)()
+        for i, tp in enumerate(topos):
+            tp.fill(sarr[i])
+        return k, tarr, sarr, np.zeros(k, dtype=np.int64), list(topos)
+
+    def score_prepared(self, batch) -> np.ndarray:
+        k, tarr, sarr, out, _ = batch
+        _check(self.lib.lvb_gpu_score_batch(self.ctx, k, tarr, sarr, out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return out
+
     def score_batch_submit(self, trees: Sequence[int], topos: Sequence[Topology]):
         """enqueue a score batch; returns (ticket, n) for batch_wait"""
         k = len(topos)
