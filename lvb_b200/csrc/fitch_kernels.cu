@@ -990,7 +990,7 @@ static cudaError_t want_smem(K kernel, size_t smem)
  * Dependent pieces: the PRODUCER waits for the level below (piece_wait_children) before it
  * publishes a piece, the consumers never wait for anything but their operands. */
 #define LVB_SR 8       /* ring slots (power of two) */
-#define LVB_SCHUNK 128 /* instructions per staged chunk */
+#define LVB_SCHUNK 128 /* instructions per staged chunk (96, which lets a CTA with 4 stack slots fit 4 to an SM, measured no better) */
 
 struct StreamWork
 {
@@ -1729,52 +1729,28 @@ cudaError_t launch_apply_kept(const FitchInstr *instr, const FitchProgram *cand,
  * branch) and returns both length differences: 6 rows of traffic per PAIR of candidates, whatever
  * the depth of u.  The kernel is bound by integer issue, not by HBM (ncu: ALU pipe 86 %), so
  * reading low(u)/up(u) instead of recomputing fitch(A,B)/fitch(C,D) is a net gain. */
-/* The neighbourhood kernel is bound by the ALU pipe (LOP3 / SHF / IADD: 82 % busy, the FMA pipe a third of that), so
- * its additions go to the FMA pipe as multiply-adds: t * one + 0x7777... with `one` = 1 from the kernel parameters
- * (an immediate 1 would be folded back into an IADD). */
-__device__ __forceinline__ unsigned add7_fma(unsigned t, unsigned one)
-{
-    unsigned a;
-    asm("mad.lo.u32 %0, %1, %2, 0x77777777;" : "=r"(a) : "r"(t & 0x77777777u), "r"(one));
-    return a;
-}
-__device__ __forceinline__ unsigned fitch_lane_flags(unsigned x, unsigned y, unsigned one)
+/* (measured: sending the additions of these steps to the FMA pipe as t * one + 0x7777... with an opaque multiplier
+ * takes the kernel from 0.776 to 0.823 ms — the ALU pipe is 82 % busy, but the longer IMAD latency costs more) */
+__device__ __forceinline__ unsigned fitch_lane_flags(unsigned x, unsigned y)
 {
     const unsigned t = x & y;
-    const unsigned a = add7_fma(t, one);
+    const unsigned a = (t & 0x77777777u) + 0x77777777u;
     return ~(a | t) & 0x88888888u;
 }
-__device__ __forceinline__ unsigned fitch_lane_fma(unsigned x, unsigned y, unsigned &out, unsigned one)
-{
-    const unsigned t = x & y;
-    const unsigned a = add7_fma(t, one);
-    const unsigned e8 = ~(a | t) & 0x88888888u;
-    const unsigned s = e8 >> 3; /* 1 per site whose intersection is empty */
-    out = t | ((x | y) & (s * 15u));
-    return s;
-}
-__device__ __forceinline__ unsigned fitch_step_fma(const uint4 &x, const uint4 &y, uint4 &out, unsigned one)
-{
-    const unsigned s0 = fitch_lane_fma(x.x, y.x, out.x, one);
-    const unsigned s1 = fitch_lane_fma(x.y, y.y, out.y, one);
-    const unsigned s2 = fitch_lane_fma(x.z, y.z, out.z, one);
-    const unsigned s3 = fitch_lane_fma(x.w, y.w, out.w, one);
-    return s0 + 2u * s1 + 4u * s2 + 8u * s3;
-}
 /* number of sites of the column whose intersection is empty (no result row wanted) */
-__device__ __forceinline__ int fitch_count(const uint4 &x, const uint4 &y, unsigned one)
+__device__ __forceinline__ int fitch_count(const uint4 &x, const uint4 &y)
 {
-    const unsigned f = (fitch_lane_flags(x.x, y.x, one) >> 3) | (fitch_lane_flags(x.y, y.y, one) >> 2) |
-                       (fitch_lane_flags(x.z, y.z, one) >> 1) | fitch_lane_flags(x.w, y.w, one);
+    const unsigned f = (fitch_lane_flags(x.x, y.x) >> 3) | (fitch_lane_flags(x.y, y.y) >> 2) |
+                       (fitch_lane_flags(x.z, y.z) >> 1) | fitch_lane_flags(x.w, y.w);
     return __popc(f);
 }
-__device__ __forceinline__ int join_cost(const uint4 &p, const uint4 &q, const uint4 &r, const uint4 &s, unsigned one)
+__device__ __forceinline__ int join_cost(const uint4 &p, const uint4 &q, const uint4 &r, const uint4 &s)
 {
     /* ((p,q),(r,s)) evaluated on its middle branch */
     uint4 pq, rs;
-    int c = __popc(fitch_step_fma(p, q, pq, one));
-    c += __popc(fitch_step_fma(r, s, rs, one));
-    return c + fitch_count(pq, rs, one);
+    int c = __popc(fitch_step(p, q, pq));
+    c += __popc(fitch_step(r, s, rs));
+    return c + fitch_count(pq, rs);
 }
 
 __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams p)
@@ -1804,9 +1780,9 @@ __global__ void __launch_bounds__(256) nni_neighbourhood_kernel(const NniParams 
         /* the current tree on this branch costs changes(A,B) + changes(C,D) + changes(low(u), up(u)):
          * the first two are the cached counts of u in the two trees (subtracted once per branch
          * below), both sets are rows already — only the third term is computed here */
-        const int cur = fitch_count(LU, UU, p.one);
-        d0 = join_cost(A, C, B, D, p.one) - cur;
-        d1 = join_cost(B, C, A, D, p.one) - cur;
+        const int cur = fitch_count(LU, UU);
+        d0 = join_cost(A, C, B, D) - cur;
+        d1 = join_cost(B, C, A, D) - cur;
     }
     d0 = __reduce_add_sync(0xffffffffu, d0);
     d1 = __reduce_add_sync(0xffffffffu, d1);

@@ -161,7 +161,6 @@ struct NniParams
     const int32_t *chg_low; /* [n_edges] cached counts of u in the evaluated tree = changes(A,B) over all columns */
     const int32_t *chg_up;  /* [n_edges] the same in the scratch tree (left by the up-pass) = changes(C,D) */
     long long *delta;       /* [2 * n_edges] */
-    unsigned one;           /* = 1: a multiplier the compiler cannot fold (additions as IMAD on the FMA pipe) */
 };
 cudaError_t launch_nni_neighbourhood(const NniParams &p, int block, cudaStream_t stream);
 

@@ -1627,7 +1627,6 @@ extern "C"
         q.chg_low = c->chg + (int64_t)tree * c->I;
         q.chg_up = c->chg + (int64_t)scratch_tree * c->I;
         q.delta = c->d_nni;
-        q.one = 1u;
         if ((int64_t)E * n_cb > (int64_t)INT32_MAX)
             return fail("lvb_gpu_nni_neighbourhood: %lld CTAs", (long long)E * n_cb);
         int ev = -1;
