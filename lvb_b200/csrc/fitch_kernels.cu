@@ -876,6 +876,174 @@ __device__ __forceinline__ void fitch_score_body(const ExecParams &p, const Fitc
     }
 }
 
+/* ---- score mode, large batches, TWO columns per thread ---------------------------------------
+ * A launch of hundreds of candidates of one tree is bound by instruction issue, not by HBM (ncu, 512 NNI
+ * candidates of a 2000 x 1M tree: issue slots 75 %, ALU pipe 73 %, DRAM 15 % — four fifths of the operand
+ * sectors hit L2): of the 70 SASS instructions of a node step only 33 are the Fitch arithmetic of a 16-byte
+ * column, the rest fetches and decodes the instruction, forms addresses, issues and awaits the copies.  Here a
+ * thread owns two columns (tid and tid + blockDim of its column block of 2 x blockDim columns), so that the
+ * per-step overhead is paid once per 32 bytes.  Same ring, same look-ahead as fitch_score_body<false, LVB_PF>. */
+__device__ __forceinline__ void fitch_score2_body(const ExecParams &p, const FitchProgram *progs, const FitchInstr *instrs)
+{
+    constexpr int PF = LVB_PF, RING = LVB_RING;
+    extern __shared__ uint4 smem_u4[];
+    uint4 *s_instr = smem_u4; /* LVB_CHUNK + 2 * RING decoded instructions */
+    const int tid = threadIdx.x;
+    const int nthr = blockDim.x;
+    uint4 *s_ring = smem_u4 + LVB_CHUNK + 2 * RING; /* [RING][2 operands][2 columns][nthr] */
+    uint4 *s_stack = s_ring + RING * 4 * nthr;      /* [n_slots][2 columns][nthr] */
+    __shared__ unsigned long long s_total;
+
+    const int prog_id = blockIdx.x % p.n_prog; /* column-block-major, see fitch_score_body */
+    const int cb = blockIdx.x / p.n_prog;
+    const FitchProgram prog = progs[prog_id];
+    const int col0 = cb * 2 * nthr + tid, col1 = col0 + nthr;
+    const unsigned amask0 = col0 < p.ncols ? ~0u : 0u, amask1 = col1 < p.ncols ? ~0u : 0u;
+    const FitchInstr *gi = instrs + prog.instr_begin;
+    const unsigned long long colbase0 = reinterpret_cast<unsigned long long>(p.pool + min(col0, p.ncols - 1));
+    const unsigned long long colbase1 = reinterpret_cast<unsigned long long>(p.pool + min(col1, p.ncols - 1));
+    const unsigned stride_b = (unsigned)p.stride_u4 * 16u;
+    const unsigned half = (unsigned)nthr * 16u; /* one column set of one operand */
+    const unsigned slot_bytes = 2u * half;      /* one operand / one stack slot: both column sets */
+    const unsigned sa_instr = (unsigned)__cvta_generic_to_shared(s_instr);
+    const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
+    const unsigned sa_stack = (unsigned)__cvta_generic_to_shared(s_stack + tid);
+
+    if (tid == 0)
+        s_total = 0ull;
+    uint4 acc0 = make_uint4(~0u, ~0u, ~0u, ~0u), acc1 = acc0;
+    unsigned total = 0;
+
+    for (int base = 0; base < prog.n_instr; base += LVB_CHUNK)
+    {
+        const int m = min(LVB_CHUNK, prog.n_instr - base);
+        const int m_pad = (m + RING - 1) / RING * RING;
+        __syncthreads();
+        for (int i = tid; i < m_pad + RING; i += nthr)
+        {
+            uint4 d = make_uint4(0u, 0u, 0u, D_APREV | D_NOP); /* padding: no loads, no arithmetic */
+            if (i < m)
+            {
+                const FitchInstr in = gi[base + i];
+                int a = in.a, b = in.b;
+                if (LVB_OPER_IS_SLOT(a) || b == LVB_OPER_PREV)
+                {
+                    const int t = a;
+                    a = b;
+                    b = t;
+                }
+                unsigned w = 0u;
+                const unsigned push = (in.ctl & LVB_CTL_PUSH_MASK) >> LVB_CTL_PUSH_SHIFT;
+                if (push)
+                    w |= D_PUSH | ((push - 1u) * slot_bytes);
+                if (a < 0)
+                {
+                    w |= D_APREV;
+                    a = 0;
+                }
+                if (b < 0)
+                {
+                    w |= D_BSLOT;
+                    b = LVB_OPER_SLOT_INDEX(b) * (int)slot_bytes;
+                }
+                d = make_uint4((unsigned)a, (unsigned)b, 0u, w);
+            }
+            s_instr[i] = d;
+        }
+        __syncthreads();
+
+#define LVB_ISSUE2(J, S)                                                                                              \
+    {                                                                                                                 \
+        const uint4 ni = lds128(sa_instr + (unsigned)(J) * 16u);                                                      \
+        const unsigned pa = !(ni.w & D_APREV), pb = !(ni.w & (D_BSLOT | D_NOP));                                      \
+        cp_async16_if(sa_ring + (2u * (S)) * slot_bytes, row_addr(ni.x, stride_b, colbase0), pa);                     \
+        cp_async16_if(sa_ring + (2u * (S)) * slot_bytes + half, row_addr(ni.x, stride_b, colbase1), pa);              \
+        cp_async16_if(sa_ring + (2u * (S) + 1u) * slot_bytes, row_addr(ni.y, stride_b, colbase0), pb);                \
+        cp_async16_if(sa_ring + (2u * (S) + 1u) * slot_bytes + half, row_addr(ni.y, stride_b, colbase1), pb);         \
+        cp_async_commit();                                                                                            \
+    }
+#define LVB_SCORE2_STEP(J, S)                                                                                         \
+    {                                                                                                                 \
+        cp_async_wait<PF - 1>(); /* this thread's operands of instruction J have landed */                        \
+        const uint4 ci = lds128(sa_instr + (unsigned)(J) * 16u);                                                      \
+        lds128_if(acc0, sa_ring + (2u * (S)) * slot_bytes, !(ci.w & D_APREV));                                        \
+        lds128_if(acc1, sa_ring + (2u * (S)) * slot_bytes + half, !(ci.w & D_APREV));                                 \
+        const unsigned ya = (ci.w & D_BSLOT) ? sa_stack + ci.y : sa_ring + (2u * (S) + 1u) * slot_bytes;              \
+        const uint4 y0 = lds128(ya), y1 = lds128(ya + half);                                                          \
+        LVB_ISSUE2((J) + PF, ((S) + PF) % RING) /* refills the slot read one step ago */                              \
+        if (!(ci.w & D_NOP))                                                                                          \
+        {                                                                                                             \
+            const unsigned f0 = fitch_step(acc0, y0, acc0) & amask0;                                                  \
+            const unsigned f1 = fitch_step(acc1, y1, acc1) & amask1;                                                  \
+            total += __popc(f0) + __popc(f1);                                                                         \
+            const unsigned pa = sa_stack + (ci.w & 0x0ffffff0u);                                                      \
+            sts128_if(pa, acc0, ci.w & D_PUSH);                                                                       \
+            sts128_if(pa + half, acc1, ci.w & D_PUSH);                                                                \
+        }                                                                                                             \
+    }
+
+#pragma unroll
+        for (int s = 0; s < PF; s++)
+            LVB_ISSUE2(s, s)
+        for (int i = 0; i < m_pad; i += RING)
+        {
+#pragma unroll
+            for (int s = 0; s < RING; s++)
+                LVB_SCORE2_STEP(i + s, s)
+        }
+        cp_async_wait<0>();
+#undef LVB_SCORE2_STEP
+#undef LVB_ISSUE2
+    }
+
+    /* per-program length: block reduce, one 64-bit atomic per CTA (as fitch_score_body) */
+    const unsigned w = __reduce_add_sync(0xffffffffu, total);
+    if ((tid & 31) == 0 && w)
+        atomicAdd(&s_total, (unsigned long long)w);
+    __syncthreads();
+    if (cb == 0)
+    {
+        long long basev = 0;
+        const int32_t *chg = p.chg + (int64_t)prog.tree * p.n_internal;
+        for (int i = tid; i < prog.n_instr; i += nthr)
+        {
+            const int node = gi[i].node;
+            if (node >= 0)
+                basev -= chg[node - p.n];
+        }
+        for (int o = 16; o > 0; o >>= 1)
+            basev += __shfl_xor_sync(0xffffffffu, basev, o);
+        if ((tid & 31) == 0 && basev)
+            atomicAdd(&s_total, (unsigned long long)basev);
+        __syncthreads();
+        if (tid == 0)
+            s_total += (unsigned long long)p.sum_chg[prog.tree];
+    }
+    if (p.n_colblocks == 1)
+    {
+        if (tid == 0)
+            p.out[prog_id] = (long long)s_total;
+        return;
+    }
+    if (tid == 0)
+    {
+        if (s_total)
+            atomicAdd(&p.totals[prog_id], s_total);
+        __threadfence();
+        if (atomicAdd(&p.done[prog_id], 1u) == (unsigned)p.n_colblocks - 1u)
+        {
+            __threadfence();
+            p.out[prog_id] = (long long)atomicExch(&p.totals[prog_id], 0ull);
+            p.done[prog_id] = 0u;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) fitch_score2_kernel(const ExecParams p)
+{
+    fitch_score2_body(p, p.prog, p.instr);
+}
+
 __global__ void __launch_bounds__(256) fitch_score_kernel(const ExecParams p)
 {
     fitch_score_body<false, LVB_PF>(p, p.prog, p.instr);
@@ -924,6 +1092,15 @@ static bool deep_enabled()
 {
     static const int on = [] {
         const char *e = getenv("LVB_GPU_DEEP");
+        return (e && atoi(e) == 0) ? 0 : 1;
+    }();
+    return on != 0;
+}
+/* large score launches: two columns per thread (LVB_GPU_SCORE2=0: the one-column kernel, for A/B runs) */
+static bool score2_enabled()
+{
+    static const int on = [] {
+        const char *e = getenv("LVB_GPU_SCORE2");
         return (e && atoi(e) == 0) ? 0 : 1;
     }();
     return on != 0;
@@ -1525,6 +1702,15 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
         if ((e = want_smem(fitch_pipe_kernel<false>, sm)) != cudaSuccess)
             return e;
         fitch_pipe_kernel<false><<<grid, block, sm, stream>>>(p);
+    }
+    else if (score2_enabled() && (long long)p.n_prog * ((p.ncols + 2 * block - 1) / (2 * block)) >= 4ll * 148 * 6)
+    { /* many candidates: two columns per thread (issue-bound regime); the column blocks are twice as wide */
+        ExecParams q = p;
+        q.n_colblocks = (p.ncols + 2 * block - 1) / (2 * block);
+        const size_t sm = (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(4 * LVB_RING + 2 * p.n_slots) * block) * sizeof(uint4);
+        if ((e = want_smem(fitch_score2_kernel, sm)) != cudaSuccess)
+            return e;
+        fitch_score2_kernel<<<(unsigned)q.n_prog * (unsigned)q.n_colblocks, block, sm, stream>>>(q);
     }
     else
     {

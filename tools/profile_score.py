@@ -20,6 +20,18 @@ cands, idx = bench.nni_candidates(left, right, root, n, 512, seed=5)
 for _ in range(2):
     lens = eng.score_batch([t] * 512, cands)
 print("score 512:", int(lens[0]), eng.last_kernel_ms())
+import time
+prep = eng.prepare_batch([t] * 512, cands)
+eng.score_prepared(prep)
+for label in ("no torch", "torch imported"):
+    t0 = time.perf_counter()
+    for _ in range(10):
+        eng.score_prepared(prep)
+    print(f"C-ABI call, 512 candidates, {label}: {(time.perf_counter() - t0) / 10 * 1e3:.3f} ms per call (kernel {eng.last_kernel_ms():.3f} ms)")
+    if label == "no torch" and os.environ.get("WITH_TORCH"):
+        import torch  # noqa: F401
+    elif label == "no torch":
+        break
 print("score 4:", eng.score_batch([t] * 4, cands[:4]).tolist(), eng.last_kernel_ms())
 print("commit of one candidate:", eng.commit(t, cands[0]), eng.last_kernel_ms())
 nn = eng.nni_neighbourhood(t, s, Topology(cands[0].left, cands[0].right, root))
