@@ -344,12 +344,13 @@ static int pick_block(const lvb_gpu_ctx *c)
 }
 
 /* consumer threads per CTA of the streaming kernel: 256 (4 KB operand segments) for wide rows, 128 when that would
- * leave under 32 column blocks — the word blocks of an 8-GPU run of 2000 x 1M: 0.0705 ms against 0.0733 per pass */
+ * leave under 16 column blocks — the word blocks of an 8-GPU run of 2000 x 1M: 0.0705 ms against 0.0733 per pass; at
+ * a quarter of that width (31 column blocks of 256) 256 is still the better one: 0.1185 against 0.128 ms */
 static int stream_threads(const lvb_gpu_ctx *c)
 {
     if (c->stream_nt >= 0)
         return c->stream_nt;
-    return c->stride_u4 >= 8192 ? 256 : 128;
+    return c->stride_u4 >= 4096 ? 256 : 128;
 }
 
 /* column-block width of a store launch of dependent pieces: the streaming kernel has its own */

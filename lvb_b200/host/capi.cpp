@@ -217,7 +217,8 @@ void lvbh_tree_set(void *hv, void *tv, const long *parent, const long *left, con
     ss_init(&((Handle *)hv)->msa, t);
 }
 
-/* the same sequence of tree-stack pushes as ref_treestack_sequence of oracle/ref_shim.cpp */
+/* a sequence of pushes into one fresh tree stack: results[i] = what the push of trees[i] returned (1 = new, 0 = a
+ * duplicate); returns the final size.  The tests run the same sequence through the reference. */
 long lvbh_treestack_sequence(void *hv, long count, void *const *trees, const long *roots, int hash, long *results)
 {
     Handle *h = (Handle *)hv;
