@@ -247,7 +247,11 @@ def nni_candidates(left, right, root, n, count, seed):
         while w != root:
             dirty.append(w)
             w = int(parent[w])
-        out.append(Topology(l2, r2, root, dirty))
+        # the candidate as LVB's operators leave it for the device layer: the current tree's arrays plus the two
+        # nodes whose links the rearrangement rewired (lvb_gpu_topology::mod_*), not a private copy of 2 x 32 kB
+        cand = Topology(left, right, root, dirty, overlay=([u, v], [l2[u], l2[v]], [r2[u], r2[v]]))
+        cand.full = (l2, r2)
+        out.append(cand)
         index.append(2 * (u - n) + (1 if swap_a else 0))
     return out, index
 

@@ -176,6 +176,7 @@ struct lvb_gpu_ctx
     int stream_lag = -1;                               /* LVB_GPU_STREAM_LAG: column-block lag between levels (-1 = automatic) */
     long long *d_nni = nullptr, *h_nni = nullptr;      /* [cap_nni] length differences of an NNI neighbourhood */
     size_t cap_nni = 0;
+    int64_t compile_par_work = 32768; /* ... and with at least this many dirty nodes in all */
     int compile_par_min = 8;  /* host compile: batches of >= min candidates are spread over
                                                         * OpenMP threads, >= grain candidates each */
     bool inline_ok = true;   /* small batches travel inside the kernel parameters (LVB_GPU_INLINE=0: always staged) */
@@ -696,11 +697,16 @@ static int run_batch(lvb_gpu_ctx *c, int64_t K, const int *trees, const lvb_gpu_
 #ifdef _OPENMP
     /* always the caller's whole team: libgomp re-creates threads when consecutive parallel regions
      * of one thread differ in size (measured: 3x slower rounds with teams alternating 8 / 16) */
-    int64_t to_compile = K;
-    if (pre)
-        for (int64_t k = 0; k < K; k++)
-            to_compile -= pre[k].instr ? 1 : 0;
-    if (to_compile >= c->compile_par_min)
+    /* ... and only when there is enough to compile: a dirty node costs ~40 ns, waking a sleeping team 0.1-0.6 ms
+     * (512 NNI candidates of a 2000-taxon tree: 0.26 ms on one thread) */
+    int64_t to_compile = 0, work = 0;
+    for (int64_t k = 0; k < K; k++)
+        if (!(pre && pre[k].instr))
+        {
+            to_compile++;
+            work += topos[k].n_dirty < 0 ? c->I : topos[k].n_dirty;
+        }
+    if (to_compile >= c->compile_par_min && work >= c->compile_par_work)
         nthreads = std::min<int>((int)c->sc.size(), omp_get_max_threads());
 #endif
     bool bad = false;

@@ -611,3 +611,70 @@ def test_score_keep_and_accept(monkeypatch, env):
                 eng.tree_destroy(spare)
     finally:
         eng.close()
+
+
+def test_keep_and_accept_errors_are_loud(golden_dir):
+    """misuse of the score-and-keep calls fails with a message, and the tree is as it was"""
+    g = load(golden_dir, "example.npz")
+    enc = g["enc"]
+    n = enc.shape[0]
+    eng = Engine(0)
+    try:
+        eng.upload(enc, max_trees=2)
+        t = eng.tree_create()
+        left, right, root = g["random_left"], g["random_right"], int(g["random_root"])
+        base = Topology(left, right, root)
+        cand = Topology(g["nni_left"], g["nni_right"], int(g["nni_root"]), np.nonzero(g["nni_dirty"])[0])
+        with pytest.raises(GpuError, match="never been evaluated"):
+            eng.score_keep([t], [cand], [1])
+        assert eng.commit(t, base) == 11808
+        with pytest.raises(GpuError, match="two kept candidates"):
+            eng.score_keep([t, t], [cand, cand], [1, 1])
+        lens, ticket = eng.score_keep([t, t], [cand, cand], [0, 1])
+        assert lens.tolist() == [11834, 11834]
+        with pytest.raises(GpuError, match="was not kept"):
+            eng.accept_kept(ticket, [0])
+        with pytest.raises(GpuError, match="was not kept"):
+            eng.accept_kept(ticket, [7])
+        plain = eng.score_batch_submit([t], [cand])
+        assert eng.batch_wait(plain).tolist() == [11834]
+        with pytest.raises(GpuError, match="does not name a batch"):
+            eng.accept_kept(plain[0], [0])
+        assert eng.score_batch([t], [Topology(left, right, root, [])]).tolist() == [11808]  # nothing has changed
+        eng.accept_kept(ticket, [1])
+        with pytest.raises(GpuError, match="accepted already"):
+            eng.accept_kept(ticket, [1])
+        assert eng.score_batch([t], [Topology(g["nni_left"], g["nni_right"], int(g["nni_root"]), [])]).tolist() == [11834]
+        want, rows, chg = oracles.oracle_getplen(enc, g["nni_left"], g["nni_right"], int(g["nni_root"]))
+        assert np.array_equal(eng.changes(t)[n:], chg[n:])
+    finally:
+        eng.close()
+
+
+def test_trace_of_a_store_launch(monkeypatch):
+    """LVB_GPU_TRACE=1 (the measuring aid behind tools/trace_store.py): every work item of a whole-tree store launch
+    leaves six increasing time stamps, and the result of the launch is the oracle's"""
+    import ctypes as C
+
+    from lvb_b200 import load_library
+    monkeypatch.setenv("LVB_GPU_TRACE", "1")
+    n, m = 400, 60_000
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=4, p=0.1))
+    left, right, root = synthetic.random_topology(n, seed=4)
+    eng = Engine(0)
+    try:
+        eng.upload(enc, max_trees=1)
+        t = eng.tree_create()
+        assert eng.commit(t, Topology(left, right, root)) == oracles.oracle_getplen(enc, left, right, root)[0]
+        lib = load_library()
+        lib.lvb_gpu_trace_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        ni, ncb = C.c_int64(0), C.c_int64(0)
+        assert lib.lvb_gpu_trace_download(eng.ctx, None, 0, C.byref(ni), C.byref(ncb)) == 0
+        assert ni.value > 0 and ncb.value > 0 and ni.value % ncb.value == 0
+        tr = np.zeros((ni.value, 6), dtype=np.uint64)
+        assert lib.lvb_gpu_trace_download(eng.ctx, tr.ctypes.data, ni.value, C.byref(ni), C.byref(ncb)) == 0
+        assert (tr > 0).all()
+        d = np.diff(tr.astype(np.int64), axis=1)
+        assert (d[:, [0, 1, 3, 4]] >= 0).all()  # ticket <= decoded <= published; first operand <= last step <= books
+    finally:
+        eng.close()

@@ -34,6 +34,6 @@ for label in ("no torch", "torch imported"):
         break
 print("score 4:", eng.score_batch([t] * 4, cands[:4]).tolist(), eng.last_kernel_ms())
 print("commit of one candidate:", eng.commit(t, cands[0]), eng.last_kernel_ms())
-nn = eng.nni_neighbourhood(t, s, Topology(cands[0].left, cands[0].right, root))
+nn = eng.nni_neighbourhood(t, s, Topology(cands[0].full[0], cands[0].full[1], root))
 print("nni:", int(nn[0]), eng.last_kernel_ms())
 eng.close()
