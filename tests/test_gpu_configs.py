@@ -131,7 +131,8 @@ def _site_block_reference(enc, left, right, root, cands):
     want, _, chg = oracles.oracle_getplen(enc, left, right, root)
     lens = []
     for c in cands:
-        lens.append(oracles.oracle_getplen(enc, c.left, c.right, c.root)[0])
+        l2, r2 = getattr(c, "full", (c.left, c.right))  # bench.nni_candidates: overlays on the current tree's arrays
+        lens.append(oracles.oracle_getplen(enc, l2, r2, c.root)[0])
     return want, chg, lens
 
 
