@@ -566,16 +566,17 @@ def main():
             got = eng.score_batch(trees, cands)
             prepared = eng.prepare_batch(trees, cands)  # the C arrays a C caller holds anyway
             eng.score_prepared(prepared)
-            t0 = time.perf_counter()
-            reps_c = 5
+            reps_c, calls = 9, []
             for _ in range(reps_c):
+                t0 = time.perf_counter()
                 got = eng.score_prepared(prepared).copy()
-            wall_c = time.perf_counter() - t0
+                calls.append(time.perf_counter() - t0)
+            wall_c = float(np.median(calls)) * reps_c  # per-call median: one host hiccup in nine calls is not the engine
             t0 = time.perf_counter()
             eng.score_batch(trees, cands)
             wall_py = time.perf_counter() - t0
             eng.kernel_time(reset=True)
-            for _ in range(reps_c):
+            for _ in range(3):
                 eng.rerun_last_batch()
             eng.synchronize()
             c_ms, c_launch = eng.kernel_time()
@@ -591,6 +592,7 @@ def main():
                 "e2e": reps_c * len(cands) / wall_c, "device": len(cands) / (score_ms * 1e-3),
                 "batch": len(cands), "mean_dirty_nodes": dirty_mean,
                 "e2e_through_python_binding": len(cands) / wall_py,
+                "e2e_ms_per_call": {"median": float(np.median(calls)) * 1e3, "min": min(calls) * 1e3, "max": max(calls) * 1e3},
                 "api": "lvb_gpu_score_batch: NNI candidates of the current tree, one launch per batch; e2e = the C-ABI call "
                        "with host topology arrays (schedule compile on the host threads, H2D of the programs, kernel, lengths "
                        "back), the lvb_gpu_topology records prepared once; e2e_through_python_binding adds building those "
