@@ -1382,12 +1382,19 @@ __global__ void __launch_bounds__(320) fitch_stream_kernel(const ExecParams p)
         const unsigned sa_ring = (unsigned)__cvta_generic_to_shared(s_ring);
         unsigned jl = 0; /* loads issued */
         unsigned q = 0;  /* chunks published */
+        bool first_item = true;
         for (;;)
         {
-            unsigned vb = 0;
-            if (lane == 0)
-                vb = atomicAdd(p.ticket, 1u);
-            vb = __shfl_sync(0xffffffffu, vb, 0);
+            /* the first item of a CTA is its own number (no round trip to the counter before the first load is
+             * issued); the counter hands out the items from gridDim.x on */
+            unsigned vb = blockIdx.x;
+            if (!first_item)
+            {
+                if (lane == 0)
+                    vb = atomicAdd(p.ticket, 1u) + gridDim.x;
+                vb = __shfl_sync(0xffffffffu, vb, 0);
+            }
+            first_item = false;
             bool stop = vb >= total;
             if (p.trace && lane == 0 && !stop)
                 p.trace[6 * (size_t)vb + 0] = global_ns();

@@ -172,7 +172,7 @@ struct lvb_gpu_ctx
     unsigned last_level_count[LVB_DEP_LEVELS] = {};    /* pieces per level of the resident batch that count themselves in */
     unsigned last_level_pieces[LVB_DEP_LEVELS] = {};   /* pieces per level of the resident batch */
     int sm_count = 148;
-    bool taper = true;                                 /* level-0 bins get smaller towards the end (LVB_GPU_TAPER=0: equal bins) */
+    int taper = 1;                                     /* level-0 bins get smaller towards the end (LVB_GPU_TAPER=0: equal bins) */
     int stream_lag = -1;                               /* LVB_GPU_STREAM_LAG: column-block lag between levels (-1 = automatic) */
     long long *d_nni = nullptr, *h_nni = nullptr;      /* [cap_nni] length differences of an NNI neighbourhood */
     size_t cap_nni = 0;
@@ -1109,7 +1109,7 @@ extern "C"
         const char *tr = getenv("LVB_GPU_TRACE");
         c->trace = tr && atoi(tr) != 0;
         const char *tp = getenv("LVB_GPU_TAPER");
-        c->taper = !(tp && atoi(tp) == 0);
+        c->taper = tp ? std::max(0, std::min(2, atoi(tp))) : 1;
         const char *slg = getenv("LVB_GPU_STREAM_LAG");
         if (slg)
             c->stream_lag = atoi(slg);

@@ -310,7 +310,7 @@ bool ScheduleCompiler::compile_impl(const lvb_gpu_topology &topo, bool store, st
                             n_bins++;
                             load = 0;
                             const int64_t left = total - filled;
-                            cap = left * 4 > total ? S : left * 8 > total ? S / 2 : left * 16 > total ? S / 4 : S / 8;
+                            cap = left * 4 > total ? S : left * 8 > total ? S / 2 : left * 16 > total ? S / 4 : (taper_ < 2 || left * 32 > total) ? S / 8 : S / 16;
                             cap = std::max<int64_t>(cap, 4);
                         }
                         klevel_[k] = (int32_t)n_bins; /* for now: the bin */

@@ -48,8 +48,8 @@ class ScheduleCompiler
 
     int64_t n() const { return n_; }
 
-    /* level-0 bins of equal size instead of bins that get smaller towards the end (A/B switch) */
-    void set_taper(bool on) { taper_ = on; }
+    /* level-0 bins: equal (0) or smaller towards the end, down to 1/8 (1) or 1/16 (2) of the full size (A/B switch) */
+    void set_taper(int depth) { taper_ = depth; }
 
     /* The up-pass of a whole tree: one store instruction per internal node v computing
      * up(v) = the Fitch set of everything that is NOT below v (the tree seen from v's parent
@@ -78,7 +78,7 @@ class ScheduleCompiler
     };
     bool is_dirty(int64_t v) const { return v >= n_ && v < B_ && stamp_[v] == cur_; }
     int64_t n_, B_;
-    bool taper_ = true;
+    int taper_ = 1; /* 0: equal bins; 1: bins down to an eighth; 2: down to a sixteenth (for the last 1/32 of the work) */
     uint32_t cur_;
     /* indexed by node */
     std::vector<uint32_t> stamp_;   /* dirty marks */
