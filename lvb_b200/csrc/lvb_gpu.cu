@@ -196,8 +196,6 @@ struct lvb_gpu_ctx
     int fault_dep = 0;                                 /* LVB_GPU_FAULT=dep: the next dependent launch gets a wait that
                                                         * can never be satisfied (test of the bounded wait) */
     bool last_dep = false;
-    std::vector<int32_t> owner_stamp, owner_piece;     /* (tree, node) -> piece that stores it in the current batch */
-    int32_t owner_cur = 0;
     int32_t *d_cnts = nullptr;                         /* [cap_cnts] per-instruction counts; zero between batches */
     size_t cap_cnts = 0;
     int block_override = 0;

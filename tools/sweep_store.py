@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--block", default="256,128")
     ap.add_argument("--shards", default="1,8")
     ap.add_argument("--taper", default="1", help="LVB_GPU_TAPER values")
+    ap.add_argument("--piece-min", default="64", help="LVB_GPU_PIECE_MIN values")
     ap.add_argument("--lag", default="-1", help="LVB_GPU_STREAM_LAG values (-1 = automatic)")
     ap.add_argument("--stream", default="0", help="LVB_GPU_STORE_STREAM values (consumer threads of the TMA streaming kernel; 0 = the other kernels)")
     args = ap.parse_args()
@@ -53,9 +54,10 @@ def main():
                 grid += [(st, lg, tw, "256") for lg in args.lag.split(",") for tw in args.warps.split(",")]
             else:
                 grid += [(st, pf, tw, blk) for pf, tw, blk in itertools.product(args.pf.split(","), args.warps.split(","), args.block.split(","))]
-        grid = [(st, pf, tw, blk, tp) for tp in args.taper.split(",") for st, pf, tw, blk in grid]
-        for st, pf, tw, blk, tp in grid:
+        grid = [(st, pf, tw, blk, tp, pm) for pm in args.piece_min.split(",") for tp in args.taper.split(",") for st, pf, tw, blk in grid]
+        for st, pf, tw, blk, tp, pm in grid:
             os.environ["LVB_GPU_TAPER"] = tp
+            os.environ["LVB_GPU_PIECE_MIN"] = pm
             os.environ["LVB_GPU_STORE_STREAM"] = st
             os.environ["LVB_GPU_STORE_PF"] = pf if int(st) == 0 else "0"
             os.environ["LVB_GPU_STREAM_LAG"] = pf if int(st) > 0 else "-1"
@@ -81,7 +83,7 @@ def main():
                 k_ms, k_n = eng.kernel_time()
                 key = shards
                 want.setdefault(key, length)
-                print(json.dumps({"shards": shards, "words": wc, "stream": int(st), "taper": int(tp), "pf_or_lag": int(pf), "target_warps_per_sm": int(tw),
+                print(json.dumps({"shards": shards, "words": wc, "stream": int(st), "taper": int(tp), "piece_min": int(pm), "pf_or_lag": int(pf), "target_warps_per_sm": int(tw),
                                   "block": int(blk), "kernel_ms": round(k_ms / max(1, k_n), 4),
                                   "stream_ms": round(e0.elapsed_time(e1) / args.reps, 4),
                                   "launches_per_pass": (eng.launches - l0) / args.reps, "length": int(length),
