@@ -94,6 +94,21 @@ int lvb_gpu_matrix_clone(lvb_gpu_ctx *ctx, lvb_gpu_ctx *src, int64_t max_trees);
 int lvb_gpu_column_stats(lvb_gpu_ctx *ctx, int64_t n, int64_t m, const char *const *rows, unsigned char *keep,
                          int64_t *n_variable, int64_t *min_len_all, int64_t *min_len_variable);
 
+/* ---- the same statistics for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that
+ * forbid cudaMalloc.  This call allocates nothing (no cudaMalloc / cudaFree / allocating library routine):
+ * d_text (n x m characters, row-major), d_keep (m bytes, may be NULL) and d_out3 (3 x int64: variable columns,
+ * MinimumTreeLength over all columns, over the variable columns) are the CALLER's device memory on the
+ * context's device; the scratch of the reduction is a fixed array inside the library (393,472 bytes, held by
+ * every GPU that loads the library until the process exits).  Limit: m <= LVB_GPU_NOALLOC_MAX_COLUMNS, more is
+ * refused with an error.  The kernel is enqueued on the context's stream (lvb_gpu_stream) and the call returns
+ * without waiting: read d_out3 / d_keep after lvb_gpu_synchronize or in stream order.  All calls on one GPU
+ * share the scratch array: calls that overlap on the GPU (contexts on different streams) race — serialise them.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress); make it before a capture. */
+#define LVB_GPU_NOALLOC_MAX_COLUMNS 4194304
+int lvb_gpu_column_stats_noalloc(lvb_gpu_ctx *ctx, int64_t n, int64_t m, const unsigned char *d_text,
+                                 unsigned char *d_keep, int64_t *d_out3);
+
 /* ---- trees: device-resident state rows + cached per-node change counts of one
  * search chain's current tree (what treealloc gives Anneal, TreeOperations.c:914-955;
  * Solve.c:194-197).  A new tree has every internal node dirty. ---- */

@@ -2151,6 +2151,145 @@ cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m,
     return cudaGetLastError();
 }
 
+/* ---- column statistics without any allocation (lvb_gpu_column_stats_noalloc) -------------------------
+ * The same statistics as column_stats_kernel for callers that must not allocate (code under CUDA graph
+ * capture, serving loops, harnesses that forbid cudaMalloc): text, keep and the three results are the
+ * CALLER's device memory, and the scratch the reduction needs — three partial sums per CTA and the ticket that
+ * tells the last CTA to add them up — lives in this file-scope array instead of a cudaMalloc'd buffer.
+ * Every GPU that loads the library holds the array (LVB_NOALLOC_SCRATCH_BYTES = 393,472 bytes) until exit.
+ * All calls on a device share it: calls that overlap on the GPU (different streams) race; it keeps the last
+ * call's contents, so the ticket is cleared on the stream before every launch (and left zero by the kernel).
+ * In host code g_noalloc_scratch is only a stand-in for the symbol, not a device address: the launcher takes
+ * the address with cudaGetSymbolAddress once per device, with that device current. */
+#define LVB_NOALLOC_BLOCK 256
+#define LVB_NOALLOC_MAX_BLOCKS (LVB_NOALLOC_MAX_COLUMNS / LVB_NOALLOC_BLOCK)
+#define LVB_NOALLOC_HEAD 32 /* long longs in front of the partial sums: [0] the ticket */
+#define LVB_NOALLOC_SCRATCH_WORDS (LVB_NOALLOC_HEAD + 3 * LVB_NOALLOC_MAX_BLOCKS)
+static __device__ __align__(256) long long g_noalloc_scratch[LVB_NOALLOC_SCRATCH_WORDS];
+
+/* one column: what column_stats_kernel computes per thread (DataOperations.c:272-307, 53-105) */
+__device__ __forceinline__ void column_stats_of(const unsigned char *text, int64_t n, int64_t m, int64_t k,
+                                                unsigned char *keep, long long &kept, long long &all, long long &of_kept)
+{
+    unsigned mask[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}; /* one bit per byte value */
+    const unsigned char *p = text + k;
+    for (int64_t i = 0; i < n; i++, p += m)
+    {
+        const unsigned c = *p;
+#pragma unroll
+        for (int w = 0; w < 8; w++)
+            mask[w] |= (c >> 5) == (unsigned)w ? 1u << (c & 31u) : 0u;
+    }
+    int present = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+        present += __popc(mask[w]);
+    mask['-' >> 5] &= ~(1u << ('-' & 31));
+    mask['?' >> 5] &= ~(1u << ('?' & 31));
+    mask['N' >> 5] &= ~(1u << ('N' & 31));
+    mask['X' >> 5] &= ~(1u << ('X' & 31));
+    int states = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+        states += __popc(mask[w]);
+    const int contrib = states > 5 ? 5 : states - 1;
+    const int variable = present > 1 ? 1 : 0;
+    if (keep)
+        keep[k] = (unsigned char)variable;
+    kept = variable;
+    all = contrib;
+    of_kept = variable ? contrib : 0;
+}
+
+__global__ void __launch_bounds__(LVB_NOALLOC_BLOCK)
+    column_stats_noalloc_kernel(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *out,
+                                long long *scratch)
+{
+    __shared__ long long s_sum[3];
+    __shared__ unsigned s_last;
+    if (threadIdx.x < 3)
+        s_sum[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    long long v[3] = {0, 0, 0};
+    if (k < m)
+        column_stats_of(text, n, m, k, keep, v[0], v[1], v[2]);
+    for (int j = 0; j < 3; j++)
+    {
+        for (int o = 16; o > 0; o >>= 1)
+            v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
+        if ((threadIdx.x & 31) == 0 && v[j])
+            atomicAdd((unsigned long long *)&s_sum[j], (unsigned long long)v[j]);
+    }
+    __syncthreads();
+    /* this CTA's partial sums into the scratch; the CTA that draws the last ticket adds all of them up */
+    long long *part = scratch + LVB_NOALLOC_HEAD;
+    if (threadIdx.x < 3)
+        part[3 * (size_t)blockIdx.x + threadIdx.x] = s_sum[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        __threadfence();
+        s_last = atomicAdd((unsigned *)scratch, 1u) == gridDim.x - 1u ? 1u : 0u;
+        s_sum[0] = s_sum[1] = s_sum[2] = 0;
+    }
+    __syncthreads();
+    if (!s_last)
+        return;
+    __threadfence();
+    long long t[3] = {0, 0, 0};
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+        for (int j = 0; j < 3; j++)
+            t[j] += __ldcg(&part[3 * (size_t)b + j]);
+    for (int j = 0; j < 3; j++)
+    {
+        for (int o = 16; o > 0; o >>= 1)
+            t[j] += __shfl_xor_sync(0xffffffffu, t[j], o);
+        if ((threadIdx.x & 31) == 0 && t[j])
+            atomicAdd((unsigned long long *)&s_sum[j], (unsigned long long)t[j]);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3)
+        out[threadIdx.x] = s_sum[threadIdx.x];
+    if (threadIdx.x == 0)
+        *(unsigned *)scratch = 0u; /* ready for the next call */
+}
+
+cudaError_t launch_column_stats_noalloc(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *out,
+                                        cudaStream_t stream)
+{
+    if (m < 1 || m > (int64_t)LVB_NOALLOC_MAX_COLUMNS)
+        return cudaErrorInvalidValue;
+    /* the device address of the scratch array, taken once per device with that device current (the caller has
+     * made the context's device current); no allocation anywhere on this path */
+    static std::mutex mu;
+    static long long *addr[LVB_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return e;
+    if (dev < 0 || dev >= LVB_MAX_DEVICES)
+        return cudaErrorInvalidDevice;
+    long long *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!addr[dev])
+        {
+            void *ptr = nullptr;
+            if ((e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch)) != cudaSuccess)
+                return e;
+            addr[dev] = static_cast<long long *>(ptr);
+        }
+        scratch = addr[dev];
+    }
+    /* the array keeps the last call's contents: the ticket must start at zero */
+    if ((e = cudaMemsetAsync(scratch, 0, LVB_NOALLOC_HEAD * sizeof(long long), stream)) != cudaSuccess)
+        return e;
+    const unsigned grid = (unsigned)((m + LVB_NOALLOC_BLOCK - 1) / LVB_NOALLOC_BLOCK);
+    column_stats_noalloc_kernel<<<grid, LVB_NOALLOC_BLOCK, 0, stream>>>(text, n, m, keep, out, scratch);
+    return cudaGetLastError();
+}
+
 /* ---- all-reduce of partial lengths over peer memory (site-block mode) ---- */
 __global__ void __launch_bounds__(256) p2p_allreduce_kernel(const __grid_constant__ P2PParams q)
 {

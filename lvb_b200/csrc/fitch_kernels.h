@@ -176,6 +176,13 @@ cudaError_t launch_pack_dna(const unsigned char *text, int64_t n, int64_t m, int
 cudaError_t launch_column_stats(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *sums,
                                 cudaStream_t stream);
 
+/* The same statistics with NO allocation: text, keep (may be NULL) and out[3] (= what launch_column_stats adds into
+ * sums, here written) are the caller's device memory; the scratch of the reduction is a file-scope device array of
+ * fitch_kernels.cu, shared by all calls on a device.  m <= LVB_NOALLOC_MAX_COLUMNS, else cudaErrorInvalidValue. */
+#define LVB_NOALLOC_MAX_COLUMNS (1 << 22)
+cudaError_t launch_column_stats_noalloc(const unsigned char *text, int64_t n, int64_t m, unsigned char *keep, long long *out,
+                                        cudaStream_t stream);
+
 cudaError_t launch_p2p_allreduce(const P2PParams &p, cudaStream_t stream);
 
 } // namespace lvbgpu

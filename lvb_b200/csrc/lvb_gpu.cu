@@ -1339,6 +1339,25 @@ extern "C"
         return 0;
     }
 
+    /* no counterpart in the reference: added (callers that cannot allocate) */
+    int lvb_gpu_column_stats_noalloc(lvb_gpu_ctx *c, int64_t n, int64_t m, const unsigned char *d_text,
+                                     unsigned char *d_keep, int64_t *d_out3)
+    {
+        if (!c || !d_text || !d_out3)
+            return fail("lvb_gpu_column_stats_noalloc: null argument");
+        if (n < 1 || m < 1)
+            return fail("lvb_gpu_column_stats_noalloc: empty alignment");
+        if (m > (int64_t)LVB_NOALLOC_MAX_COLUMNS)
+            return fail("lvb_gpu_column_stats_noalloc: %lld columns, the fixed scratch array holds the partial sums of at "
+                        "most %lld (LVB_GPU_NOALLOC_MAX_COLUMNS); use lvb_gpu_column_stats", (long long)m,
+                        (long long)LVB_NOALLOC_MAX_COLUMNS);
+        CU(cudaSetDevice(c->device));
+        static_assert(sizeof(long long) == sizeof(int64_t), "out3 is written as long long");
+        CU(launch_column_stats_noalloc(d_text, n, m, d_keep, reinterpret_cast<long long *>(d_out3), c->stream));
+        c->launches++;
+        return 0;
+    }
+
     int lvb_gpu_tree_create(lvb_gpu_ctx *c, int *tree)
     {
         if (!c || !tree)
