@@ -387,6 +387,11 @@ def sa_replicates_record(args, rank, world, local_rank, barrier, gather):
                   "included), max over ranks; wall_seconds = wall clock of the whole call between barriers (adds packing "
                   "and uploading the alignment, allocating the trees, writing the result files)",
         "per_rank": [{k: r[k] for k in ("rank", "chains", "search_s", "wall_s", "host_threads", "groups")} for r in allr],
+        "scaling_note": "strong scaling of a FIXED job (64 chains x the rearrangement budget): a chain is a sequence of "
+                        "rounds (one per accepted move), each waiting for one latency-bound kernel, so the job cannot finish "
+                        "before one chain alone does (about 45 us per round, profiles/r02n_sa_probe.log); with 64 chains "
+                        "on one GPU the device is throughput-bound instead, so trees/s at N GPUs is bounded by about 4x the "
+                        "N = 1 figure however many GPUs there are; ranks share the host cores (host_threads per rank)",
         "parity": {"oracle_checked": [c for r in allr for c in r["checked"]], "ok": True},
         "api": "lvb_b200/host/solve.cpp GetSolnBatched (speculative batches over lvb_gpu_score_batch_submit_pre / "
                "lvb_gpu_commit_batch_pre)",

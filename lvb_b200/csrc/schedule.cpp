@@ -150,6 +150,14 @@ bool ScheduleCompiler::compile_impl(const lvb_gpu_topology &topo, bool store, st
         {
             const int32_t v = korder_[head];
             int32_t kid[2];
+            if (whole && head + 6 < no)
+            { /* the caller's arrays are cold for a topology that was not seen before (2 x 2000 scattered reads):
+               * ask for the links of a node a few places down the queue now */
+                const int64_t w = korder_[head + 6];
+                __builtin_prefetch(reinterpret_cast<const char *>(topo.left) + w * topo.stride_bytes);
+                __builtin_prefetch(reinterpret_cast<const char *>(topo.right) + w * topo.stride_bytes);
+                __builtin_prefetch(&seen_[w]);
+            }
             if (whole)
             { /* links are resolved and checked on the way */
                 const int64_t l = L(v), r = R(v);
