@@ -36,8 +36,12 @@ def tiny_msa(n: int):
     return host.HostMSA.from_rows(rows)
 
 
-@pytest.mark.parametrize("n,m,structured", [(500, 100_000, True), (1000, 200_000, False)])
-def test_proposals_at_config_shapes(n, m, structured):
+@pytest.mark.parametrize("n,m,structured,keeping", [(500, 100_000, True, False), (1000, 200_000, False, False),
+                                                    (500, 100_000, True, True), (1000, 200_000, False, True)])
+def test_proposals_at_config_shapes(n, m, structured, keeping):
+    """keeping: the accepted proposal of a round is scored AND kept (lvb_gpu_score_keep) and accepted with
+    lvb_gpu_accept_kept instead of being committed — in two rounds of three; the third commits, so that commits
+    run on trees whose rows sit in both banks"""
     nwords = (m + 15) // 16
     enc = synthetic.packed(n, m, seed=1, p=0.02) if structured else synthetic.random_packed(n, nwords, seed=1)
     eng = Engine(0)
@@ -81,12 +85,17 @@ def test_proposals_at_config_shapes(n, m, structured):
                 if k == pick:
                     keep = (l2.copy(), r2.copy(), dirty, rows[dirty].copy(), chg[dirty].copy(), w)
                 rows[dirty], chg[dirty] = saved_rows, saved_chg  # the proposal is not applied
-            got = eng.score_batch([t] * len(batch), batch)
-            assert got.tolist() == wants, rnd
-            scored += len(batch)
-            # accept one of them: commit on the device, apply on the host tree and in the oracle's rows
             l2, r2, dirty, new_rows, new_chg, w = keep
-            assert eng.commit(t, Topology(l2, r2, cur.root, dirty)) == w, rnd
+            if keeping and rnd % 3 != 2:
+                got, ticket = eng.score_keep([t] * len(batch), batch, [1 if k == pick else 0 for k in range(6)])
+                assert got.tolist() == wants, rnd
+                eng.accept_kept(ticket, [pick])
+            else:
+                got = eng.score_batch([t] * len(batch), batch)
+                assert got.tolist() == wants, rnd
+                # accept one of them: commit on the device, apply on the host tree and in the oracle's rows
+                assert eng.commit(t, Topology(l2, r2, cur.root, dirty)) == w, rnd
+            scored += len(batch)
             rows[dirty], chg[dirty] = new_rows, new_chg
             cur, props[pick] = props[pick], cur  # SwapTrees (TreeOperations.c:1062-1080)
             cur.mark_clean()
