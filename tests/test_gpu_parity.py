@@ -445,8 +445,10 @@ def test_full_size_2000x1M(engine):
     want, rows, chg = oracles.oracle_getplen(enc, left, right, root)
     assert engine.commit(t, Topology(left, right, root)) == want
     assert np.array_equal(engine.changes(t)[n:], chg[n:])
-    for v in (n, n + 999, 2 * n - 4):
-        assert np.array_equal(engine.download_row(t, v), rows[v])
+    # EVERY state row (1 GB), not a sample: the rows at the boundaries of the dependent pieces of the one-launch
+    # route are the ones a scheduling mistake would get wrong
+    bad = [v for v in range(n, 2 * n - 3) if not np.array_equal(engine.download_row(t, v), rows[v])]
+    assert not bad, bad[:10]
     # a candidate: NNI at some deep node, scored incrementally, then committed, then re-evaluated in full
     cands = nni_neighbourhood(left, right, root, n)
     pick = [cands[k] for k in (0, 1777, 3993)]
