@@ -671,6 +671,37 @@ def main():
                 "ms_per_step": w_all / args.steps * 1e3, "per_rank": rr,
                 "workload": f"one whole {n} x {m} tree per GPU per step, alignment replicated, no collective",
             }
+            # ---- candidates of ONE tree sharded over the GPUs (third row): every rank holds the whole
+            # alignment and the same tree and scores its range of the batch; the lengths are gathered by the host
+            from lvb_b200 import sharding as _sh
+
+            eng2.commit(t2, topo)
+            cands, _ = nni_candidates(left, right, root, n, args.candidates, seed=5)
+            first, count = _sh.candidate_range(len(cands), rank, world)
+            mine_c = cands[first:first + count]
+            prepared = eng2.prepare_batch([t2] * count, mine_c)
+            eng2.score_prepared(prepared)
+            calls = []
+            for _ in range(5):
+                barrier()
+                t0 = time.perf_counter()
+                got_c = eng2.score_prepared(prepared).copy()
+                calls.append(max_over_ranks(time.perf_counter() - t0))
+            kms = eng2.last_kernel_ms()
+            parts = gather({"rank": rank, "first": first, "lengths": got_c.tolist(), "kernel_ms": kms})
+            # cross-check: the first candidate of every other rank's range, scored here too
+            probe = [cands[r["first"]] for r in parts if r["lengths"]]
+            probe_len = eng2.score_batch([t2] * len(probe), probe).tolist()
+            ok = probe_len == [r["lengths"][0] for r in parts if r["lengths"]]
+            extras["candidate_shards"] = {
+                "candidates": len(cands), "ms_per_batch": float(np.median(calls)) * 1e3,
+                "candidates_per_s": len(cands) / float(np.median(calls)), "kernel_ms_per_rank": [r["kernel_ms"] for r in parts],
+                "cross_checked": bool(ok),
+                "workload": f"{len(cands)} NNI candidates of one {n} x {m} tree, contiguous ranges over the ranks "
+                            "(sharding.candidate_range), whole alignment and the same tree on every GPU, lengths gathered on "
+                            "the host; the C-ABI call with host topology records, slowest rank, median of 5",
+            }
+            assert ok, "candidate shards: a rank's lengths differ from another rank's for the same candidate"
             eng2.close()
 
     # =================== SA replicates (config 5) ===================

@@ -7,6 +7,11 @@ Two partitions, both from BASELINE.json:
     the same programs; partial tree lengths are summed (one all-reduce of K int64).
   * replicates (configs[4]): independent SA chains, chain r has seed s + r; ranks take
     contiguous ranges of chains and never talk on the data path.
+  * candidates (third row): every rank holds the WHOLE alignment and the same current
+    tree and scores a contiguous range of the K candidates of a batch (an NNI neighbourhood, the
+    speculative proposals of a chain); the K lengths are gathered by the host layer, and the accepted
+    candidate is committed by every rank itself (its dirty rows are recomputed locally: cheaper than
+    shipping them).  No collective on the device side.
 Used by bench.py, by the multi-rank tests, and mirrored in C++ by the host layer (-D).
 """
 from __future__ import annotations
@@ -44,3 +49,9 @@ def replicate_shard(seed: int, replicates: int, rank: int, world: int) -> Tuple[
     """(seed of the rank's first chain, number of chains): chain r always runs with seed + r."""
     first, count = chain_range(replicates, rank, world)
     return seed + first, count
+
+
+def candidate_range(candidates: int, rank: int, world: int) -> Tuple[int, int]:
+    """(first_candidate, count) of `rank` for a batch of `candidates`: contiguous, sizes differ by at most
+    one, every candidate scored exactly once."""
+    return chain_range(candidates, rank, world)

@@ -7,6 +7,9 @@
     whole-alignment lengths of the reference.
   * replicates (configs[4]): lvb_b200.sharding.replicate_shard gives each rank its chains; the
     gathered results must equal the single-process run of all chains.
+  * candidates (SURVEY.md 8(e) third row): every rank holds the whole alignment, scores its range of
+    the NNI neighbourhood's candidates (sharding.candidate_range), the lengths are gathered, and the
+    best candidate is committed by every rank.
 """
 import ctypes as C
 import json
@@ -199,3 +202,95 @@ def test_replicates_sharded_over_two_ranks_gloo(tmp_path):
     for r in range(3):
         assert got[r][1:] == [one[r]["final_length"], one[r]["rearrangements"], one[r]["topologies"], one[r]["start_temperature"]], r
     assert got[0][1] == 1846  # test_treelength_5_thread_2's pin is for seed 509739986; seed 1 reaches the same optimum
+
+
+def _candidate_worker(rank: int, world: int, port: int, out_path: str) -> None:
+    import torch
+    import torch.distributed as dist
+    from lvb_b200.gpu import Topology, _Topo
+    from test_schedule import _nni_candidates
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        g = np.load(os.path.join(HERE, "golden", "example.npz"))
+        enc = np.ascontiguousarray(g["enc"], dtype=np.uint64)
+        n, nwords = enc.shape
+        left, right, root = g["random_left"], g["random_right"], int(g["random_root"])
+        L = _mock_api()
+        ctx = C.c_void_p()
+        assert L.lvb_gpu_init(0, C.byref(ctx)) == 0
+        assert L.lvb_gpu_matrix_upload_flat(ctx, n, nwords, enc.ctypes.data, 0, nwords, 1) == 0  # the WHOLE alignment
+        t = C.c_int(-1)
+        assert L.lvb_gpu_tree_create(ctx, C.byref(t)) == 0
+        ts = Topology(left, right, root).as_struct()
+        cur = C.c_int64(0)
+        assert L.lvb_gpu_tree_commit(ctx, t.value, C.byref(ts), C.byref(cur)) == 0, L.lvb_gpu_last_error()
+        B = 2 * n - 3
+        parent = np.full(B, -1, dtype=np.int64)
+        for v in list(range(n, B)) + [root]:
+            parent[left[v]] = v
+            parent[right[v]] = v
+        cands = []
+        for u, v, a, b, c, l2, r2 in _nni_candidates(left, right, root, n):
+            dirty, w = [], u
+            while w != root:
+                dirty.append(w)
+                w = int(parent[w])
+            cands.append(Topology(l2, r2, root, dirty))
+        K = len(cands)
+        first, count = sharding.candidate_range(K, rank, world)
+        arr = (_Topo * count)()
+        for i in range(count):
+            cands[first + i].fill(arr[i])
+        out = (C.c_int64 * count)()
+        trees = (C.c_int * count)(*([t.value] * count))
+        assert L.lvb_gpu_score_batch(ctx, count, trees, arr, out) == 0, L.lvb_gpu_last_error()
+        # the exchange step: K lengths gathered (ranks hold ranges of different sizes: pad to the largest)
+        width = (K + world - 1) // world
+        mine = torch.full((width,), -1, dtype=torch.int64)
+        mine[:count] = torch.tensor(list(out), dtype=torch.int64)
+        parts = [torch.empty(width, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(parts, mine)
+        lens = []
+        for r in range(world):
+            lens += parts[r][: sharding.candidate_range(K, r, world)[1]].tolist()
+        assert len(lens) == K and min(lens) > 0
+        # the winner (first of the shortest) is committed by EVERY rank on its own copy of the tree
+        best = int(np.argmin(lens))
+        bs = cands[best].as_struct()
+        got = C.c_int64(0)
+        assert L.lvb_gpu_tree_commit(ctx, t.value, C.byref(bs), C.byref(got)) == 0, L.lvb_gpu_last_error()
+        agree = torch.tensor([got.value, best], dtype=torch.int64)
+        both = [torch.empty(2, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(both, agree)
+        L.lvb_gpu_shutdown(ctx)
+        if rank == 0:
+            json.dump({"current": int(cur.value), "lengths": lens, "best": best, "committed": [b.tolist() for b in both],
+                       "range0": [first, count]}, open(out_path, "w"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_candidates_sharded_over_two_ranks_gloo(tmp_path):
+    import torch.multiprocessing as mp
+
+    import oracles
+    from test_schedule import _nni_candidates
+
+    for world in (1, 2, 3, 8):
+        rs = [sharding.candidate_range(194, r, world) for r in range(world)]
+        assert rs[0][0] == 0 and sum(c for _, c in rs) == 194 and all(b0 + c0 == b1 for (b0, c0), (b1, _) in zip(rs, rs[1:]))
+    out = str(tmp_path / "candidates.json")
+    mp.spawn(_candidate_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = json.load(open(out))
+    g = np.load(os.path.join(HERE, "golden", "example.npz"))
+    enc, root = g["enc"], int(g["random_root"])
+    n = enc.shape[0]
+    cands = list(_nni_candidates(g["random_left"], g["random_right"], root, n))
+    assert got["current"] == 11808 and len(got["lengths"]) == len(cands) == 2 * (n - 3)
+    assert got["range0"] == [0, n - 3]  # rank 0 scored the first half only
+    for k in list(range(0, len(cands), 17)) + [got["best"], len(cands) - 1]:
+        u, v, a, b, c, l2, r2 = cands[k]
+        assert got["lengths"][k] == oracles.oracle_getplen(enc, l2, r2, root)[0], k
+    assert got["lengths"][got["best"]] == min(got["lengths"])
+    assert got["committed"] == [[got["lengths"][got["best"]], got["best"]]] * 2  # both ranks hold the same new tree
