@@ -631,7 +631,8 @@ def main():
                 "l2_hit_pct": prof.get("score_l2_hit_pct"), "alu_pipe_pct": prof.get("score_alu_pipe_pct"),
                 "issue_pct": prof.get("score_issue_pct"),
                 "operand_gbs": operand_gbs, "operand_frac": operand_gbs / peak,
-                "rows_read_per_candidate": rows_read_mean, "kernel": "fitch_score_kernel", "kernel_ms_per_batch": score_ms,
+                "rows_read_per_candidate": rows_read_mean, "kernel": prof.get("score_kernel", "fitch_score2_kernel"),
+                "kernel_ms_per_batch": score_ms,
                 "note": "achieved/frac = DRAM bytes per batch of the committed ncu capture / this run's kernel time / HBM peak "
                         "(low by design: 80 % of the operand sectors hit L2); what bounds the kernel is instruction issue, "
                         "alu_pipe_pct / issue_pct of the same capture; operand_* = 8 B x nwords x (clean rows read) per "

@@ -1710,14 +1710,21 @@ cudaError_t launch_fitch_exec(const ExecParams &p, bool per_node, int block, cud
             return e;
         fitch_pipe_kernel<false><<<grid, block, sm, stream>>>(p);
     }
-    else if (score2_enabled() && (long long)p.n_prog * ((p.ncols + 2 * block - 1) / (2 * block)) >= 4ll * 148 * 6)
+    else if (score2_enabled() && (long long)p.n_prog * ((p.ncols + 511) / 512) >= 4ll * 148 * 6)
     { /* many candidates: two columns per thread (issue-bound regime); the column blocks are twice as wide */
+        static const int b2 = [] {
+            const char *e = getenv("LVB_GPU_SCORE2_BLOCK"); /* threads per CTA of this kernel (A/B runs) */
+            return (e && atoi(e) >= 32) ? atoi(e) / 32 * 32 : 0;
+        }();
+        /* 128 threads: 5 CTAs of 4 warps per SM instead of 2 of 8 (the ring of a CTA holds 4 operands x 2 columns per
+         * thread): 0.683 -> 0.645 ms per 512 candidates of a 2000 x 1M tree (profiles/r02am_score2_block.log) */
+        const int blk = b2 ? std::min(b2, 256) : std::min(block, 128);
         ExecParams q = p;
-        q.n_colblocks = (p.ncols + 2 * block - 1) / (2 * block);
-        const size_t sm = (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(4 * LVB_RING + 2 * p.n_slots) * block) * sizeof(uint4);
+        q.n_colblocks = (p.ncols + 2 * blk - 1) / (2 * blk);
+        const size_t sm = (size_t)(LVB_CHUNK + 2 * LVB_RING + (size_t)(4 * LVB_RING + 2 * p.n_slots) * blk) * sizeof(uint4);
         if ((e = want_smem(fitch_score2_kernel, sm)) != cudaSuccess)
             return e;
-        fitch_score2_kernel<<<(unsigned)q.n_prog * (unsigned)q.n_colblocks, block, sm, stream>>>(q);
+        fitch_score2_kernel<<<(unsigned)q.n_prog * (unsigned)q.n_colblocks, blk, sm, stream>>>(q);
     }
     else
     {

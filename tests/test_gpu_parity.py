@@ -680,3 +680,29 @@ def test_trace_of_a_store_launch(monkeypatch):
         assert (d[:, [0, 1, 3, 4]] >= 0).all()  # ticket <= decoded <= published; first operand <= last step <= books
     finally:
         eng.close()
+
+
+def test_large_score_batch_two_columns_per_thread():
+    """a score launch of thousands of CTAs goes through fitch_score2_kernel (two columns per thread): every NNI
+    candidate of a 150-taxon tree on a ragged 200 003-site alignment (the last column block is partly empty, the
+    second column of its threads wholly), against the oracle"""
+    n, m = 150, 200_003
+    enc = synthetic.pack_states(synthetic.states(n, m, seed=9, p=0.1))
+    left, right, root = synthetic.random_topology(n, seed=9)
+    eng = Engine(0)
+    try:
+        eng.upload(enc, max_trees=1)
+        t = eng.tree_create()
+        want, rows, chg = oracles.oracle_getplen(enc, left, right, root)
+        assert eng.commit(t, Topology(left, right, root)) == want
+        cands = nni_neighbourhood(left, right, root, n)
+        assert len(cands) * ((enc.shape[1] // 2 + 511) // 512) >= 4 * 148 * 6  # enough CTAs for the two-column route
+        got = eng.score_batch([t] * len(cands), cands)
+        for k in range(len(cands)):
+            if k % 3 == 0 or k > len(cands) - 4:
+                assert got[k] == oracles.oracle_getplen(enc, cands[k].left, cands[k].right, root)[0], k
+        # the same candidates in small batches (the one-column kernels) give the same lengths
+        small = np.concatenate([eng.score_batch([t] * 6, cands[i:i + 6]) for i in range(0, 60, 6)])
+        assert np.array_equal(small, got[:60])
+    finally:
+        eng.close()

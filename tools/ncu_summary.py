@@ -88,12 +88,13 @@ def main() -> None:
         tj.update({"kernel": "fitch_stream_kernel", "grid": stream[0][hdr.index("Grid Size")], "launches_averaged": len(stream),
                    "dram_bytes_read_per_pass": rd, "dram_bytes_write_per_pass": wr, "dram_bytes_per_pass": rd + wr,
                    "duration_us_under_ncu": us, "source": rel, "command": command})
-    score = [r for r in data if name(r).startswith("fitch_score_kernel")]
+    score = [r for r in data if name(r).startswith("fitch_score2_kernel")] or \
+            [r for r in data if name(r).startswith("fitch_score_kernel")]
     if score:
         rd = sum(val(r, "dram__bytes_read.sum") for r in score) / len(score)
         wr = sum(val(r, "dram__bytes_write.sum") for r in score) / len(score)
         pick = lambda k: sum(float(r[hdr.index(k)]) for r in score) / len(score)
-        tj.update({"score_kernel": "fitch_score_kernel (512 NNI candidates of a 2000 x 1M tree)",
+        tj.update({"score_kernel": name(score[0]).split("(")[0] + " (512 NNI candidates of a 2000 x 1M tree)",
                    "score_dram_bytes_per_batch": rd + wr, "score_duration_us_under_ncu": pick("gpu__time_duration.sum"),
                    "score_l2_hit_pct": pick("lts__t_sector_hit_rate.pct"),
                    "score_alu_pipe_pct": pick("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
